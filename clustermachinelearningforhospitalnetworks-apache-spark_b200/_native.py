@@ -1,0 +1,112 @@
+"""ctypes binding of csrc/libhkm.so (the C ABI in include/hkm.h).
+
+There is deliberately NO fallback: if the CUDA library is missing or no GPU is present the
+product path raises.  PyTorch is used only for device memory and streams.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "csrc", "libhkm.so")
+
+EXPORTS = (
+    "hkm_last_error", "hkm_version", "hkm_max_k", "hkm_max_d",
+    "hkm_assign_reduce_scratch_bytes", "hkm_assign_reduce", "hkm_update_centers",
+)
+
+_lib = None
+
+
+class HkmError(RuntimeError):
+    pass
+
+
+class LloydState(ctypes.Structure):
+    _fields_ = [("cost", ctypes.c_double), ("iter", ctypes.c_int32), ("converged", ctypes.c_int32),
+                ("max_shift2", ctypes.c_double), ("reserved", ctypes.c_int64)]
+
+
+STATE_BYTES = ctypes.sizeof(LloydState)
+
+
+def load() -> ctypes.CDLL:
+    """Load libhkm.so; raises if it has not been built (python __graft_entry__.py / _build.py)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise HkmError(f"{SO_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'`. "
+                           "There is no CPU fallback.")
+        L = ctypes.CDLL(SO_PATH)
+        vp, i32, i64, sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_size_t
+        L.hkm_last_error.restype = ctypes.c_char_p
+        L.hkm_assign_reduce_scratch_bytes.restype = sz
+        L.hkm_assign_reduce_scratch_bytes.argtypes = [i32, i32]
+        L.hkm_assign_reduce.argtypes = [vp, i64, i32, vp, i32, vp, vp, vp, vp, vp, i32, vp, sz, vp]
+        L.hkm_update_centers.argtypes = [vp, i32, i32, vp, ctypes.c_double, vp, vp]
+        _lib = L
+    return _lib
+
+
+def _check(rc: int) -> None:
+    if rc != 0:
+        raise HkmError(f"libhkm error {rc}: {load().hkm_last_error().decode()}")
+
+
+def require_cuda(t: torch.Tensor, name: str, dtype=None) -> None:
+    if not t.is_cuda:
+        raise HkmError(f"{name} must be a CUDA tensor (no CPU fallback)")
+    if not t.is_contiguous():
+        raise HkmError(f"{name} must be contiguous")
+    if dtype is not None and t.dtype != dtype:
+        raise HkmError(f"{name} must be {dtype}, got {t.dtype}")
+
+
+def _ptr(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def assign_reduce_scratch_bytes(d: int, k: int) -> int:
+    return int(load().hkm_assign_reduce_scratch_bytes(d, k))
+
+
+def new_scratch(d: int, k: int, device) -> torch.Tensor:
+    with torch.cuda.device(device):
+        nbytes = assign_reduce_scratch_bytes(d, k)
+    return torch.zeros((nbytes + 7) // 8, dtype=torch.int64, device=device)
+
+
+def new_state(device) -> torch.Tensor:
+    return torch.zeros(STATE_BYTES // 8, dtype=torch.int64, device=device)
+
+
+def read_state(state: torch.Tensor) -> LloydState:
+    raw = state.cpu().numpy().tobytes()
+    return LloydState.from_buffer_copy(raw)
+
+
+def assign_reduce(X, C, partial=None, labels=None, mind2=None, weights=None, state=None, scratch=None, do_reduce=True):
+    """One Lloyd data pass on the current stream (hkm_assign_reduce)."""
+    require_cuda(X, "X", torch.float64)
+    require_cuda(C, "C", torch.float64)
+    n, d = X.shape
+    k = C.shape[0]
+    with torch.cuda.device(X.device):
+        rc = load().hkm_assign_reduce(_ptr(X), n, d, _ptr(C), k, _ptr(weights), _ptr(partial), _ptr(labels), _ptr(mind2),
+                                      _ptr(state), int(do_reduce), _ptr(scratch),
+                                      scratch.numel() * scratch.element_size() if scratch is not None else 0, _stream())
+    _check(rc)
+
+
+def update_centers(partial, C, tol: float, state):
+    k, d = C.shape
+    with torch.cuda.device(C.device):
+        rc = load().hkm_update_centers(_ptr(partial), k, d, _ptr(C), float(tol), _ptr(state), _stream())
+    _check(rc)

@@ -1,0 +1,125 @@
+// C ABI of libhkm (see include/hkm.h): argument checks, kernel dispatch, small driver kernels.
+#include "../../include/hkm.h"
+#include "hkm_lloyd_launch.cuh"
+#include <cstring>
+#include <mutex>
+
+namespace hkm {
+
+static thread_local char g_err[512] = "";
+void set_error(const char* fmt, ...) {
+  va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof(g_err), fmt, ap); va_end(ap);
+}
+int cuda_fail(cudaError_t e, const char* what) {
+  set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+  return HKM_ERR_CUDA;
+}
+int sm_count() {
+  static int cached[64]; static bool have[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (!have[dev]) {
+    int v = 0;
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+    cached[dev] = v; have[dev] = true;
+  }
+  return cached[dev];
+}
+
+// ------------------------------------------------------------------ Lloyd pass dispatch (per-NT translation units)
+static int dispatch_lloyd(const LloydParams& p, const LaunchPlan& pl, int grid, cudaStream_t st) {
+  switch ((p.k + 7) / 8) {
+    case 1: return dispatch_lloyd_nt1(p, pl, grid, st);
+    case 2: return dispatch_lloyd_nt2(p, pl, grid, st);
+    case 3: return dispatch_lloyd_nt3(p, pl, grid, st);
+    case 4: return dispatch_lloyd_nt4(p, pl, grid, st);
+    case 5: return dispatch_lloyd_nt5(p, pl, grid, st);
+    case 6: return dispatch_lloyd_nt6(p, pl, grid, st);
+    case 7: return dispatch_lloyd_nt7(p, pl, grid, st);
+    case 8: return dispatch_lloyd_nt8(p, pl, grid, st);
+  }
+  set_error("k=%d outside the fp64 kernel range (max %d)", p.k, 64);
+  return HKM_ERR_UNSUPPORTED;
+}
+
+// ------------------------------------------------------------------ centre update
+__global__ void update_centers_kernel(const double* __restrict__ partial, int k, int d, double* __restrict__ C, double tol2,
+                                      hkm_lloyd_state* __restrict__ state) {
+  if (state->converged != 0) return;
+  __shared__ double s_shift[64];
+  const int j = threadIdx.x;  // one thread per cluster (k <= 64)
+  double shift = -1.0;
+  if (j < k) {
+    const double wsum = partial[(size_t)k * d + j];
+    if (wsum > 0) {
+      const double inv = 1.0 / wsum;  // scal(1.0 / weightSum, sum)
+      double s = 0;
+      for (int f = 0; f < d; ++f) {
+        const double nc = partial[(size_t)j * d + f] * inv;
+        const double df = nc - C[(size_t)j * d + f];
+        s = fma(df, df, s);
+        C[(size_t)j * d + f] = nc;
+      }
+      shift = s;
+    }
+  }
+  s_shift[j] = shift;
+  __syncthreads();
+  if (j == 0) {
+    double mx = -1.0;
+    for (int i = 0; i < k; ++i) mx = fmax(mx, s_shift[i]);
+    state->cost = partial[(size_t)k * d + k];
+    state->iter += 1;
+    state->max_shift2 = mx < 0 ? 0.0 : mx;
+    state->converged = (mx <= tol2) ? 1 : 0;  // every updated centre within tol (none updated => converged)
+  }
+}
+
+}  // namespace hkm
+
+using namespace hkm;
+
+extern "C" {
+
+const char* hkm_last_error(void) { return g_err; }
+int hkm_version(void) { return 100; }
+int hkm_max_k(void) { return 64; }
+int hkm_max_d(void) { return 128; }
+
+size_t hkm_assign_reduce_scratch_bytes(int d, int k) {
+  if (d < 1 || k < 1) return 0;
+  const int k_pad = ((k + 7) / 8) * 8;
+  LaunchPlan pl = plan_lloyd(d, k_pad);
+  size_t grid = (size_t)sm_count() * pl.ctas_per_sm;
+  return 256 + grid * ((size_t)k * d + k + 1) * sizeof(double);
+}
+
+int hkm_assign_reduce(const double* X, int64_t n, int d, const double* C, int k, const double* weights, double* partial_out,
+                      int32_t* labels_out, double* mind2_out, const hkm_lloyd_state* state, int do_reduce, void* scratch,
+                      size_t scratch_bytes, void* stream) {
+  if (n < 0 || d < 1 || k < 1 || (n > 0 && X == nullptr) || C == nullptr) { set_error("hkm_assign_reduce: bad X/C/n/d/k"); return HKM_ERR_INVALID; }
+  if (d > hkm_max_d() || k > hkm_max_k()) { set_error("hkm_assign_reduce: d=%d k=%d outside fp64 kernel range (d<=%d, k<=%d)", d, k, hkm_max_d(), hkm_max_k()); return HKM_ERR_UNSUPPORTED; }
+  if ((reinterpret_cast<uintptr_t>(X) & 15) != 0) { set_error("hkm_assign_reduce: X must be 16-byte aligned"); return HKM_ERR_INVALID; }
+  if (do_reduce && (partial_out == nullptr || scratch == nullptr)) { set_error("hkm_assign_reduce: reduce needs partial_out and scratch"); return HKM_ERR_INVALID; }
+  if (do_reduce && scratch_bytes < hkm_assign_reduce_scratch_bytes(d, k)) { set_error("hkm_assign_reduce: scratch too small (%zu < %zu)", scratch_bytes, hkm_assign_reduce_scratch_bytes(d, k)); return HKM_ERR_INVALID; }
+  const int k_pad = ((k + 7) / 8) * 8;
+  LaunchPlan pl = plan_lloyd(d, k_pad);
+  if (pl.stages < 2) { set_error("hkm_assign_reduce: d=%d does not fit the shared-memory ring", d); return HKM_ERR_UNSUPPORTED; }
+  LloydParams p{};
+  p.X = X; p.n = n; p.d = d; p.k = k; p.C = C; p.w = weights; p.partial_out = partial_out; p.labels_out = labels_out;
+  p.mind2_out = mind2_out; p.skip = state ? &state->converged : nullptr; p.do_reduce = do_reduce;
+  p.counter = reinterpret_cast<unsigned int*>(scratch);
+  p.cta_partials = scratch ? reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(scratch) + 256) : nullptr;
+  p.stages = pl.stages; p.ks = (d + 3) / 4;
+  const int grid = sm_count() * pl.ctas_per_sm;
+  return dispatch_lloyd(p, pl, grid, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int hkm_update_centers(const double* partial, int k, int d, double* C_inout, double tol, hkm_lloyd_state* state, void* stream) {
+  if (partial == nullptr || C_inout == nullptr || state == nullptr || k < 1 || k > hkm_max_k() || d < 1) { set_error("hkm_update_centers: bad arguments"); return HKM_ERR_INVALID; }
+  update_centers_kernel<<<1, 64, 0, reinterpret_cast<cudaStream_t>(stream)>>>(partial, k, d, C_inout, tol * tol, state);
+  HKM_CUDA_TRY(cudaGetLastError());
+  return HKM_OK;
+}
+
+}  // extern "C"

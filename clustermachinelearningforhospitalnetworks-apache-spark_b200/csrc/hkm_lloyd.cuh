@@ -1,0 +1,361 @@
+// Lloyd data pass: fused assign (fp64 DMMA score tiles + shuffle argmin) and per-cluster
+// sum/count/cost reduction, X streamed once from HBM through a bulk-async (TMA 1-D) ring.
+//
+// Replaces, per row, mllib EuclideanDistanceMeasure.findClosest + updateClusterSum + costAccum
+// (SURVEY 8a-4/8a-5); Spark runs these as scalar JVM loops inside mapPartitions.
+//
+// Tile geometry (kTileRows = 128 rows per stage): the tile is fetched as 8 chunks of 16
+// consecutive rows; chunk c lands at smem offset c * (16*d*8 + 32).  MMA sub-tile i (0..15)
+// takes row i of every chunk, so the 8 rows of one DMMA A-fragment sit 32 bytes apart modulo
+// 128 and the LDS.64 fragment loads are bank-conflict free for every d.
+//
+// Phase 1 (per warp, two sub-tiles): score_j = x.c_j - 0.5|c_j|^2 by DMMA.8x8x4, argmax over j
+//   (lowest index wins ties, as findClosest's strict '<'), dist = max(|x|^2 - 2 score, 0).
+// Phase 2 (after one CTA barrier): warp w owns clusters w, w+8, ...; it ballots the tile's
+//   labels and adds the rows of its clusters, one feature per lane, into REGISTER accumulators
+//   -- no atomics, no contention, fixed summation order.
+// Tail: per-CTA partials -> global scratch; the last CTA to finish sums them in CTA order, so
+// results are bit-stable run to run.
+#pragma once
+#include "hkm_common.cuh"
+
+namespace hkm {
+
+constexpr int kComputeWarps = 8;
+constexpr int kComputeThreads = kComputeWarps * 32;
+constexpr int kThreads = kComputeThreads + 32;  // + producer warp
+constexpr int kTileRows = 128;
+constexpr int kChunks = 8;
+constexpr int kChunkRows = kTileRows / kChunks;  // 16
+constexpr int kChunkPad = 32;                    // bytes
+constexpr int kMaxStages = 8;
+
+struct LloydParams {
+  const double* X;
+  int64_t n;
+  int d;
+  int k;
+  const double* C;
+  const double* w;         // nullable
+  double* partial_out;     // [k*d + k + 1]
+  int32_t* labels_out;     // nullable
+  double* mind2_out;       // nullable
+  const int32_t* skip;     // nullable: device flag, nonzero => no-op
+  int do_reduce;
+  double* cta_partials;    // scratch: [gridDim.x][k*d + k + 1]
+  unsigned int* counter;   // scratch: zero before launch; left zero
+  int stages;
+  int ks;                  // ceil(d/4)
+};
+
+__host__ __device__ inline int chunk_stride_bytes(int d) { return kChunkRows * d * 8 + kChunkPad; }
+__host__ __device__ inline int stage_bytes(int d) { return kChunks * chunk_stride_bytes(d); }
+__host__ __device__ inline int cs_ld(int d) { return ((d + 3) & ~3) + 4; }  // padded centre row (doubles), == 4 mod 8 when d%8==0
+
+// dynamic smem carve-up (bytes), all 16-byte aligned
+struct SmemLayout {
+  int x_off, labels_off, mind2_off, cs_off, cn_off, red_off, bar_off, total;
+};
+__host__ __device__ inline SmemLayout smem_layout(int d, int k_pad, int stages) {
+  SmemLayout L;
+  int o = 0;
+  L.x_off = o; o += stages * stage_bytes(d); o = (o + 127) & ~127;
+  L.labels_off = o; o += 2 * kTileRows * 4;
+  L.mind2_off = o; o += 2 * kTileRows * 8;
+  L.cs_off = o; o += k_pad * cs_ld(d) * 8;
+  L.cn_off = o; o += k_pad * 8;
+  L.red_off = o; o += kComputeWarps * 8 + 16;
+  L.bar_off = o; o += 2 * kMaxStages * 8;
+  L.total = o;
+  return L;
+}
+
+// KS_T > 0: centre B-fragments live in registers (d_pad = 4*KS_T, fully unrolled);
+// KS_T == 0: B-fragments are re-read from shared memory, runtime k-step count.
+// NT = ceil(k/8) score column tiles == clusters owned per warp in phase 2.
+// LPR = lanes per row in phase 2 (8/16/32), FPL = features per lane (d > 32).
+template <int KS_T, int NT, int LPR, int FPL, int MINB>
+__global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydParams p) {
+  if (p.skip != nullptr && *p.skip != 0) return;
+
+  extern __shared__ __align__(128) unsigned char smem[];
+  const int d = p.d, k = p.k;
+  const int k_pad = NT * 8;
+  const int KS = KS_T > 0 ? KS_T : p.ks;
+  const SmemLayout L = smem_layout(d, k_pad, p.stages);
+  int* labels_s = reinterpret_cast<int*>(smem + L.labels_off);
+  double* mind2_s = reinterpret_cast<double*>(smem + L.mind2_off);
+  double* Cs = reinterpret_cast<double*>(smem + L.cs_off);
+  double* cn_s = reinterpret_cast<double*>(smem + L.cn_off);
+  double* red_s = reinterpret_cast<double*>(smem + L.red_off);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + L.bar_off);
+  uint64_t* empty = full + kMaxStages;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int stages = p.stages;
+  const int csld = cs_ld(d);
+  const int cstride = chunk_stride_bytes(d);
+  const int sbytes = stage_bytes(d);
+
+  const int64_t full_tiles = p.n / kTileRows;
+  const int tail_rows = (int)(p.n - full_tiles * kTileRows);
+
+  if (tid == 0) {
+    for (int s = 0; s < stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], kComputeWarps); }
+    mbar_fence_init();
+  }
+  // stage centres: Cs[j][f] (zero padded), cn_s[j] = -0.5|c_j|^2 (-inf for padding)
+  for (int i = tid; i < k_pad * csld; i += kThreads) {
+    int j = i / csld, f = i - j * csld;
+    Cs[i] = (j < k && f < d) ? p.C[(size_t)j * d + f] : 0.0;
+  }
+  __syncthreads();
+  for (int j = tid; j < k_pad; j += kThreads) {
+    double s = 0;
+    for (int f = 0; f < d; ++f) s = fma(Cs[j * csld + f], Cs[j * csld + f], s);
+    cn_s[j] = j < k ? -0.5 * s : -__longlong_as_double(0x7ff0000000000000LL);
+  }
+  __syncthreads();
+
+  // ===================================================================== producer warp
+  if (warp == kComputeWarps) {
+    if (lane == 0) {
+      int s = 0; uint32_t ph = 0;
+      const uint32_t cbytes = (uint32_t)(kChunkRows * d * 8);
+      for (int64_t t = blockIdx.x; t < full_tiles; t += gridDim.x) {
+        mbar_wait(&empty[s], ph ^ 1);
+        mbar_expect_tx(&full[s], cbytes * kChunks);
+        const unsigned char* src = reinterpret_cast<const unsigned char*>(p.X) + (size_t)t * kTileRows * d * 8;
+        unsigned char* dst = smem + L.x_off + (size_t)s * sbytes;
+#pragma unroll
+        for (int c = 0; c < kChunks; ++c) bulk_g2s(dst + c * cstride, src + (size_t)c * cbytes, cbytes, &full[s]);
+        if (++s == stages) { s = 0; ph ^= 1; }
+      }
+    }
+    return;
+  }
+
+  // ===================================================================== compute warps
+  const int r = lane >> 2, q = lane & 3;
+
+  // centre B-fragments: lane (n = r, q) holds C[8*nt + n][4*s + q]
+  double breg[KS_T > 0 ? KS_T * NT : 1];
+  if (KS_T > 0) {
+#pragma unroll
+    for (int s = 0; s < (KS_T > 0 ? KS_T : 1); ++s)
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) breg[s * NT + nt] = Cs[(8 * nt + r) * csld + 4 * s + q];
+  }
+  double cinit[NT][2];
+#pragma unroll
+  for (int nt = 0; nt < NT; ++nt) { cinit[nt][0] = cn_s[8 * nt + 2 * q]; cinit[nt][1] = cn_s[8 * nt + 2 * q + 1]; }
+
+  // phase-2 register accumulators: cluster warp + 8*m, features (lane % LPR) + 32*e
+  double acc_a[NT][FPL], acc_b[NT][FPL];
+  double cnt[NT];
+#pragma unroll
+  for (int m = 0; m < NT; ++m) {
+    cnt[m] = 0;
+#pragma unroll
+    for (int e = 0; e < FPL; ++e) { acc_a[m][e] = 0; acc_b[m][e] = 0; }
+  }
+  double cost = 0;
+  const int sub = lane / LPR, fl = lane % LPR;
+  constexpr int RPS = 32 / LPR;  // rows handled per warp load step
+  const bool has_w = p.w != nullptr;
+
+  auto process_tile = [&](const unsigned char* xs, int rows_valid, int64_t row0, int buf) {
+    // ---------------- phase 1: two MMA sub-tiles per warp (rows i0 / i1 of every chunk)
+    const int i0 = warp, i1 = warp + 8;
+    const double* xa = reinterpret_cast<const double*>(xs + r * cstride) + q;
+    const double* xa0 = xa + i0 * d;
+    const double* xa1 = xa + i1 * d;
+    double s0[NT][2], s1[NT][2];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) { s0[nt][0] = cinit[nt][0]; s0[nt][1] = cinit[nt][1]; s1[nt][0] = cinit[nt][0]; s1[nt][1] = cinit[nt][1]; }
+    double xx0 = 0, xx1 = 0;
+    if (KS_T > 0) {
+#pragma unroll
+      for (int s = 0; s < (KS_T > 0 ? KS_T : 1); ++s) {
+        const bool ok = (s < KS_T - 1) || (4 * s + q < d);
+        double a0 = ok ? xa0[4 * s] : 0.0, a1 = ok ? xa1[4 * s] : 0.0;
+        xx0 = fma(a0, a0, xx0); xx1 = fma(a1, a1, xx1);
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) { dmma884(s0[nt][0], s0[nt][1], a0, breg[s * NT + nt]); dmma884(s1[nt][0], s1[nt][1], a1, breg[s * NT + nt]); }
+      }
+    } else {
+      const double* cb = Cs + r * csld + q;
+      for (int s = 0; s < KS; ++s) {
+        const bool ok = 4 * s + q < d;
+        double a0 = ok ? xa0[4 * s] : 0.0, a1 = ok ? xa1[4 * s] : 0.0;
+        xx0 = fma(a0, a0, xx0); xx1 = fma(a1, a1, xx1);
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+          double b = cb[(8 * nt) * csld + 4 * s];
+          dmma884(s0[nt][0], s0[nt][1], a0, b); dmma884(s1[nt][0], s1[nt][1], a1, b);
+        }
+      }
+    }
+    // argmax over this lane's columns (ascending index), then across the 4 lanes of the row
+    double b0 = s0[0][0], b1 = s1[0][0]; int j0 = 2 * q, j1 = 2 * q;
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        if (nt == 0 && e == 0) continue;
+        const int j = 8 * nt + 2 * q + e;
+        if (s0[nt][e] > b0) { b0 = s0[nt][e]; j0 = j; }
+        if (s1[nt][e] > b1) { b1 = s1[nt][e]; j1 = j; }
+      }
+#pragma unroll
+    for (int msk = 1; msk <= 2; msk <<= 1) {
+      double o0 = shfl_xor_d(b0, msk), o1 = shfl_xor_d(b1, msk);
+      int oj0 = __shfl_xor_sync(0xffffffffu, j0, msk), oj1 = __shfl_xor_sync(0xffffffffu, j1, msk);
+      if (o0 > b0 || (o0 == b0 && oj0 < j0)) { b0 = o0; j0 = oj0; }
+      if (o1 > b1 || (o1 == b1 && oj1 < j1)) { b1 = o1; j1 = oj1; }
+      xx0 += shfl_xor_d(xx0, msk); xx1 += shfl_xor_d(xx1, msk);
+    }
+    if (q == 0) {
+      const int t0 = r * kChunkRows + i0, t1 = r * kChunkRows + i1;
+      const bool v0 = t0 < rows_valid, v1 = t1 < rows_valid;
+      double d0 = fmax(fma(-2.0, b0, xx0), 0.0), d1 = fmax(fma(-2.0, b1, xx1), 0.0);
+      if (has_w) { if (v0) cost = fma(d0, p.w[row0 + t0], cost); if (v1) cost = fma(d1, p.w[row0 + t1], cost); }
+      else { if (v0) cost += d0; if (v1) cost += d1; }
+      labels_s[buf * kTileRows + t0] = v0 ? j0 : -1;
+      labels_s[buf * kTileRows + t1] = v1 ? j1 : -1;
+      if (p.mind2_out != nullptr) { mind2_s[buf * kTileRows + t0] = d0; mind2_s[buf * kTileRows + t1] = d1; }
+    }
+    named_bar_sync(1, kComputeThreads);
+
+    // ---------------- outputs (coalesced from smem)
+    if (p.labels_out != nullptr && tid < kTileRows && tid < rows_valid) p.labels_out[row0 + tid] = labels_s[buf * kTileRows + tid];
+    if (p.mind2_out != nullptr && tid >= kTileRows && (tid - kTileRows) < rows_valid)
+      p.mind2_out[row0 + tid - kTileRows] = mind2_s[buf * kTileRows + tid - kTileRows];
+
+    // ---------------- phase 2: owner warps gather their clusters' rows
+    if (p.do_reduce) {
+#pragma unroll 1
+      for (int g = 0; g < kTileRows / 32; ++g) {
+        const int lab = labels_s[buf * kTileRows + g * 32 + lane];
+#pragma unroll
+        for (int m = 0; m < NT; ++m) {
+          const int j = warp + 8 * m;
+          unsigned mask = __ballot_sync(0xffffffffu, lab == j);
+          if (!has_w) cnt[m] += (double)__popc(mask);
+          while (mask) {
+            // next 4 member rows (tile-relative), -1 when exhausted
+            int rr[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) { rr[u] = mask ? (__ffs(mask) - 1) : -1; mask &= mask - 1; }
+            // lane group `sub` takes rows sub, sub+RPS, ... of these four
+#pragma unroll
+            for (int u = 0; u < 4 / RPS; ++u) {
+              int rsel = rr[u * RPS];
+#pragma unroll
+              for (int z = 1; z < RPS; ++z) rsel = (sub == z) ? rr[u * RPS + z] : rsel;
+              const bool okr = rsel >= 0;
+              const int t = g * 32 + (okr ? rsel : 0);
+              const double* xr = reinterpret_cast<const double*>(xs + (t >> 4) * cstride) + (t & 15) * d;
+              double wv = 1.0;
+              if (has_w) { wv = okr ? p.w[row0 + t] : 0.0; if (fl == 0 && okr) cnt[m] += wv; }
+#pragma unroll
+              for (int e = 0; e < FPL; ++e) {
+                const int f = fl + 32 * e;
+                double v = (okr && f < d) ? xr[f] : 0.0;
+                if (has_w) v *= wv;
+                if (u & 1) acc_b[m][e] += v; else acc_a[m][e] += v;
+              }
+            }
+          }
+        }
+      }
+    }
+  };
+
+  // main loop over this CTA's full tiles
+  {
+    int s = 0; uint32_t ph = 0; int buf = 0;
+    for (int64_t t = blockIdx.x; t < full_tiles; t += gridDim.x) {
+      mbar_wait(&full[s], ph);
+      process_tile(smem + L.x_off + (size_t)s * sbytes, kTileRows, t * kTileRows, buf);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&empty[s]);
+      if (++s == stages) { s = 0; ph ^= 1; }
+      buf ^= 1;
+    }
+    // ragged tail (< 128 rows): the CTA next in round-robin order loads it with plain loads
+    if (tail_rows > 0 && (int)(full_tiles % gridDim.x) == (int)blockIdx.x) {
+      named_bar_sync(1, kComputeThreads);  // every warp is done with all stages
+      unsigned char* xs = smem + L.x_off;
+      const double* src = p.X + (size_t)full_tiles * kTileRows * d;
+      for (int i = tid; i < kTileRows * d; i += kComputeThreads) {
+        int t = i / d, f = i - t * d;
+        double v = t < tail_rows ? src[(size_t)t * d + f] : 0.0;
+        reinterpret_cast<double*>(xs + (t >> 4) * cstride)[(t & 15) * d + f] = v;
+      }
+      named_bar_sync(1, kComputeThreads);
+      process_tile(xs, tail_rows, full_tiles * kTileRows, buf);
+    }
+  }
+  if (!p.do_reduce) return;
+
+  // ===================================================================== CTA-level combine
+  const int P = k * d + k + 1;
+  // cost: warp shuffle, then across warps through smem
+#pragma unroll
+  for (int msk = 16; msk >= 1; msk >>= 1) cost += shfl_xor_d(cost, msk);
+  if (lane == 0) red_s[warp] = cost;
+  // fold lane sub-groups and the two interleaved accumulators
+#pragma unroll
+  for (int m = 0; m < NT; ++m) {
+#pragma unroll
+    for (int e = 0; e < FPL; ++e) {
+      double v = acc_a[m][e] + acc_b[m][e];
+#pragma unroll
+      for (int msk = LPR; msk < 32; msk <<= 1) v += shfl_xor_d(v, msk);
+      acc_a[m][e] = v;
+    }
+    if (has_w) {
+      double c = cnt[m];
+#pragma unroll
+      for (int msk = 16; msk >= 1; msk >>= 1) c += shfl_xor_d(c, msk);
+      cnt[m] = c;
+    }
+  }
+  double* out = p.cta_partials + (size_t)blockIdx.x * P;
+#pragma unroll
+  for (int m = 0; m < NT; ++m) {
+    const int j = warp + 8 * m;
+    if (j < k) {
+      if (sub == 0) {
+#pragma unroll
+        for (int e = 0; e < FPL; ++e) { const int f = fl + 32 * e; if (f < d) out[(size_t)j * d + f] = acc_a[m][e]; }
+      }
+      if (lane == 0) out[(size_t)k * d + j] = cnt[m];
+    }
+  }
+  named_bar_sync(1, kComputeThreads);
+  if (tid == 0) {
+    double c = 0;
+#pragma unroll
+    for (int wv = 0; wv < kComputeWarps; ++wv) c += red_s[wv];
+    out[(size_t)k * d + k] = c;
+  }
+  // ===================================================================== last CTA folds all partials
+  __threadfence();
+  named_bar_sync(1, kComputeThreads);
+  __shared__ unsigned int s_ticket;
+  if (tid == 0) s_ticket = atomicAdd(p.counter, 1u);
+  named_bar_sync(1, kComputeThreads);
+  if (s_ticket == gridDim.x - 1) {
+    __threadfence();
+    for (int i = tid; i < P; i += kComputeThreads) {
+      double s = 0;
+      for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(p.cta_partials + (size_t)b * P + i);
+      p.partial_out[i] = s;
+    }
+    if (tid == 0) *p.counter = 0u;
+  }
+}
+
+}  // namespace hkm

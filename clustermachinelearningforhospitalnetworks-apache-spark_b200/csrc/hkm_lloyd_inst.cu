@@ -1,0 +1,66 @@
+// Instantiations of lloyd_pass_kernel for one NT = ceil(k/8) (compile with -DHKM_NT=<1..8>).
+#include "../../include/hkm.h"
+#include "hkm_lloyd_launch.cuh"
+
+#ifndef HKM_NT
+#error "compile with -DHKM_NT=<1..8>"
+#endif
+
+namespace hkm {
+
+template <int KS_T, int NT, int LPR, int FPL, int MINB>
+static int launch_lloyd(const LloydParams& p, const LaunchPlan& pl, int grid, cudaStream_t st) {
+  auto kern = lloyd_pass_kernel<KS_T, NT, LPR, FPL, MINB>;
+  static int attr_smem[64];  // per device: largest dynamic smem opted into so far
+  int dev = 0; HKM_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev >= 64 || attr_smem[dev] < pl.smem) {
+    HKM_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.smem));
+    if (dev < 64) attr_smem[dev] = pl.smem;
+  }
+  kern<<<grid, kThreads, pl.smem, st>>>(p);
+  HKM_CUDA_TRY(cudaGetLastError());
+  return HKM_OK;
+}
+
+// register-resident centre fragments: LPR/FPL follow from KS
+template <int KS_T, int NT>
+static int launch_regb(const LloydParams& p, const LaunchPlan& pl, int grid, cudaStream_t st) {
+  constexpr int LPR = KS_T <= 2 ? 8 : (KS_T <= 4 ? 16 : 32);
+  constexpr int FPL = KS_T <= 8 ? 1 : 2;
+  constexpr int MINB = (KS_T * NT <= 16 && NT <= 2) ? 2 : 1;
+  return launch_lloyd<KS_T, NT, LPR, FPL, MINB>(p, pl, grid, st);
+}
+template <int NT>
+static int launch_smemb(const LloydParams& p, const LaunchPlan& pl, int grid, cudaStream_t st) {
+  const int d = p.d;
+  constexpr int MINB = NT <= 2 ? 2 : 1;
+  if (d <= 8) return launch_lloyd<0, NT, 8, 1, MINB>(p, pl, grid, st);
+  if (d <= 16) return launch_lloyd<0, NT, 16, 1, MINB>(p, pl, grid, st);
+  if (d <= 32) return launch_lloyd<0, NT, 32, 1, MINB>(p, pl, grid, st);
+  if (d <= 64) return launch_lloyd<0, NT, 32, 2, MINB>(p, pl, grid, st);
+  if (d <= 96) return launch_lloyd<0, NT, 32, 3, 1>(p, pl, grid, st);
+  return launch_lloyd<0, NT, 32, 4, 1>(p, pl, grid, st);
+}
+
+#define HKM_CAT2(a, b) a##b
+#define HKM_CAT(a, b) HKM_CAT2(a, b)
+
+int HKM_CAT(dispatch_lloyd_nt, HKM_NT)(const LloydParams& p, const LaunchPlan& pl, int grid, cudaStream_t st) {
+  constexpr int NT = HKM_NT;
+  const int ks = p.ks;
+  // register-resident B fragments while KS*NT doubles per lane stay affordable
+#define HKM_REGB(KS) if constexpr (KS * NT <= 32) { if (ks == KS) return launch_regb<KS, NT>(p, pl, grid, st); }
+#ifndef HKM_DEV_FAST
+  HKM_REGB(1) HKM_REGB(2) HKM_REGB(3) HKM_REGB(4) HKM_REGB(5) HKM_REGB(6) HKM_REGB(7)
+#endif
+  HKM_REGB(8)
+#ifndef HKM_DEV_FAST
+  HKM_REGB(10) HKM_REGB(12) HKM_REGB(16)
+#else
+  HKM_REGB(4) HKM_REGB(6)
+#endif
+#undef HKM_REGB
+  return launch_smemb<NT>(p, pl, grid, st);
+}
+
+}  // namespace hkm

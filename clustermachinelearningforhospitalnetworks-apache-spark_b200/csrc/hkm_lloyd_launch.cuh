@@ -1,0 +1,36 @@
+// Host-side launch plan and per-NT dispatch of lloyd_pass_kernel.  The kernel template is
+// instantiated in hkm_lloyd_inst.cu, compiled once per NT (-DHKM_NT=1..8) so the build
+// parallelises across translation units.
+#pragma once
+#include "hkm_lloyd.cuh"
+
+namespace hkm {
+
+struct LaunchPlan { int stages; int ctas_per_sm; int smem; };
+
+inline LaunchPlan plan_lloyd(int d, int k_pad) {
+  // two CTAs per SM when at least 3 stages fit in ~112 KB each, else one CTA with a deep ring
+  LaunchPlan pl{};
+  const int budget2 = 112 * 1024, budget1 = 224 * 1024;
+  const int fixed = smem_layout(d, k_pad, 0).total;
+  int st2 = (budget2 - fixed) / stage_bytes(d);
+  if (st2 >= 3) { pl.stages = st2 > 4 ? 4 : st2; pl.ctas_per_sm = 2; }
+  else {
+    int st1 = (budget1 - fixed) / stage_bytes(d);
+    pl.stages = st1 > kMaxStages ? kMaxStages : st1; pl.ctas_per_sm = 1;
+  }
+  pl.smem = smem_layout(d, k_pad, pl.stages).total;
+  return pl;
+}
+
+// one function per NT, defined in hkm_lloyd_inst.cu
+int dispatch_lloyd_nt1(const LloydParams&, const LaunchPlan&, int grid, cudaStream_t);
+int dispatch_lloyd_nt2(const LloydParams&, const LaunchPlan&, int grid, cudaStream_t);
+int dispatch_lloyd_nt3(const LloydParams&, const LaunchPlan&, int grid, cudaStream_t);
+int dispatch_lloyd_nt4(const LloydParams&, const LaunchPlan&, int grid, cudaStream_t);
+int dispatch_lloyd_nt5(const LloydParams&, const LaunchPlan&, int grid, cudaStream_t);
+int dispatch_lloyd_nt6(const LloydParams&, const LaunchPlan&, int grid, cudaStream_t);
+int dispatch_lloyd_nt7(const LloydParams&, const LaunchPlan&, int grid, cudaStream_t);
+int dispatch_lloyd_nt8(const LloydParams&, const LaunchPlan&, int grid, cudaStream_t);
+
+}  // namespace hkm

@@ -1,0 +1,92 @@
+/*
+ * hkm.h -- C ABI of the B200-native KMeans hot path (libhkm.so).
+ *
+ * Drop-in boundary: the reference (/root/reference/mllearnforhospitalnetwork.py) has no FFI of
+ * its own; it drives pyspark.ml Estimators/Transformers/Evaluators (idiom: ref:L135-136
+ * VectorAssembler.transform, ref:L146-148 Estimator.fit / Model.transform, ref:L162-163
+ * Evaluator.evaluate), which in Spark cross Py4J into the JVM.  These entry points are what a
+ * Py4J/JNI replacement of that seam binds for the KMeans path; each comment names the upstream
+ * Spark routine whose per-row work it replaces.
+ *
+ * Conventions
+ *  - All pointers are DEVICE pointers unless the name ends in _host.  X is row-major fp64
+ *    [n, d], 16-byte aligned.  Labels are int32.  Sizes are int64/int.
+ *  - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *  - The library allocates nothing: callers pass `scratch` buffers sized by the matching
+ *    *_scratch_bytes() query and zero-filled once before first use (the kernels leave them
+ *    zeroed where that matters).
+ *  - No entry point synchronises the host.  Return value 0 = ok, < 0 = error; the text of the
+ *    last error on the calling thread is hkm_last_error().
+ *  - Calls are asynchronous on `stream`; two calls sharing one scratch buffer must be ordered
+ *    on the same stream.
+ */
+#ifndef HKM_H_
+#define HKM_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define HKM_API __attribute__((visibility("default")))
+#else
+#define HKM_API
+#endif
+
+#define HKM_OK 0
+#define HKM_ERR_INVALID (-1)     /* bad argument (null pointer, size, alignment) */
+#define HKM_ERR_UNSUPPORTED (-2) /* shape outside what the built kernels cover */
+#define HKM_ERR_CUDA (-3)        /* a CUDA runtime call failed */
+
+/* Device-side iteration state shared by the Lloyd entry points (32 bytes). */
+typedef struct hkm_lloyd_state {
+  double cost;        /* cost accumulated by the last executed iteration (KMeans.runAlgorithmWithWeight `cost`) */
+  int32_t iter;       /* iterations executed so far */
+  int32_t converged;  /* 1 once every updated centre moved by <= tol^2 */
+  double max_shift2;  /* largest squared centre movement of the last executed iteration */
+  int64_t reserved;
+} hkm_lloyd_state;
+
+HKM_API const char* hkm_last_error(void);
+HKM_API int hkm_version(void);
+
+/* Largest k and d the fp64 DMMA kernels accept. */
+HKM_API int hkm_max_k(void);
+HKM_API int hkm_max_d(void);
+
+/* Bytes of scratch hkm_assign_reduce needs for (d, k) on the current device. */
+HKM_API size_t hkm_assign_reduce_scratch_bytes(int d, int k);
+
+/*
+ * One data pass of Lloyd's algorithm over this rank's rows.
+ * Replaces the mapPartitions body + reduceByKey of mllib KMeans.runAlgorithmWithWeight
+ * (findClosest / updateClusterSum / costAccum).
+ *   partial_out [k*d + k + 1]: per-cluster sums (row-major k x d), weight sums, then cost.
+ *   labels_out  [n] or NULL: argmin index per row (KMeansModel.transform / predict, 8a-9).
+ *   mind2_out   [n] or NULL: squared distance to the closest centre (pointCost, 8a-6).
+ *   weights     [n] or NULL: per-row weights (weightCol); NULL = 1.0.
+ *   state       NULL, or a device hkm_lloyd_state: when state->converged != 0 the pass is a
+ *               no-op (lets a host enqueue maxIter passes without reading back in between).
+ *   do_reduce   0 = only labels/mind2 are produced (partial_out may be NULL).
+ */
+HKM_API int hkm_assign_reduce(const double* X, int64_t n, int d, const double* C, int k, const double* weights,
+                      double* partial_out, int32_t* labels_out, double* mind2_out,
+                      const hkm_lloyd_state* state, int do_reduce,
+                      void* scratch, size_t scratch_bytes, void* stream);
+
+/*
+ * Driver side of the iteration (KMeans.runAlgorithmWithWeight after collectAsMap, 8a-5):
+ * new_j = sums_j * (1/w_j) for clusters with w_j > 0 (others keep their centre), converged iff
+ * every updated centre moved by sqdist <= tol^2; state->cost/iter/converged updated.
+ * `partial` is the (all-reduced) vector hkm_assign_reduce produced.  No-op once converged.
+ */
+HKM_API int hkm_update_centers(const double* partial, int k, int d, double* C_inout, double tol,
+                       hkm_lloyd_state* state, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HKM_H_ */
