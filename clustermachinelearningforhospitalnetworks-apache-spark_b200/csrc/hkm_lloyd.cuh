@@ -54,8 +54,9 @@ __host__ __device__ inline int cs_ld(int d) { return ((d + 3) & ~3) + 4; }  // p
 
 // dynamic smem carve-up (bytes), all 16-byte aligned
 struct SmemLayout {
-  int x_off, labels_off, mind2_off, cs_off, cn_off, red_off, bar_off, total;
+  int x_off, labels_off, mind2_off, cs_off, cn_off, red_off, bar_off, list_off, zero_off, w_off, total;
 };
+__host__ __device__ inline int list_entries(int k_pad) { return kTileRows + 4 * (k_pad / 8) + 4; }  // per warp
 __host__ __device__ inline SmemLayout smem_layout(int d, int k_pad, int stages) {
   SmemLayout L;
   int o = 0;
@@ -66,6 +67,9 @@ __host__ __device__ inline SmemLayout smem_layout(int d, int k_pad, int stages) 
   L.cn_off = o; o += k_pad * 8;
   L.red_off = o; o += kComputeWarps * 8 + 16;
   L.bar_off = o; o += 2 * kMaxStages * 8;
+  L.list_off = o; o += kComputeWarps * list_entries(k_pad) * 4; o = (o + 15) & ~15;
+  L.zero_off = o; o += ((d + 3) & ~3) * 8;
+  L.w_off = o; o += 2 * kTileRows * 8;
   L.total = o;
   return L;
 }
@@ -90,6 +94,7 @@ __global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydP
   double* red_s = reinterpret_cast<double*>(smem + L.red_off);
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + L.bar_off);
   uint64_t* empty = full + kMaxStages;
+  double* w_s = reinterpret_cast<double*>(smem + L.w_off);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int stages = p.stages;
@@ -109,6 +114,7 @@ __global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydP
     int j = i / csld, f = i - j * csld;
     Cs[i] = (j < k && f < d) ? p.C[(size_t)j * d + f] : 0.0;
   }
+  for (int i = tid; i < ((d + 3) & ~3); i += kThreads) reinterpret_cast<double*>(smem + L.zero_off)[i] = 0.0;
   __syncthreads();
   for (int j = tid; j < k_pad; j += kThreads) {
     double s = 0;
@@ -152,10 +158,11 @@ __global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydP
 
   // phase-2 register accumulators: cluster warp + 8*m, features (lane % LPR) + 32*e
   double acc_a[NT][FPL], acc_b[NT][FPL];
-  double cnt[NT];
+  double wacc[NT];        // weighted runs: per-lane partial weight sums
+  unsigned cnt[NT];       // unweighted runs: rows per owned cluster (warp-uniform)
 #pragma unroll
   for (int m = 0; m < NT; ++m) {
-    cnt[m] = 0;
+    cnt[m] = 0; wacc[m] = 0;
 #pragma unroll
     for (int e = 0; e < FPL; ++e) { acc_a[m][e] = 0; acc_b[m][e] = 0; }
   }
@@ -163,6 +170,13 @@ __global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydP
   const int sub = lane / LPR, fl = lane % LPR;
   constexpr int RPS = 32 / LPR;  // rows handled per warp load step
   const bool has_w = p.w != nullptr;
+  uint32_t* list_w = reinterpret_cast<uint32_t*>(smem + L.list_off) + warp * list_entries(k_pad);
+  const unsigned lt_mask = (1u << lane) - 1u;
+  const int row_bytes = d * 8;
+  // byte offset (from the stage base) of tile row `lane`; row lane+32g adds g*group_stride
+  const uint32_t off_lane = (uint32_t)(lane * row_bytes + (lane >> 4) * kChunkPad);
+  const uint32_t group_stride = (uint32_t)(32 * row_bytes + 2 * kChunkPad);
+  const unsigned char* smem_lane = smem + fl * 8;
 
   auto process_tile = [&](const unsigned char* xs, int rows_valid, int64_t row0, int buf) {
     // ---------------- phase 1: two MMA sub-tiles per warp (rows i0 / i1 of every chunk)
@@ -219,8 +233,11 @@ __global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydP
       const int t0 = r * kChunkRows + i0, t1 = r * kChunkRows + i1;
       const bool v0 = t0 < rows_valid, v1 = t1 < rows_valid;
       double d0 = fmax(fma(-2.0, b0, xx0), 0.0), d1 = fmax(fma(-2.0, b1, xx1), 0.0);
-      if (has_w) { if (v0) cost = fma(d0, p.w[row0 + t0], cost); if (v1) cost = fma(d1, p.w[row0 + t1], cost); }
-      else { if (v0) cost += d0; if (v1) cost += d1; }
+      if (has_w) {
+        const double w0 = v0 ? p.w[row0 + t0] : 0.0, w1 = v1 ? p.w[row0 + t1] : 0.0;
+        cost = fma(d0, w0, cost); cost = fma(d1, w1, cost);
+        w_s[buf * kTileRows + t0] = w0; w_s[buf * kTileRows + t1] = w1;
+      } else { if (v0) cost += d0; if (v1) cost += d1; }
       labels_s[buf * kTileRows + t0] = v0 ? j0 : -1;
       labels_s[buf * kTileRows + t1] = v1 ? j1 : -1;
       if (p.mind2_out != nullptr) { mind2_s[buf * kTileRows + t0] = d0; mind2_s[buf * kTileRows + t1] = d1; }
@@ -233,42 +250,84 @@ __global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydP
       p.mind2_out[row0 + tid - kTileRows] = mind2_s[buf * kTileRows + tid - kTileRows];
 
     // ---------------- phase 2: owner warps gather their clusters' rows
+    // Each owner warp compacts the smem byte offsets of its clusters' rows into a private
+    // list (ballot + prefix popcount, one predicated store per group), pads every segment to
+    // a multiple of 4 with the offset of an all-zero row, then streams the list: one
+    // broadcast LDS.128 of four offsets, four row loads, four adds -- no per-row bit
+    // twiddling, no predication, fixed order.
     if (p.do_reduce) {
-#pragma unroll 1
-      for (int g = 0; g < kTileRows / 32; ++g) {
-        const int lab = labels_s[buf * kTileRows + g * 32 + lane];
+      const uint32_t stage_off = (uint32_t)(xs - smem);
+      int lab[kTileRows / 32];
 #pragma unroll
-        for (int m = 0; m < NT; ++m) {
-          const int j = warp + 8 * m;
-          unsigned mask = __ballot_sync(0xffffffffu, lab == j);
-          if (!has_w) cnt[m] += (double)__popc(mask);
-          while (mask) {
-            // next 4 member rows (tile-relative), -1 when exhausted
-            int rr[4];
+      for (int g = 0; g < kTileRows / 32; ++g) lab[g] = labels_s[buf * kTileRows + g * 32 + lane];
+      unsigned seg_begin[NT], seg_cnt[NT];
+      unsigned pos = 0;
 #pragma unroll
-            for (int u = 0; u < 4; ++u) { rr[u] = mask ? (__ffs(mask) - 1) : -1; mask &= mask - 1; }
-            // lane group `sub` takes rows sub, sub+RPS, ... of these four
+      for (int m = 0; m < NT; ++m) {
+        const int j = warp + 8 * m;
+        seg_begin[m] = pos;
+#pragma unroll
+        for (int g = 0; g < kTileRows / 32; ++g) {
+          const bool mine = lab[g] == j;
+          const unsigned mask = __ballot_sync(0xffffffffu, mine);
+          if (mine) {
+            uint32_t e = stage_off + off_lane + g * group_stride;
+            if (has_w) { e |= (uint32_t)(g * 32 + lane) << 20; }
+            list_w[pos + __popc(mask & lt_mask)] = e;
+          }
+          pos += __popc(mask);
+        }
+        seg_cnt[m] = pos - seg_begin[m];
+        if (lane < (int)((4u - (pos & 3u)) & 3u)) list_w[pos + lane] = (uint32_t)L.zero_off;  // padding -> zero row
+        pos = (pos + 3) & ~3u;
+      }
+      __syncwarp();
+#pragma unroll
+      for (int m = 0; m < NT; ++m) {
+        cnt[m] += seg_cnt[m];
+        const uint32_t* lp = list_w + seg_begin[m];
+        const unsigned nquad = (seg_cnt[m] + 3) >> 2;
+        if (!has_w) {
+#pragma unroll 2
+          for (unsigned i = 0; i < nquad; ++i) {
+            const uint4 o = *reinterpret_cast<const uint4*>(lp + 4 * i);
+            const uint32_t oo[4] = {o.x, o.y, o.z, o.w};
 #pragma unroll
             for (int u = 0; u < 4 / RPS; ++u) {
-              int rsel = rr[u * RPS];
+              uint32_t osel = oo[u * RPS];
 #pragma unroll
-              for (int z = 1; z < RPS; ++z) rsel = (sub == z) ? rr[u * RPS + z] : rsel;
-              const bool okr = rsel >= 0;
-              const int t = g * 32 + (okr ? rsel : 0);
-              const double* xr = reinterpret_cast<const double*>(xs + (t >> 4) * cstride) + (t & 15) * d;
-              double wv = 1.0;
-              if (has_w) { wv = okr ? p.w[row0 + t] : 0.0; if (fl == 0 && okr) cnt[m] += wv; }
+              for (int z = 1; z < RPS; ++z) osel = (sub == z) ? oo[u * RPS + z] : osel;
+              const double* xr = reinterpret_cast<const double*>(smem_lane + osel);
 #pragma unroll
               for (int e = 0; e < FPL; ++e) {
-                const int f = fl + 32 * e;
-                double v = (okr && f < d) ? xr[f] : 0.0;
-                if (has_w) v *= wv;
+                const double v = xr[32 * e];  // lanes past d read neighbouring smem into accumulators that are never stored
                 if (u & 1) acc_b[m][e] += v; else acc_a[m][e] += v;
+              }
+            }
+          }
+        } else {
+          for (unsigned i = 0; i < nquad; ++i) {
+            const uint4 o = *reinterpret_cast<const uint4*>(lp + 4 * i);
+            const uint32_t oo[4] = {o.x, o.y, o.z, o.w};
+#pragma unroll
+            for (int u = 0; u < 4 / RPS; ++u) {
+              uint32_t osel = oo[u * RPS];
+#pragma unroll
+              for (int z = 1; z < RPS; ++z) osel = (sub == z) ? oo[u * RPS + z] : osel;
+              const double* xr = reinterpret_cast<const double*>(smem_lane + (osel & 0xFFFFFu));
+              const bool pad = (osel & 0xFFFFFu) == (uint32_t)L.zero_off;
+              const double wv = pad ? 0.0 : w_s[buf * kTileRows + (osel >> 20)];
+              if (fl == 0) wacc[m] += wv;
+#pragma unroll
+              for (int e = 0; e < FPL; ++e) {
+                const double v = (fl + 32 * e) < d ? xr[32 * e] : 0.0;  // keep 0*garbage out of the fma
+                if (u & 1) acc_b[m][e] = fma(v, wv, acc_b[m][e]); else acc_a[m][e] = fma(v, wv, acc_a[m][e]);
               }
             }
           }
         }
       }
+      __syncwarp();
     }
   };
 
@@ -316,11 +375,11 @@ __global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydP
       acc_a[m][e] = v;
     }
     if (has_w) {
-      double c = cnt[m];
+      double c = wacc[m];
 #pragma unroll
       for (int msk = 16; msk >= 1; msk >>= 1) c += shfl_xor_d(c, msk);
-      cnt[m] = c;
-    }
+      wacc[m] = c;
+    } else wacc[m] = (double)cnt[m];
   }
   double* out = p.cta_partials + (size_t)blockIdx.x * P;
 #pragma unroll
@@ -331,7 +390,7 @@ __global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydP
 #pragma unroll
         for (int e = 0; e < FPL; ++e) { const int f = fl + 32 * e; if (f < d) out[(size_t)j * d + f] = acc_a[m][e]; }
       }
-      if (lane == 0) out[(size_t)k * d + j] = cnt[m];
+      if (lane == 0) out[(size_t)k * d + j] = wacc[m];
     }
   }
   named_bar_sync(1, kComputeThreads);
