@@ -45,7 +45,7 @@ def load() -> ctypes.CDLL:
         L.hkm_last_error.restype = ctypes.c_char_p
         L.hkm_assign_reduce_scratch_bytes.restype = sz
         L.hkm_assign_reduce_scratch_bytes.argtypes = [i32, i32]
-        L.hkm_assign_reduce.argtypes = [vp, i64, i32, vp, i32, vp, vp, vp, vp, vp, i32, vp, sz, vp]
+        L.hkm_assign_reduce.argtypes = [vp, i64, i32, vp, i32, vp, vp, vp, vp, vp, i32, vp, i32, vp, sz, vp]
         L.hkm_update_centers.argtypes = [vp, i32, i32, vp, ctypes.c_double, vp, vp]
         _lib = L
     return _lib
@@ -92,7 +92,8 @@ def read_state(state: torch.Tensor) -> LloydState:
     return LloydState.from_buffer_copy(raw)
 
 
-def assign_reduce(X, C, partial=None, labels=None, mind2=None, weights=None, state=None, scratch=None, do_reduce=True):
+def assign_reduce(X, C, partial=None, labels=None, mind2=None, weights=None, state=None, scratch=None, do_reduce=True,
+                  xnorm2_sum=None, xnorm2_mode=0):
     """One Lloyd data pass on the current stream (hkm_assign_reduce)."""
     require_cuda(X, "X", torch.float64)
     require_cuda(C, "C", torch.float64)
@@ -100,7 +101,7 @@ def assign_reduce(X, C, partial=None, labels=None, mind2=None, weights=None, sta
     k = C.shape[0]
     with torch.cuda.device(X.device):
         rc = load().hkm_assign_reduce(_ptr(X), n, d, _ptr(C), k, _ptr(weights), _ptr(partial), _ptr(labels), _ptr(mind2),
-                                      _ptr(state), int(do_reduce), _ptr(scratch),
+                                      _ptr(xnorm2_sum), int(xnorm2_mode), _ptr(state), int(do_reduce), _ptr(scratch),
                                       scratch.numel() * scratch.element_size() if scratch is not None else 0, _stream())
     _check(rc)
 

@@ -91,23 +91,25 @@ size_t hkm_assign_reduce_scratch_bytes(int d, int k) {
   const int k_pad = ((k + 7) / 8) * 8;
   LaunchPlan pl = plan_lloyd(d, k_pad);
   size_t grid = (size_t)sm_count() * pl.ctas_per_sm;
-  return 256 + grid * ((size_t)k * d + k + 1) * sizeof(double);
+  return 256 + grid * ((size_t)k * d + k + 2) * sizeof(double);
 }
 
 int hkm_assign_reduce(const double* X, int64_t n, int d, const double* C, int k, const double* weights, double* partial_out,
-                      int32_t* labels_out, double* mind2_out, const hkm_lloyd_state* state, int do_reduce, void* scratch,
-                      size_t scratch_bytes, void* stream) {
+                      int32_t* labels_out, double* mind2_out, double* xnorm2_sum, int xnorm2_mode, const hkm_lloyd_state* state,
+                      int do_reduce, void* scratch, size_t scratch_bytes, void* stream) {
   if (n < 0 || d < 1 || k < 1 || (n > 0 && X == nullptr) || C == nullptr) { set_error("hkm_assign_reduce: bad X/C/n/d/k"); return HKM_ERR_INVALID; }
   if (d > hkm_max_d() || k > hkm_max_k()) { set_error("hkm_assign_reduce: d=%d k=%d outside fp64 kernel range (d<=%d, k<=%d)", d, k, hkm_max_d(), hkm_max_k()); return HKM_ERR_UNSUPPORTED; }
   if ((reinterpret_cast<uintptr_t>(X) & 15) != 0) { set_error("hkm_assign_reduce: X must be 16-byte aligned"); return HKM_ERR_INVALID; }
   if (do_reduce && (partial_out == nullptr || scratch == nullptr)) { set_error("hkm_assign_reduce: reduce needs partial_out and scratch"); return HKM_ERR_INVALID; }
   if (do_reduce && scratch_bytes < hkm_assign_reduce_scratch_bytes(d, k)) { set_error("hkm_assign_reduce: scratch too small (%zu < %zu)", scratch_bytes, hkm_assign_reduce_scratch_bytes(d, k)); return HKM_ERR_INVALID; }
+  if (xnorm2_mode < 0 || xnorm2_mode > 2 || (xnorm2_mode != 0 && xnorm2_sum == nullptr)) { set_error("hkm_assign_reduce: bad xnorm2_mode/xnorm2_sum"); return HKM_ERR_INVALID; }
+  if (xnorm2_mode == 2 && mind2_out != nullptr) { set_error("hkm_assign_reduce: mind2_out needs per-row norms (xnorm2_mode 0 or 1)"); return HKM_ERR_INVALID; }
   const int k_pad = ((k + 7) / 8) * 8;
   LaunchPlan pl = plan_lloyd(d, k_pad);
   if (pl.stages < 2) { set_error("hkm_assign_reduce: d=%d does not fit the shared-memory ring", d); return HKM_ERR_UNSUPPORTED; }
   LloydParams p{};
   p.X = X; p.n = n; p.d = d; p.k = k; p.C = C; p.w = weights; p.partial_out = partial_out; p.labels_out = labels_out;
-  p.mind2_out = mind2_out; p.skip = state ? &state->converged : nullptr; p.do_reduce = do_reduce;
+  p.mind2_out = mind2_out; p.skip = state ? &state->converged : nullptr; p.do_reduce = do_reduce; p.xnorm2_sum = xnorm2_sum; p.xx_mode = do_reduce ? xnorm2_mode : 0;
   p.counter = reinterpret_cast<unsigned int*>(scratch);
   p.cta_partials = scratch ? reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(scratch) + 256) : nullptr;
   p.stages = pl.stages; p.ks = (d + 3) / 4;

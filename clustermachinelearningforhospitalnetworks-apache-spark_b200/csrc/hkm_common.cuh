@@ -52,7 +52,7 @@ __device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
 // fp64 tensor MMA, D(8x8) += A(8x4, row) * B(4x8, col).  Lane l: a = A[l>>2][l&3],
 // b = B[l&3][l>>2], c0/c1 = C[l>>2][2*(l&3) + {0,1}].   SASS: DMMA.8x8x4
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
-  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 __device__ __forceinline__ double shfl_xor_d(double v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
 

@@ -18,12 +18,13 @@
 // results are bit-stable run to run.
 #pragma once
 #include "hkm_common.cuh"
+#include <type_traits>
 
 namespace hkm {
 
 constexpr int kComputeWarps = 8;
 constexpr int kComputeThreads = kComputeWarps * 32;
-constexpr int kThreads = kComputeThreads + 32;  // + producer warp
+constexpr int kThreads = kComputeThreads;  // warp 0 lane 0 doubles as the TMA producer
 constexpr int kTileRows = 128;
 constexpr int kChunks = 8;
 constexpr int kChunkRows = kTileRows / kChunks;  // 16
@@ -42,7 +43,9 @@ struct LloydParams {
   double* mind2_out;       // nullable
   const int32_t* skip;     // nullable: device flag, nonzero => no-op
   int do_reduce;
-  double* cta_partials;    // scratch: [gridDim.x][k*d + k + 1]
+  double* xnorm2_sum;      // see xx_mode
+  int xx_mode;             // 0: per-row |x|^2 in-pass; 1: same, and store sum_w|x|^2; 2: reuse stored sum, skip per-row norms
+  double* cta_partials;    // scratch: [gridDim.x][k*d + k + 2]
   unsigned int* counter;   // scratch: zero before launch; left zero
   int stages;
   int ks;                  // ceil(d/4)
@@ -65,8 +68,8 @@ __host__ __device__ inline SmemLayout smem_layout(int d, int k_pad, int stages) 
   L.mind2_off = o; o += 2 * kTileRows * 8;
   L.cs_off = o; o += k_pad * cs_ld(d) * 8;
   L.cn_off = o; o += k_pad * 8;
-  L.red_off = o; o += kComputeWarps * 8 + 16;
-  L.bar_off = o; o += 2 * kMaxStages * 8;
+  L.red_off = o; o += 2 * kComputeWarps * 8 + 16;
+  L.bar_off = o; o += kMaxStages * 8;
   L.list_off = o; o += kComputeWarps * list_entries(k_pad) * 4; o = (o + 15) & ~15;
   L.zero_off = o; o += ((d + 3) & ~3) * 8;
   L.w_off = o; o += 2 * kTileRows * 8;
@@ -78,8 +81,8 @@ __host__ __device__ inline SmemLayout smem_layout(int d, int k_pad, int stages) 
 // KS_T == 0: B-fragments are re-read from shared memory, runtime k-step count.
 // NT = ceil(k/8) score column tiles == clusters owned per warp in phase 2.
 // LPR = lanes per row in phase 2 (8/16/32), FPL = features per lane (d > 32).
-template <int KS_T, int NT, int LPR, int FPL, int MINB>
-__global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydParams p) {
+template <int KS_T, int NT, int LPR, int FPL, int MAXREG>
+__global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kernel(const LloydParams p) {
   if (p.skip != nullptr && *p.skip != 0) return;
 
   extern __shared__ __align__(128) unsigned char smem[];
@@ -93,7 +96,6 @@ __global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydP
   double* cn_s = reinterpret_cast<double*>(smem + L.cn_off);
   double* red_s = reinterpret_cast<double*>(smem + L.red_off);
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + L.bar_off);
-  uint64_t* empty = full + kMaxStages;
   double* w_s = reinterpret_cast<double*>(smem + L.w_off);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -106,7 +108,7 @@ __global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydP
   const int tail_rows = (int)(p.n - full_tiles * kTileRows);
 
   if (tid == 0) {
-    for (int s = 0; s < stages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], kComputeWarps); }
+    for (int s = 0; s < stages; ++s) mbar_init(&full[s], 1);
     mbar_fence_init();
   }
   // stage centres: Cs[j][f] (zero padded), cn_s[j] = -0.5|c_j|^2 (-inf for padding)
@@ -123,22 +125,23 @@ __global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydP
   }
   __syncthreads();
 
-  // ===================================================================== producer warp
-  if (warp == kComputeWarps) {
-    if (lane == 0) {
-      int s = 0; uint32_t ph = 0;
-      const uint32_t cbytes = (uint32_t)(kChunkRows * d * 8);
-      for (int64_t t = blockIdx.x; t < full_tiles; t += gridDim.x) {
-        mbar_wait(&empty[s], ph ^ 1);
-        mbar_expect_tx(&full[s], cbytes * kChunks);
-        const unsigned char* src = reinterpret_cast<const unsigned char*>(p.X) + (size_t)t * kTileRows * d * 8;
-        unsigned char* dst = smem + L.x_off + (size_t)s * sbytes;
+  // ---- TMA producer (lane 0 of warp 0): fetch local tile `i` (global tile blockIdx.x + i*gridDim.x)
+  // into stage i % stages.  A stage is refilled right after the CTA barrier of the NEXT tile,
+  // which every warp reaches only after it has finished reading the stage -- so no "empty"
+  // mbarriers are needed.
+  const int64_t my_tiles = full_tiles > (int64_t)blockIdx.x ? (full_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+  auto issue_tile = [&](int64_t i) {
+    const int s = (int)(i % stages);
+    const uint32_t cbytes = (uint32_t)(kChunkRows * d * 8);
+    const int64_t t = (int64_t)blockIdx.x + i * gridDim.x;
+    mbar_expect_tx(&full[s], cbytes * kChunks);
+    const unsigned char* src = reinterpret_cast<const unsigned char*>(p.X) + (size_t)t * kTileRows * d * 8;
+    unsigned char* dst = smem + L.x_off + (size_t)s * sbytes;
 #pragma unroll
-        for (int c = 0; c < kChunks; ++c) bulk_g2s(dst + c * cstride, src + (size_t)c * cbytes, cbytes, &full[s]);
-        if (++s == stages) { s = 0; ph ^= 1; }
-      }
-    }
-    return;
+    for (int c = 0; c < kChunks; ++c) bulk_g2s(dst + c * cstride, src + (size_t)c * cbytes, cbytes, &full[s]);
+  };
+  if (tid == 0) {
+    for (int64_t i = 0; i < my_tiles && i < stages; ++i) issue_tile(i);
   }
 
   // ===================================================================== compute warps
@@ -178,7 +181,11 @@ __global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydP
   const uint32_t group_stride = (uint32_t)(32 * row_bytes + 2 * kChunkPad);
   const unsigned char* smem_lane = smem + fl * 8;
 
-  auto process_tile = [&](const unsigned char* xs, int rows_valid, int64_t row0, int buf) {
+  const int xx_mode = p.xx_mode;
+  double xxs = 0;  // mode 1: sum of w*|x|^2 over this thread's rows
+
+  auto process_tile = [&](auto need_xx_tag, const unsigned char* xs, int rows_valid, int64_t row0, int buf, int64_t refill) {
+    constexpr bool NEED_XX = decltype(need_xx_tag)::value;
     // ---------------- phase 1: two MMA sub-tiles per warp (rows i0 / i1 of every chunk)
     const int i0 = warp, i1 = warp + 8;
     const double* xa = reinterpret_cast<const double*>(xs + r * cstride) + q;
@@ -193,7 +200,7 @@ __global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydP
       for (int s = 0; s < (KS_T > 0 ? KS_T : 1); ++s) {
         const bool ok = (s < KS_T - 1) || (4 * s + q < d);
         double a0 = ok ? xa0[4 * s] : 0.0, a1 = ok ? xa1[4 * s] : 0.0;
-        xx0 = fma(a0, a0, xx0); xx1 = fma(a1, a1, xx1);
+        if (NEED_XX) { xx0 = fma(a0, a0, xx0); xx1 = fma(a1, a1, xx1); }
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) { dmma884(s0[nt][0], s0[nt][1], a0, breg[s * NT + nt]); dmma884(s1[nt][0], s1[nt][1], a1, breg[s * NT + nt]); }
       }
@@ -202,7 +209,7 @@ __global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydP
       for (int s = 0; s < KS; ++s) {
         const bool ok = 4 * s + q < d;
         double a0 = ok ? xa0[4 * s] : 0.0, a1 = ok ? xa1[4 * s] : 0.0;
-        xx0 = fma(a0, a0, xx0); xx1 = fma(a1, a1, xx1);
+        if (NEED_XX) { xx0 = fma(a0, a0, xx0); xx1 = fma(a1, a1, xx1); }
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) {
           double b = cb[(8 * nt) * csld + 4 * s];
@@ -227,22 +234,34 @@ __global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydP
       int oj0 = __shfl_xor_sync(0xffffffffu, j0, msk), oj1 = __shfl_xor_sync(0xffffffffu, j1, msk);
       if (o0 > b0 || (o0 == b0 && oj0 < j0)) { b0 = o0; j0 = oj0; }
       if (o1 > b1 || (o1 == b1 && oj1 < j1)) { b1 = o1; j1 = oj1; }
-      xx0 += shfl_xor_d(xx0, msk); xx1 += shfl_xor_d(xx1, msk);
+      if (NEED_XX) { xx0 += shfl_xor_d(xx0, msk); xx1 += shfl_xor_d(xx1, msk); }
     }
     if (q == 0) {
       const int t0 = r * kChunkRows + i0, t1 = r * kChunkRows + i1;
       const bool v0 = t0 < rows_valid, v1 = t1 < rows_valid;
-      double d0 = fmax(fma(-2.0, b0, xx0), 0.0), d1 = fmax(fma(-2.0, b1, xx1), 0.0);
+      // per-row term of the cost: the clamped distance, or (mode 2) the score itself, folded
+      // against the stored sum of |x|^2 by the last CTA
+      double d0 = b0, d1 = b1;
+      if (NEED_XX) {
+        d0 = fmax(fma(-2.0, b0, xx0), 0.0); d1 = fmax(fma(-2.0, b1, xx1), 0.0);
+      }
+      const double c0 = (NEED_XX && xx_mode == 2) ? b0 : d0, c1 = (NEED_XX && xx_mode == 2) ? b1 : d1;
       if (has_w) {
         const double w0 = v0 ? p.w[row0 + t0] : 0.0, w1 = v1 ? p.w[row0 + t1] : 0.0;
-        cost = fma(d0, w0, cost); cost = fma(d1, w1, cost);
+        cost = fma(c0, w0, cost); cost = fma(c1, w1, cost);
+        if (NEED_XX && xx_mode == 1) { xxs = fma(xx0, w0, xxs); xxs = fma(xx1, w1, xxs); }
         w_s[buf * kTileRows + t0] = w0; w_s[buf * kTileRows + t1] = w1;
-      } else { if (v0) cost += d0; if (v1) cost += d1; }
+      } else {
+        if (v0) cost += c0;
+        if (v1) cost += c1;
+        if (NEED_XX && xx_mode == 1) { if (v0) xxs += xx0; if (v1) xxs += xx1; }
+      }
       labels_s[buf * kTileRows + t0] = v0 ? j0 : -1;
       labels_s[buf * kTileRows + t1] = v1 ? j1 : -1;
       if (p.mind2_out != nullptr) { mind2_s[buf * kTileRows + t0] = d0; mind2_s[buf * kTileRows + t1] = d1; }
     }
-    named_bar_sync(1, kComputeThreads);
+    __syncthreads();
+    if (tid == 0 && refill >= 0) issue_tile(refill);  // the previous tile's stage is free now
 
     // ---------------- outputs (coalesced from smem)
     if (p.labels_out != nullptr && tid < kTileRows && tid < rows_valid) p.labels_out[row0 + tid] = labels_s[buf * kTileRows + tid];
@@ -334,17 +353,18 @@ __global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydP
   // main loop over this CTA's full tiles
   {
     int s = 0; uint32_t ph = 0; int buf = 0;
-    for (int64_t t = blockIdx.x; t < full_tiles; t += gridDim.x) {
+    for (int64_t i = 0; i < my_tiles; ++i) {
+      const int64_t t = (int64_t)blockIdx.x + i * gridDim.x;
+      const int64_t refill = (i >= 1 && i - 1 + stages < my_tiles) ? i - 1 + stages : -1;
       mbar_wait(&full[s], ph);
-      process_tile(smem + L.x_off + (size_t)s * sbytes, kTileRows, t * kTileRows, buf);
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&empty[s]);
+      if (xx_mode != 2) process_tile(std::true_type{}, smem + L.x_off + (size_t)s * sbytes, kTileRows, t * kTileRows, buf, refill);
+      else process_tile(std::false_type{}, smem + L.x_off + (size_t)s * sbytes, kTileRows, t * kTileRows, buf, refill);
       if (++s == stages) { s = 0; ph ^= 1; }
       buf ^= 1;
     }
     // ragged tail (< 128 rows): the CTA next in round-robin order loads it with plain loads
     if (tail_rows > 0 && (int)(full_tiles % gridDim.x) == (int)blockIdx.x) {
-      named_bar_sync(1, kComputeThreads);  // every warp is done with all stages
+      __syncthreads();  // every warp is done with all stages
       unsigned char* xs = smem + L.x_off;
       const double* src = p.X + (size_t)full_tiles * kTileRows * d;
       for (int i = tid; i < kTileRows * d; i += kComputeThreads) {
@@ -352,8 +372,8 @@ __global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydP
         double v = t < tail_rows ? src[(size_t)t * d + f] : 0.0;
         reinterpret_cast<double*>(xs + (t >> 4) * cstride)[(t & 15) * d + f] = v;
       }
-      named_bar_sync(1, kComputeThreads);
-      process_tile(xs, tail_rows, full_tiles * kTileRows, buf);
+      __syncthreads();
+      process_tile(std::true_type{}, xs, tail_rows, full_tiles * kTileRows, buf, -1);
     }
   }
   if (!p.do_reduce) return;
@@ -362,8 +382,8 @@ __global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydP
   const int P = k * d + k + 1;
   // cost: warp shuffle, then across warps through smem
 #pragma unroll
-  for (int msk = 16; msk >= 1; msk >>= 1) cost += shfl_xor_d(cost, msk);
-  if (lane == 0) red_s[warp] = cost;
+  for (int msk = 16; msk >= 1; msk >>= 1) { cost += shfl_xor_d(cost, msk); xxs += shfl_xor_d(xxs, msk); }
+  if (lane == 0) { red_s[warp] = cost; red_s[kComputeWarps + warp] = xxs; }
   // fold lane sub-groups and the two interleaved accumulators
 #pragma unroll
   for (int m = 0; m < NT; ++m) {
@@ -381,7 +401,7 @@ __global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydP
       wacc[m] = c;
     } else wacc[m] = (double)cnt[m];
   }
-  double* out = p.cta_partials + (size_t)blockIdx.x * P;
+  double* out = p.cta_partials + (size_t)blockIdx.x * (P + 1);
 #pragma unroll
   for (int m = 0; m < NT; ++m) {
     const int j = warp + 8 * m;
@@ -393,25 +413,27 @@ __global__ void __launch_bounds__(kThreads, MINB) lloyd_pass_kernel(const LloydP
       if (lane == 0) out[(size_t)k * d + j] = wacc[m];
     }
   }
-  named_bar_sync(1, kComputeThreads);
+  __syncthreads();
   if (tid == 0) {
-    double c = 0;
+    double c = 0, x2 = 0;
 #pragma unroll
-    for (int wv = 0; wv < kComputeWarps; ++wv) c += red_s[wv];
-    out[(size_t)k * d + k] = c;
+    for (int wv = 0; wv < kComputeWarps; ++wv) { c += red_s[wv]; x2 += red_s[kComputeWarps + wv]; }
+    out[P - 1] = c; out[P] = x2;
   }
   // ===================================================================== last CTA folds all partials
   __threadfence();
-  named_bar_sync(1, kComputeThreads);
+  __syncthreads();
   __shared__ unsigned int s_ticket;
   if (tid == 0) s_ticket = atomicAdd(p.counter, 1u);
-  named_bar_sync(1, kComputeThreads);
+  __syncthreads();
   if (s_ticket == gridDim.x - 1) {
     __threadfence();
-    for (int i = tid; i < P; i += kComputeThreads) {
+    for (int i = tid; i < P + 1; i += kComputeThreads) {
       double s = 0;
-      for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(p.cta_partials + (size_t)b * P + i);
-      p.partial_out[i] = s;
+      for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(p.cta_partials + (size_t)b * (P + 1) + i);
+      if (i == P - 1 && xx_mode == 2) s = fmax(fma(-2.0, s, *p.xnorm2_sum), 0.0);  // cost = sum w|x|^2 - 2 sum w*score
+      if (i < P) p.partial_out[i] = s;
+      else if (xx_mode == 1) *p.xnorm2_sum = s;
     }
     if (tid == 0) *p.counter = 0u;
   }

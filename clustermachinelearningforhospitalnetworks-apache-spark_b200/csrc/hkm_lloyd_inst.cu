@@ -8,9 +8,9 @@
 
 namespace hkm {
 
-template <int KS_T, int NT, int LPR, int FPL, int MINB>
+template <int KS_T, int NT, int LPR, int FPL, int MAXREG>
 static int launch_lloyd(const LloydParams& p, const LaunchPlan& pl, int grid, cudaStream_t st) {
-  auto kern = lloyd_pass_kernel<KS_T, NT, LPR, FPL, MINB>;
+  auto kern = lloyd_pass_kernel<KS_T, NT, LPR, FPL, MAXREG>;
   static int attr_smem[64];  // per device: largest dynamic smem opted into so far
   int dev = 0; HKM_CUDA_TRY(cudaGetDevice(&dev));
   if (dev >= 64 || attr_smem[dev] < pl.smem) {
@@ -27,19 +27,20 @@ template <int KS_T, int NT>
 static int launch_regb(const LloydParams& p, const LaunchPlan& pl, int grid, cudaStream_t st) {
   constexpr int LPR = KS_T <= 2 ? 8 : (KS_T <= 4 ? 16 : 32);
   constexpr int FPL = KS_T <= 8 ? 1 : 2;
-  constexpr int MINB = (KS_T * NT <= 16 && NT <= 2) ? 2 : 1;
-  return launch_lloyd<KS_T, NT, LPR, FPL, MINB>(p, pl, grid, st);
+  // 16 warps/SM = 4 per scheduler partition (16K registers each) -> 128 regs when two CTAs share an SM
+  constexpr int MAXREG = (KS_T * NT <= 16 && NT <= 2) ? 128 : 255;
+  return launch_lloyd<KS_T, NT, LPR, FPL, MAXREG>(p, pl, grid, st);
 }
 template <int NT>
 static int launch_smemb(const LloydParams& p, const LaunchPlan& pl, int grid, cudaStream_t st) {
   const int d = p.d;
-  constexpr int MINB = NT <= 2 ? 2 : 1;
+  constexpr int MINB = NT <= 2 ? 128 : 255;
   if (d <= 8) return launch_lloyd<0, NT, 8, 1, MINB>(p, pl, grid, st);
   if (d <= 16) return launch_lloyd<0, NT, 16, 1, MINB>(p, pl, grid, st);
   if (d <= 32) return launch_lloyd<0, NT, 32, 1, MINB>(p, pl, grid, st);
   if (d <= 64) return launch_lloyd<0, NT, 32, 2, MINB>(p, pl, grid, st);
-  if (d <= 96) return launch_lloyd<0, NT, 32, 3, 1>(p, pl, grid, st);
-  return launch_lloyd<0, NT, 32, 4, 1>(p, pl, grid, st);
+  if (d <= 96) return launch_lloyd<0, NT, 32, 3, 255>(p, pl, grid, st);
+  return launch_lloyd<0, NT, 32, 4, 255>(p, pl, grid, st);
 }
 
 #define HKM_CAT2(a, b) a##b

@@ -14,7 +14,7 @@ inline LaunchPlan plan_lloyd(int d, int k_pad) {
   const int budget2 = 112 * 1024, budget1 = 224 * 1024;
   const int fixed = smem_layout(d, k_pad, 0).total;
   int st2 = (budget2 - fixed) / stage_bytes(d);
-  if (st2 >= 3) { pl.stages = st2 > 4 ? 4 : st2; pl.ctas_per_sm = 2; }
+  if (st2 >= 3) { pl.stages = st2 > kMaxStages ? kMaxStages : st2; pl.ctas_per_sm = 2; }
   else {
     int st1 = (budget1 - fixed) / stage_bytes(d);
     pl.stages = st1 > kMaxStages ? kMaxStages : st1; pl.ctas_per_sm = 1;

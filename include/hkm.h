@@ -41,6 +41,10 @@ extern "C" {
 #define HKM_ERR_UNSUPPORTED (-2) /* shape outside what the built kernels cover */
 #define HKM_ERR_CUDA (-3)        /* a CUDA runtime call failed */
 
+#define HKM_XNORM_PER_ROW 0
+#define HKM_XNORM_STORE 1
+#define HKM_XNORM_REUSE 2
+
 /* Device-side iteration state shared by the Lloyd entry points (32 bytes). */
 typedef struct hkm_lloyd_state {
   double cost;        /* cost accumulated by the last executed iteration (KMeans.runAlgorithmWithWeight `cost`) */
@@ -68,12 +72,19 @@ HKM_API size_t hkm_assign_reduce_scratch_bytes(int d, int k);
  *   labels_out  [n] or NULL: argmin index per row (KMeansModel.transform / predict, 8a-9).
  *   mind2_out   [n] or NULL: squared distance to the closest centre (pointCost, 8a-6).
  *   weights     [n] or NULL: per-row weights (weightCol); NULL = 1.0.
+ *   xnorm2_mode HKM_XNORM_PER_ROW (0): |x|^2 is recomputed per row inside the pass (always
+ *               correct; required for mind2_out).  HKM_XNORM_STORE (1): same, and the pass
+ *               also stores sum_i w_i |x_i|^2 to *xnorm2_sum.  HKM_XNORM_REUSE (2): the pass
+ *               skips the per-row norms and forms cost = *xnorm2_sum - 2 sum_i w_i score_i
+ *               (X and weights must be those of the STORE pass).  The sum is exact to fp64
+ *               rounding of ~1e-16 * sum|x|^2, so REUSE is meant for cost / sum|x|^2 > 1e-9.
  *   state       NULL, or a device hkm_lloyd_state: when state->converged != 0 the pass is a
  *               no-op (lets a host enqueue maxIter passes without reading back in between).
  *   do_reduce   0 = only labels/mind2 are produced (partial_out may be NULL).
  */
 HKM_API int hkm_assign_reduce(const double* X, int64_t n, int d, const double* C, int k, const double* weights,
                       double* partial_out, int32_t* labels_out, double* mind2_out,
+                      double* xnorm2_sum, int xnorm2_mode,
                       const hkm_lloyd_state* state, int do_reduce,
                       void* scratch, size_t scratch_bytes, void* stream);
 

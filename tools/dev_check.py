@@ -18,6 +18,15 @@ def check(n, d, k, seed=0, weights=False):
     for rep in range(2):
         N.assign_reduce(X, C, partial, labels, mind2, weights=w, scratch=scratch)
     torch.cuda.synchronize()
+    # STORE then REUSE must reproduce the same partials (cost to rounding)
+    xs = torch.zeros(1, dtype=torch.float64, device="cuda"); p1 = torch.empty_like(partial); p2 = torch.empty_like(partial)
+    N.assign_reduce(X, C, p1, weights=w, scratch=scratch, xnorm2_sum=xs, xnorm2_mode=1)
+    N.assign_reduce(X, C, p2, weights=w, scratch=scratch, xnorm2_sum=xs, xnorm2_mode=2)
+    torch.cuda.synchronize()
+    assert torch.equal(p1, partial), "STORE pass differs from PER_ROW pass"
+    assert torch.equal(p1[:-1], p2[:-1]), "REUSE sums differ"
+    rel = abs(p2[-1].item() - p1[-1].item()) / max(p1[-1].item(), 1e-300)
+    assert rel < 1e-10, f"REUSE cost rel err {rel}"
     sums, wsum, cost, lab = O.lloyd_pass(Xh, Ch, w=wh, P=1, want_labels=True)
     _, dist = O.predict(Xh, Ch, want_dist=True)
     p = partial.cpu().numpy()
@@ -36,10 +45,11 @@ def bench(n, d, k, iters=20):
     C = X[:k].clone()
     partial = torch.empty(k * d + k + 1, dtype=torch.float64, device="cuda")
     scratch = N.new_scratch(d, k, "cuda")
-    for _ in range(3): N.assign_reduce(X, C, partial, scratch=scratch)
+    xs = torch.zeros(1, dtype=torch.float64, device="cuda")
+    for _ in range(3): N.assign_reduce(X, C, partial, scratch=scratch, xnorm2_sum=xs, xnorm2_mode=1)
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize(); e0.record()
-    for _ in range(iters): N.assign_reduce(X, C, partial, scratch=scratch)
+    for _ in range(iters): N.assign_reduce(X, C, partial, scratch=scratch, xnorm2_sum=xs, xnorm2_mode=2)
     e1.record(); torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / iters
     print(json.dumps(dict(n=n, d=d, k=k, ms=round(ms, 4), GBps=round(n * d * 8 / ms * 1e-6, 1), rows_per_s=round(n / ms * 1e3))), flush=True)
