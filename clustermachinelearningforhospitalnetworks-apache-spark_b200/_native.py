@@ -16,6 +16,7 @@ SO_PATH = os.path.join(_HERE, "csrc", "libhkm.so")
 EXPORTS = (
     "hkm_last_error", "hkm_version", "hkm_max_k", "hkm_max_d",
     "hkm_assign_reduce_scratch_bytes", "hkm_assign_reduce", "hkm_update_centers",
+    "hkm_kmpar_scratch_bytes", "hkm_kmpar_cost_update", "hkm_kmpar_sample", "hkm_kmpar_strip_rows", "hkm_closest_counts",
 )
 
 _lib = None
@@ -47,6 +48,11 @@ def load() -> ctypes.CDLL:
         L.hkm_assign_reduce_scratch_bytes.argtypes = [i32, i32]
         L.hkm_assign_reduce.argtypes = [vp, i64, i32, vp, i32, vp, vp, vp, vp, vp, i32, vp, i32, vp, sz, vp]
         L.hkm_update_centers.argtypes = [vp, i32, i32, vp, ctypes.c_double, vp, vp]
+        L.hkm_kmpar_scratch_bytes.restype = sz
+        L.hkm_kmpar_scratch_bytes.argtypes = [i32]
+        L.hkm_kmpar_cost_update.argtypes = [vp, i64, i32, vp, i32, vp, vp, vp, sz, vp]
+        L.hkm_kmpar_sample.argtypes = [vp, i64, vp, vp, i64, i32, i32, ctypes.c_int32, i32, i32, vp, vp, i32, vp, vp]
+        L.hkm_closest_counts.argtypes = [vp, i64, i32, vp, i32, vp, vp, vp, vp]
         _lib = L
     return _lib
 
@@ -110,4 +116,43 @@ def update_centers(partial, C, tol: float, state):
     k, d = C.shape
     with torch.cuda.device(C.device):
         rc = load().hkm_update_centers(_ptr(partial), k, d, _ptr(C), float(tol), _ptr(state), _stream())
+    _check(rc)
+
+
+def kmpar_new_scratch(d: int, device) -> torch.Tensor:
+    with torch.cuda.device(device):
+        nbytes = int(load().hkm_kmpar_scratch_bytes(d))
+    return torch.zeros((nbytes + 7) // 8, dtype=torch.int64, device=device)
+
+
+def kmpar_cost_update(X, newC, costs, sum_out, scratch):
+    """costs = min(costs, pointCost(newC, x)); sum_out[0] = costs.sum()  (hkm_kmpar_cost_update)."""
+    require_cuda(X, "X", torch.float64); require_cuda(newC, "newC", torch.float64); require_cuda(costs, "costs", torch.float64)
+    n, d = X.shape
+    with torch.cuda.device(X.device):
+        rc = load().hkm_kmpar_cost_update(_ptr(X), n, d, _ptr(newC), newC.shape[0], _ptr(costs), _ptr(sum_out), _ptr(scratch),
+                                          scratch.numel() * scratch.element_size(), _stream())
+    _check(rc)
+
+
+def kmpar_strip_rows() -> int:
+    return int(load().hkm_kmpar_strip_rows())
+
+
+def kmpar_sample(costs, part_rows, strip_start, total_strips, part_index0, seed32, step, k, sum_costs, idx_out, count_out):
+    require_cuda(costs, "costs", torch.float64)
+    P = part_rows.numel() - 1
+    with torch.cuda.device(costs.device):
+        rc = load().hkm_kmpar_sample(_ptr(costs), costs.numel(), _ptr(part_rows), _ptr(strip_start), int(total_strips), P,
+                                     int(part_index0), int(seed32), int(step), int(k), _ptr(sum_costs), _ptr(idx_out),
+                                     idx_out.numel(), _ptr(count_out), _stream())
+    _check(rc)
+
+
+def closest_counts(X, cand, labels_work, mind2_work, counts_out):
+    require_cuda(X, "X", torch.float64); require_cuda(cand, "cand", torch.float64)
+    n, d = X.shape
+    with torch.cuda.device(X.device):
+        rc = load().hkm_closest_counts(_ptr(X), n, d, _ptr(cand), cand.shape[0], _ptr(labels_work), _ptr(mind2_work),
+                                       _ptr(counts_out), _stream())
     _check(rc)

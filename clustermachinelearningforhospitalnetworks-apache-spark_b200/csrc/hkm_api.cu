@@ -77,6 +77,35 @@ __global__ void update_centers_kernel(const double* __restrict__ partial, int k,
 
 }  // namespace hkm
 
+namespace hkm {
+
+int assign_pass(const AssignArgs& a, const char* who) {
+  const int d = a.d, k = a.k;
+  if (a.n < 0 || d < 1 || k < 1 || (a.n > 0 && a.X == nullptr) || a.C == nullptr) { set_error("%s: bad X/C/n/d/k", who); return HKM_ERR_INVALID; }
+  if (d > hkm_max_d() || k > hkm_max_k()) { set_error("%s: d=%d k=%d outside fp64 kernel range (d<=%d, k<=%d)", who, d, k, hkm_max_d(), hkm_max_k()); return HKM_ERR_UNSUPPORTED; }
+  if ((reinterpret_cast<uintptr_t>(a.X) & 15) != 0) { set_error("%s: X must be 16-byte aligned", who); return HKM_ERR_INVALID; }
+  if (a.do_reduce && (a.partial_out == nullptr || a.scratch == nullptr)) { set_error("%s: reduce needs partial_out and scratch", who); return HKM_ERR_INVALID; }
+  if (a.do_reduce && a.scratch_bytes < hkm_assign_reduce_scratch_bytes(d, k)) { set_error("%s: scratch too small (%zu < %zu)", who, a.scratch_bytes, hkm_assign_reduce_scratch_bytes(d, k)); return HKM_ERR_INVALID; }
+  if (a.xnorm2_mode < 0 || a.xnorm2_mode > 2 || (a.xnorm2_mode != 0 && a.xnorm2_sum == nullptr)) { set_error("%s: bad xnorm2_mode/xnorm2_sum", who); return HKM_ERR_INVALID; }
+  if (a.xnorm2_mode == 2 && a.mind2_out != nullptr) { set_error("%s: mind2_out needs per-row norms (xnorm2_mode 0 or 1)", who); return HKM_ERR_INVALID; }
+  if (a.out_mode != 0 && a.mind2_out == nullptr) { set_error("%s: min-merge needs mind2", who); return HKM_ERR_INVALID; }
+  const int k_pad = ((k + 7) / 8) * 8;
+  LaunchPlan pl = plan_lloyd(d, k_pad);
+  if (pl.stages < 2) { set_error("%s: d=%d does not fit the shared-memory ring", who, d); return HKM_ERR_UNSUPPORTED; }
+  LloydParams p{};
+  p.X = a.X; p.n = a.n; p.d = d; p.k = k; p.C = a.C; p.w = a.weights; p.partial_out = a.partial_out; p.labels_out = a.labels_out;
+  p.mind2_out = a.mind2_out; p.skip = a.state ? &a.state->converged : nullptr; p.do_reduce = a.do_reduce;
+  p.out_mode = a.out_mode; p.label_base = a.label_base;
+  p.xnorm2_sum = a.xnorm2_sum; p.xx_mode = a.do_reduce == 1 ? a.xnorm2_mode : 0;
+  p.counter = reinterpret_cast<unsigned int*>(a.scratch);
+  p.cta_partials = a.scratch ? reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(a.scratch) + 256) : nullptr;
+  p.stages = pl.stages; p.ks = (d + 3) / 4;
+  const int grid = sm_count() * pl.ctas_per_sm;
+  return dispatch_lloyd(p, pl, grid, reinterpret_cast<cudaStream_t>(a.stream));
+}
+
+}  // namespace hkm
+
 using namespace hkm;
 
 extern "C" {
@@ -97,24 +126,11 @@ size_t hkm_assign_reduce_scratch_bytes(int d, int k) {
 int hkm_assign_reduce(const double* X, int64_t n, int d, const double* C, int k, const double* weights, double* partial_out,
                       int32_t* labels_out, double* mind2_out, double* xnorm2_sum, int xnorm2_mode, const hkm_lloyd_state* state,
                       int do_reduce, void* scratch, size_t scratch_bytes, void* stream) {
-  if (n < 0 || d < 1 || k < 1 || (n > 0 && X == nullptr) || C == nullptr) { set_error("hkm_assign_reduce: bad X/C/n/d/k"); return HKM_ERR_INVALID; }
-  if (d > hkm_max_d() || k > hkm_max_k()) { set_error("hkm_assign_reduce: d=%d k=%d outside fp64 kernel range (d<=%d, k<=%d)", d, k, hkm_max_d(), hkm_max_k()); return HKM_ERR_UNSUPPORTED; }
-  if ((reinterpret_cast<uintptr_t>(X) & 15) != 0) { set_error("hkm_assign_reduce: X must be 16-byte aligned"); return HKM_ERR_INVALID; }
-  if (do_reduce && (partial_out == nullptr || scratch == nullptr)) { set_error("hkm_assign_reduce: reduce needs partial_out and scratch"); return HKM_ERR_INVALID; }
-  if (do_reduce && scratch_bytes < hkm_assign_reduce_scratch_bytes(d, k)) { set_error("hkm_assign_reduce: scratch too small (%zu < %zu)", scratch_bytes, hkm_assign_reduce_scratch_bytes(d, k)); return HKM_ERR_INVALID; }
-  if (xnorm2_mode < 0 || xnorm2_mode > 2 || (xnorm2_mode != 0 && xnorm2_sum == nullptr)) { set_error("hkm_assign_reduce: bad xnorm2_mode/xnorm2_sum"); return HKM_ERR_INVALID; }
-  if (xnorm2_mode == 2 && mind2_out != nullptr) { set_error("hkm_assign_reduce: mind2_out needs per-row norms (xnorm2_mode 0 or 1)"); return HKM_ERR_INVALID; }
-  const int k_pad = ((k + 7) / 8) * 8;
-  LaunchPlan pl = plan_lloyd(d, k_pad);
-  if (pl.stages < 2) { set_error("hkm_assign_reduce: d=%d does not fit the shared-memory ring", d); return HKM_ERR_UNSUPPORTED; }
-  LloydParams p{};
-  p.X = X; p.n = n; p.d = d; p.k = k; p.C = C; p.w = weights; p.partial_out = partial_out; p.labels_out = labels_out;
-  p.mind2_out = mind2_out; p.skip = state ? &state->converged : nullptr; p.do_reduce = do_reduce; p.xnorm2_sum = xnorm2_sum; p.xx_mode = do_reduce ? xnorm2_mode : 0;
-  p.counter = reinterpret_cast<unsigned int*>(scratch);
-  p.cta_partials = scratch ? reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(scratch) + 256) : nullptr;
-  p.stages = pl.stages; p.ks = (d + 3) / 4;
-  const int grid = sm_count() * pl.ctas_per_sm;
-  return dispatch_lloyd(p, pl, grid, reinterpret_cast<cudaStream_t>(stream));
+  AssignArgs a{};
+  a.X = X; a.n = n; a.d = d; a.C = C; a.k = k; a.weights = weights; a.partial_out = partial_out; a.labels_out = labels_out;
+  a.mind2_out = mind2_out; a.xnorm2_sum = xnorm2_sum; a.xnorm2_mode = xnorm2_mode; a.state = state; a.do_reduce = do_reduce ? 1 : 0;
+  a.scratch = scratch; a.scratch_bytes = scratch_bytes; a.stream = stream;
+  return assign_pass(a, "hkm_assign_reduce");
 }
 
 int hkm_update_centers(const double* partial, int k, int d, double* C_inout, double tol, hkm_lloyd_state* state, void* stream) {

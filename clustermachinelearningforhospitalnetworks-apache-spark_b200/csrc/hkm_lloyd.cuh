@@ -42,7 +42,9 @@ struct LloydParams {
   int32_t* labels_out;     // nullable
   double* mind2_out;       // nullable
   const int32_t* skip;     // nullable: device flag, nonzero => no-op
-  int do_reduce;
+  int do_reduce;           // 0: labels/mind2 only; 1: sums + counts + cost; 2: cost only (partial_out[0])
+  int out_mode;            // 0: labels/mind2 are written; 1: mind2_out = min(mind2_out, new), labels follow the winner
+  int label_base;          // added to labels written in out_mode 1 (centre chunk offset)
   double* xnorm2_sum;      // see xx_mode
   int xx_mode;             // 0: per-row |x|^2 in-pass; 1: same, and store sum_w|x|^2; 2: reuse stored sum, skip per-row norms
   double* cta_partials;    // scratch: [gridDim.x][k*d + k + 2]
@@ -246,7 +248,9 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
         d0 = fmax(fma(-2.0, b0, xx0), 0.0); d1 = fmax(fma(-2.0, b1, xx1), 0.0);
       }
       const double c0 = (NEED_XX && xx_mode == 2) ? b0 : d0, c1 = (NEED_XX && xx_mode == 2) ? b1 : d1;
-      if (has_w) {
+      if (p.out_mode != 0) {
+        // min-merge mode: the output threads below own the cost
+      } else if (has_w) {
         const double w0 = v0 ? p.w[row0 + t0] : 0.0, w1 = v1 ? p.w[row0 + t1] : 0.0;
         cost = fma(c0, w0, cost); cost = fma(c1, w1, cost);
         if (NEED_XX && xx_mode == 1) { xxs = fma(xx0, w0, xxs); xxs = fma(xx1, w1, xxs); }
@@ -258,15 +262,26 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
       }
       labels_s[buf * kTileRows + t0] = v0 ? j0 : -1;
       labels_s[buf * kTileRows + t1] = v1 ? j1 : -1;
-      if (p.mind2_out != nullptr) { mind2_s[buf * kTileRows + t0] = d0; mind2_s[buf * kTileRows + t1] = d1; }
+      if (NEED_XX && p.mind2_out != nullptr) { mind2_s[buf * kTileRows + t0] = d0; mind2_s[buf * kTileRows + t1] = d1; }
     }
     __syncthreads();
     if (tid == 0 && refill >= 0) issue_tile(refill);  // the previous tile's stage is free now
 
     // ---------------- outputs (coalesced from smem)
-    if (p.labels_out != nullptr && tid < kTileRows && tid < rows_valid) p.labels_out[row0 + tid] = labels_s[buf * kTileRows + tid];
-    if (p.mind2_out != nullptr && tid >= kTileRows && (tid - kTileRows) < rows_valid)
-      p.mind2_out[row0 + tid - kTileRows] = mind2_s[buf * kTileRows + tid - kTileRows];
+    if (p.out_mode == 0) {
+      if (p.labels_out != nullptr && tid < kTileRows && tid < rows_valid) p.labels_out[row0 + tid] = labels_s[buf * kTileRows + tid];
+      if (p.mind2_out != nullptr && tid >= kTileRows && (tid - kTileRows) < rows_valid)
+        p.mind2_out[row0 + tid - kTileRows] = mind2_s[buf * kTileRows + tid - kTileRows];
+    } else if (tid < kTileRows && tid < rows_valid) {
+      // running minimum over successive centre chunks (k-means|| cost update, candidate weights):
+      // strict '<' keeps the earlier (lower-index) centre on ties, as findClosest does
+      const double nv = mind2_s[buf * kTileRows + tid], old = p.mind2_out[row0 + tid];
+      if (nv < old) {
+        p.mind2_out[row0 + tid] = nv;
+        if (p.labels_out != nullptr) p.labels_out[row0 + tid] = labels_s[buf * kTileRows + tid] + p.label_base;
+        cost += nv;
+      } else cost += old;
+    }
 
     // ---------------- phase 2: owner warps gather their clusters' rows
     // Each owner warp compacts the smem byte offsets of its clusters' rows into a private
@@ -274,7 +289,7 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
     // a multiple of 4 with the offset of an all-zero row, then streams the list: one
     // broadcast LDS.128 of four offsets, four row loads, four adds -- no per-row bit
     // twiddling, no predication, fixed order.
-    if (p.do_reduce) {
+    if (p.do_reduce == 1) {
       const uint32_t stage_off = (uint32_t)(xs - smem);
       int lab[kTileRows / 32];
 #pragma unroll
@@ -405,7 +420,7 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
 #pragma unroll
   for (int m = 0; m < NT; ++m) {
     const int j = warp + 8 * m;
-    if (j < k) {
+    if (j < k && p.do_reduce == 1) {
       if (sub == 0) {
 #pragma unroll
         for (int e = 0; e < FPL; ++e) { const int f = fl + 32 * e; if (f < d) out[(size_t)j * d + f] = acc_a[m][e]; }
@@ -428,11 +443,12 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
   __syncthreads();
   if (s_ticket == gridDim.x - 1) {
     __threadfence();
-    for (int i = tid; i < P + 1; i += kComputeThreads) {
+    for (int i = (p.do_reduce == 2 ? P - 1 + tid : tid); i < (p.do_reduce == 2 ? P : P + 1); i += kComputeThreads) {
       double s = 0;
       for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(p.cta_partials + (size_t)b * (P + 1) + i);
       if (i == P - 1 && xx_mode == 2) s = fmax(fma(-2.0, s, *p.xnorm2_sum), 0.0);  // cost = sum w|x|^2 - 2 sum w*score
-      if (i < P) p.partial_out[i] = s;
+      if (p.do_reduce == 2) p.partial_out[0] = s;
+      else if (i < P) p.partial_out[i] = s;
       else if (xx_mode == 1) *p.xnorm2_sum = s;
     }
     if (tid == 0) *p.counter = 0u;

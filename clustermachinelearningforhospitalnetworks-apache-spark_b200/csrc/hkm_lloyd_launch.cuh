@@ -2,6 +2,7 @@
 // instantiated in hkm_lloyd_inst.cu, compiled once per NT (-DHKM_NT=1..8) so the build
 // parallelises across translation units.
 #pragma once
+#include "../../include/hkm.h"
 #include "hkm_lloyd.cuh"
 
 namespace hkm {
@@ -22,6 +23,15 @@ inline LaunchPlan plan_lloyd(int d, int k_pad) {
   pl.smem = smem_layout(d, k_pad, pl.stages).total;
   return pl;
 }
+
+// Validated, dispatched Lloyd data pass shared by the C entry points (hkm_api.cu).
+struct AssignArgs {
+  const double* X; int64_t n; int d; const double* C; int k; const double* weights;
+  double* partial_out; int32_t* labels_out; double* mind2_out; double* xnorm2_sum; int xnorm2_mode;
+  const hkm_lloyd_state* state; int do_reduce; int out_mode; int label_base;
+  void* scratch; size_t scratch_bytes; void* stream;
+};
+int assign_pass(const AssignArgs& a, const char* who);
 
 // one function per NT, defined in hkm_lloyd_inst.cu
 int dispatch_lloyd_nt1(const LloydParams&, const LaunchPlan&, int grid, cudaStream_t);

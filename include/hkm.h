@@ -97,6 +97,43 @@ HKM_API int hkm_assign_reduce(const double* X, int64_t n, int d, const double* C
 HKM_API int hkm_update_centers(const double* partial, int k, int d, double* C_inout, double tol,
                        hkm_lloyd_state* state, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * k-means|| seeding (mllib KMeans.initKMeansParallel)
+ * ------------------------------------------------------------------------------------------- */
+
+/* Scratch bytes for hkm_kmpar_cost_update on the current device. */
+HKM_API size_t hkm_kmpar_scratch_bytes(int d);
+
+/*
+ * costs[i] = min(costs[i], min_j |x_i - newC_j|^2) and *sum_out = sum_i costs[i]
+ * (`costs = data.zip(preCosts).map(min(pointCost(newCenters, point), cost))` + `costs.sum()`).
+ * m new centres; any m >= 1 (processed in chunks of hkm_max_k()).
+ */
+HKM_API int hkm_kmpar_cost_update(const double* X, int64_t n, int d, const double* newC, int m, double* costs_inout,
+                                  double* sum_out, void* scratch, size_t scratch_bytes, void* stream);
+
+/*
+ * Bernoulli selection of one k-means|| step, partition-exact: row i of partition p is kept iff
+ * the i-th nextDouble() of XORShiftRandom(seed ^ (step << 16) ^ (part_index0 + p)) is
+ * < 2.0 * costs[i] * k / *sum_costs.  part_rows[P+1] are this rank's partition boundaries (local
+ * row offsets); strip_start[P+1] is the prefix sum of ceil(len_p / hkm_kmpar_strip_rows()).
+ * Selected local row indices are appended to idx_out (unordered; sort on the host), their number
+ * to *count_out (may exceed cap: then re-run with a larger buffer).  The first call on a device
+ * also builds the XORShift jump table on `stream`.
+ */
+HKM_API int hkm_kmpar_sample(const double* costs, int64_t n, const int64_t* part_rows, const int64_t* strip_start,
+                             int64_t total_strips, int P, int part_index0, int32_t seed, int step, int k,
+                             const double* sum_costs, int64_t* idx_out, int cap, int32_t* count_out, void* stream);
+HKM_API int hkm_kmpar_strip_rows(void);
+
+/*
+ * counts_out[j] = number of rows whose closest candidate (strict '<', lowest index on ties) is j
+ * (`data.map(findClosest(candidates, _)._1).countByValue()`); m candidates, any m >= 1.
+ * labels_work [n] int32 and mind2_work [n] double are caller-provided work arrays.
+ */
+HKM_API int hkm_closest_counts(const double* X, int64_t n, int d, const double* cand, int m, int32_t* labels_work,
+                               double* mind2_work, unsigned long long* counts_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

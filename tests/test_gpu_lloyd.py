@@ -1,0 +1,168 @@
+"""GPU parity of the Lloyd data pass (hkm_assign_reduce / hkm_update_centers, through the C ABI)
+against the CPU oracle on seeded inputs, plus size-independent properties at larger sizes."""
+import numpy as np
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+# north_star tolerances: labels >= 99.99 % identical (fp near-ties documented), sums / centres / cost 1e-6 relative.
+# The kernels do far better on well-conditioned data; the asserts below use tighter bounds where exactness is expected.
+LABEL_AGREE = 0.9999
+REL = 1e-6
+
+
+def _pass(N, Xh, Ch, wh=None, want=("labels", "mind2"), mode=0, xs=None):
+    X = torch.from_numpy(Xh).cuda(); C = torch.from_numpy(Ch).cuda()
+    n, d = Xh.shape; k = Ch.shape[0]
+    partial = torch.empty(k * d + k + 1, dtype=torch.float64, device="cuda")
+    labels = torch.empty(n, dtype=torch.int32, device="cuda") if "labels" in want else None
+    mind2 = torch.empty(n, dtype=torch.float64, device="cuda") if "mind2" in want else None
+    w = torch.from_numpy(wh).cuda() if wh is not None else None
+    scratch = N.new_scratch(d, k, "cuda")
+    N.assign_reduce(X, C, partial, labels, mind2, weights=w, scratch=scratch, xnorm2_sum=xs, xnorm2_mode=mode)
+    torch.cuda.synchronize()
+    p = partial.cpu().numpy()
+    return dict(sums=p[:k * d].reshape(k, d), wsum=p[k * d:k * d + k], cost=p[-1],
+                labels=None if labels is None else labels.cpu().numpy(), mind2=None if mind2 is None else mind2.cpu().numpy())
+
+
+def _check(g, o_sums, o_wsum, o_cost, o_lab, o_dist, scale):
+    assert (g["labels"] == o_lab).mean() >= LABEL_AGREE
+    same = g["labels"] == o_lab
+    assert np.abs(g["mind2"][same] - o_dist[same]).max() <= 1e-9 * scale
+    if same.all():
+        assert np.abs(g["sums"] - o_sums).max() <= 1e-11 * max(1.0, np.abs(o_sums).max())
+        assert np.abs(g["wsum"] - o_wsum).max() <= 1e-9 * max(1.0, o_wsum.max())
+    assert g["cost"] == pytest.approx(o_cost, rel=REL, abs=1e-9 * scale)
+
+
+SHAPES = [(1000, 8, 5), (128, 32, 8), (127, 32, 8), (129, 32, 8), (4096, 32, 8), (100003, 32, 8), (50000, 16, 16), (30000, 24, 7),
+          (30000, 24, 32), (20000, 5, 3), (20000, 7, 2), (20000, 64, 16), (20000, 33, 9), (77, 3, 2), (1, 4, 2), (20000, 64, 64),
+          (5000, 1, 3), (5000, 2, 8), (9000, 12, 20), (6000, 48, 24), (3000, 63, 33)]
+
+
+@pytest.mark.parametrize("n,d,k", SHAPES)
+def test_pass_matches_oracle(hkm, oracle, n, d, k):
+    rng = np.random.default_rng(n * 131 + d * 17 + k)
+    X = rng.normal(size=(n, d)) + rng.integers(0, k, size=(n, 1)) * 2.0
+    C = X[rng.choice(n, k, replace=n < k)].copy() if n >= k else rng.normal(size=(k, d))
+    g = _pass(hkm._native, X, C)
+    sums, wsum, cost, lab = oracle.lloyd_pass(X, C, P=1, want_labels=True)
+    _, dist = oracle.predict(X, C, want_dist=True)
+    _check(g, sums, wsum, cost, lab, dist, scale=float((X * X).sum(1).max()))
+
+
+def test_weighted_pass(hkm, oracle):
+    rng = np.random.default_rng(5)
+    for n, d, k in [(50000, 32, 8), (50000, 16, 16), (3000, 9, 40)]:
+        X = rng.normal(size=(n, d)) * 2; C = X[:k].copy(); w = rng.uniform(0.0, 3.0, size=n); w[::97] = 0.0
+        g = _pass(hkm._native, X, C, wh=w)
+        sums, wsum, cost, lab = oracle.lloyd_pass(X, C, w=w, P=1, want_labels=True)
+        _, dist = oracle.predict(X, C, want_dist=True)
+        _check(g, sums, wsum, cost, lab, dist, scale=float((X * X).sum(1).max()))
+
+
+def test_exact_ties_pick_lowest_index(hkm, oracle):
+    # integer lattice data with duplicated centres and midpoints: every tie must go to the lower index
+    rng = np.random.default_rng(1)
+    X = rng.integers(-3, 4, size=(20000, 6)).astype(np.float64)
+    C = np.array([[0, 0, 0, 0, 0, 0], [2, 0, 0, 0, 0, 0], [0, 0, 0, 0, 0, 0], [-2, 0, 0, 0, 0, 0], [2, 0, 0, 0, 0, 0],
+                  [0, 2, 0, 0, 0, 0], [0, -2, 0, 0, 0, 0], [1, 1, 1, 1, 1, 1], [1, 1, 1, 1, 1, 1]], dtype=np.float64)
+    g = _pass(hkm._native, X, C)
+    sums, wsum, cost, lab = oracle.lloyd_pass(X, C, P=1, want_labels=True)
+    assert np.array_equal(g["labels"], lab)            # exact arithmetic on small integers: no near-ties, only true ties
+    assert wsum[2] == 0 and wsum[4] == 0 and wsum[8] == 0 and np.array_equal(g["wsum"], wsum)
+    assert np.array_equal(g["sums"], sums) and g["cost"] == cost
+
+
+def test_duplicate_rows_and_empty_clusters(hkm, oracle):
+    X = np.repeat(np.array([[0.0, 0, 0], [1, 1, 1], [5, 5, 5]]), 1000, axis=0)
+    C = np.array([[0.0, 0, 0], [1, 1, 1], [5, 5, 5], [100, 100, 100], [-50, 0, 0]])
+    g = _pass(hkm._native, X, C)
+    assert g["wsum"].tolist() == [1000, 1000, 1000, 0, 0] and g["cost"] == 0.0 and np.all(g["mind2"] == 0.0)
+    assert np.array_equal(g["sums"][:3], C[:3] * 1000) and np.all(g["sums"][3:] == 0)
+
+
+def test_store_then_reuse_modes(hkm, oracle):
+    rng = np.random.default_rng(8)
+    X = rng.normal(size=(70001, 24)) + 1.5; C = X[:12].copy()
+    N = hkm._native
+    xs = torch.zeros(1, dtype=torch.float64, device="cuda")
+    a = _pass(N, X, C, want=(), mode=0)
+    b = _pass(N, X, C, want=(), mode=1, xs=xs)
+    c = _pass(N, X, C, want=(), mode=2, xs=xs)
+    assert np.array_equal(a["sums"], b["sums"]) and a["cost"] == b["cost"] and np.array_equal(a["sums"], c["sums"])
+    assert xs.item() == pytest.approx(float((X * X).sum()), rel=1e-13)
+    assert c["cost"] == pytest.approx(a["cost"], rel=1e-11)
+
+
+def test_update_centers_and_state(hkm, oracle):
+    rng = np.random.default_rng(4)
+    N = hkm._native
+    X = rng.normal(size=(30000, 10)) + rng.integers(0, 4, size=(30000, 1)) * 3
+    C0 = np.vstack([X[:5], [[500.0] * 10]])          # last centre attracts nothing and must stay put
+    Xd = torch.from_numpy(X).cuda(); C = torch.from_numpy(C0).cuda()
+    k, d = C0.shape
+    partial = torch.empty(k * d + k + 1, dtype=torch.float64, device="cuda")
+    scratch = N.new_scratch(d, k, "cuda"); state = N.new_state("cuda")
+    Co = C0.copy()
+    for it in range(1, 4):
+        N.assign_reduce(Xd, C, partial, state=state, scratch=scratch)
+        N.update_centers(partial, C, 1e-4, state)
+        sums, wsum, cost, _ = oracle.lloyd_pass(X, Co, P=1)
+        Co, conv = oracle.update_centers(sums, wsum, Co, 1e-4)
+        st = N.read_state(state)
+        assert st.iter == it and st.cost == pytest.approx(cost, rel=1e-12) and bool(st.converged) == conv
+        assert np.allclose(C.cpu().numpy(), Co, rtol=1e-12, atol=1e-12) and C.cpu().numpy()[5, 0] == 500.0
+    # once converged, further passes are no-ops on the device state
+    C2, it_o, cost_o = oracle.lloyd(X, C0, max_iter=100, tol=1e-4, P=1)
+    for _ in range(100):
+        N.assign_reduce(Xd, C, partial, state=state, scratch=scratch)
+        N.update_centers(partial, C, 1e-4, state)
+    st = N.read_state(state)
+    assert st.converged == 1 and st.iter == it_o and st.cost == pytest.approx(cost_o, rel=1e-10)
+    assert np.allclose(C.cpu().numpy(), C2, rtol=1e-9, atol=1e-9)
+
+
+def test_argument_errors(hkm):
+    N = hkm._native
+    X = torch.zeros(10, 4, dtype=torch.float64, device="cuda"); C = torch.zeros(2, 4, dtype=torch.float64, device="cuda")
+    with pytest.raises(N.HkmError, match="CUDA tensor"):
+        N.assign_reduce(X.cpu(), C, do_reduce=False)
+    with pytest.raises(N.HkmError, match="reduce needs"):
+        N.assign_reduce(X, C, do_reduce=True)
+    with pytest.raises(N.HkmError, match="outside fp64 kernel range"):
+        N.assign_reduce(torch.zeros(10, 500, dtype=torch.float64, device="cuda"), torch.zeros(2, 500, dtype=torch.float64, device="cuda"), do_reduce=False)
+    with pytest.raises(N.HkmError, match="16-byte aligned"):
+        N.assign_reduce(torch.zeros(41, dtype=torch.float64, device="cuda")[1:].view(10, 4), C, do_reduce=False)
+
+
+def test_full_size_properties(hkm):
+    """cfg2 size (10 M x 32, k = 8): properties that need no oracle -- counts add up, sums equal
+    the column totals, shard-by-shard partials add up to the whole (the multi-GPU reduction identity),
+    and the pass is bit-stable run to run."""
+    N = hkm._native
+    n, d, k = 10_000_000, 32, 8
+    g = torch.Generator(device="cuda"); g.manual_seed(3)
+    X = torch.randn(n, d, dtype=torch.float64, device="cuda", generator=g)
+    C = X[:k].clone()
+    P = k * d + k + 1
+    scratch = N.new_scratch(d, k, "cuda")
+    p1 = torch.empty(P, dtype=torch.float64, device="cuda"); p2 = torch.empty_like(p1)
+    labels = torch.empty(n, dtype=torch.int32, device="cuda")
+    N.assign_reduce(X, C, p1, labels=labels, scratch=scratch)
+    N.assign_reduce(X, C, p2, scratch=scratch)
+    assert torch.equal(p1, p2)
+    assert p1[k * d:k * d + k].sum().item() == n
+    assert torch.equal(p1[k * d:k * d + k], torch.bincount(labels, minlength=k).double())
+    col = X.sum(0)
+    assert torch.allclose(p1[:k * d].view(k, d).sum(0), col, rtol=1e-9, atol=1e-6)
+    acc = torch.zeros_like(p1)
+    bounds = [0, 1_234_567, 5_000_064, 9_999_999, n]
+    for lo, hi in zip(bounds[:-1], bounds[1:]):
+        lo16 = lo  # rows are 256 B, so any row offset keeps 16-byte alignment
+        N.assign_reduce(X[lo16:hi], C, p2, scratch=scratch)
+        acc += p2
+    assert torch.equal(acc[k * d:k * d + k], p1[k * d:k * d + k])
+    assert torch.allclose(acc, p1, rtol=1e-10, atol=1e-8)
