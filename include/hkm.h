@@ -89,6 +89,34 @@ HKM_API int hkm_assign_reduce(const double* X, int64_t n, int d, const double* C
                       void* scratch, size_t scratch_bytes, void* stream);
 
 /*
+ * hkm_assign_reduce for callers that cannot allocate device memory.  (No counterpart in the
+ * reference or in Spark: it exists for the way this library gets embedded.)
+ *
+ * Some hosts of this code are handed their device buffers and may not call cudaMalloc themselves:
+ * a plugin inside a JVM/Spark executor whose memory pool owns the GPU, a serving process with a
+ * pre-sized arena, a loop that must stay off the allocator lock.  They can pass X, C and the output
+ * vectors, but not the per-CTA scratch of hkm_assign_reduce -- so here the scratch is a fixed
+ * HKM_NOALLOC_SCRATCH_BYTES array that lives inside libhkm.so on every GPU that loads it, until
+ * the process exits.  Arguments and results are those of hkm_assign_reduce, minus scratch.
+ *
+ *  - Limit: hkm_assign_reduce_scratch_bytes(d, k) must fit in HKM_NOALLOC_SCRATCH_BYTES (4 MiB;
+ *    on a 148-SM B200 that is k*d + k + 2 <= 1770, e.g. k = 32, d = 32).  Larger shapes are
+ *    refused with HKM_ERR_UNSUPPORTED and a message naming both sizes.
+ *  - The call itself performs no cudaMalloc / cudaFree and calls no allocating library routine.
+ *  - The first call on each device looks up the array's device address (one cudaGetSymbolAddress
+ *    with that device current).  Make that first call before starting any stream capture.
+ *  - All calls on a device share the one array, which still holds the previous call's contents;
+ *    the entry point clears the 256-byte header it needs zeroed (on `stream`) before launching.
+ *    Two calls that overlap on the GPU -- different streams, no ordering between them -- race
+ *    on the array and produce garbage: keep calls to this entry point ordered on one stream.
+ */
+#define HKM_NOALLOC_SCRATCH_BYTES (4u << 20)
+HKM_API int hkm_assign_reduce_noalloc(const double* X, int64_t n, int d, const double* C, int k, const double* weights,
+                                      double* partial_out, int32_t* labels_out, double* mind2_out,
+                                      double* xnorm2_sum, int xnorm2_mode,
+                                      const hkm_lloyd_state* state, int do_reduce, void* stream);
+
+/*
  * Driver side of the iteration (KMeans.runAlgorithmWithWeight after collectAsMap, 8a-5):
  * new_j = sums_j * (1/w_j) for clusters with w_j > 0 (others keep their centre), converged iff
  * every updated centre moved by sqdist <= tol^2; state->cost/iter/converged updated.
