@@ -8,7 +8,8 @@
 """
 from . import _native, _runtime, _sparkrand, table  # noqa: F401
 from .table import Table, DeviceMatrix, Column  # noqa: F401
-from .ml import param, linalg, clustering, _kmeans_init  # noqa: F401
+from .ml import param, linalg, clustering, evaluation, _kmeans_init  # noqa: F401
+from .ml.evaluation import ClusteringEvaluator  # noqa: F401
 from . import datagen  # noqa: F401
 from .ml.clustering import KMeans, KMeansModel, KMeansSummary  # noqa: F401
 from .ml.param import IllegalArgumentException  # noqa: F401

@@ -17,6 +17,7 @@ EXPORTS = (
     "hkm_last_error", "hkm_version", "hkm_max_k", "hkm_max_d",
     "hkm_assign_reduce_scratch_bytes", "hkm_assign_reduce", "hkm_update_centers",
     "hkm_kmpar_scratch_bytes", "hkm_kmpar_cost_update", "hkm_kmpar_sample", "hkm_kmpar_strip_rows", "hkm_closest_counts",
+    "hkm_silhouette_stats", "hkm_silhouette_score",
 )
 
 _lib = None
@@ -53,6 +54,8 @@ def load() -> ctypes.CDLL:
         L.hkm_kmpar_cost_update.argtypes = [vp, i64, i32, vp, i32, vp, vp, vp, sz, vp]
         L.hkm_kmpar_sample.argtypes = [vp, i64, vp, vp, i64, i32, i32, ctypes.c_int32, i32, i32, vp, vp, i32, vp, vp]
         L.hkm_closest_counts.argtypes = [vp, i64, i32, vp, i32, vp, vp, vp, vp]
+        L.hkm_silhouette_stats.argtypes = [vp, vp, vp, i64, i32, i32, vp, vp, sz, vp]
+        L.hkm_silhouette_score.argtypes = [vp, vp, vp, i64, i32, i32, vp, vp, vp, vp, sz, vp]
         _lib = L
     return _lib
 
@@ -155,4 +158,22 @@ def closest_counts(X, cand, labels_work, mind2_work, counts_out):
     with torch.cuda.device(X.device):
         rc = load().hkm_closest_counts(_ptr(X), n, d, _ptr(cand), cand.shape[0], _ptr(labels_work), _ptr(mind2_work),
                                        _ptr(counts_out), _stream())
+    _check(rc)
+
+
+def silhouette_stats(X, labels, k, stats_out, scratch, weights=None):
+    require_cuda(X, "X", torch.float64); require_cuda(labels, "labels", torch.int32)
+    n, d = X.shape
+    with torch.cuda.device(X.device):
+        rc = load().hkm_silhouette_stats(_ptr(X), _ptr(labels), _ptr(weights), n, d, k, _ptr(stats_out), _ptr(scratch),
+                                         scratch.numel() * scratch.element_size(), _stream())
+    _check(rc)
+
+
+def silhouette_score(X, labels, k, stats, work, out2, scratch, weights=None):
+    require_cuda(X, "X", torch.float64); require_cuda(labels, "labels", torch.int32)
+    n, d = X.shape
+    with torch.cuda.device(X.device):
+        rc = load().hkm_silhouette_score(_ptr(X), _ptr(labels), _ptr(weights), n, d, k, _ptr(stats), _ptr(work), _ptr(out2),
+                                         _ptr(scratch), scratch.numel() * scratch.element_size(), _stream())
     _check(rc)

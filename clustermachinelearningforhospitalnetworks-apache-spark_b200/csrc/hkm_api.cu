@@ -27,16 +27,16 @@ int sm_count() {
 }
 
 // ------------------------------------------------------------------ Lloyd pass dispatch (per-NT translation units)
-static int dispatch_lloyd(const LloydParams& p, const LaunchPlan& pl, int grid, cudaStream_t st) {
+static int dispatch_lloyd(const LloydParams& p, const LaunchPlan& pl, int grid, int mode, cudaStream_t st) {
   switch ((p.k + 7) / 8) {
-    case 1: return dispatch_lloyd_nt1(p, pl, grid, st);
-    case 2: return dispatch_lloyd_nt2(p, pl, grid, st);
-    case 3: return dispatch_lloyd_nt3(p, pl, grid, st);
-    case 4: return dispatch_lloyd_nt4(p, pl, grid, st);
-    case 5: return dispatch_lloyd_nt5(p, pl, grid, st);
-    case 6: return dispatch_lloyd_nt6(p, pl, grid, st);
-    case 7: return dispatch_lloyd_nt7(p, pl, grid, st);
-    case 8: return dispatch_lloyd_nt8(p, pl, grid, st);
+    case 1: return dispatch_lloyd_nt1(p, pl, grid, mode, st);
+    case 2: return dispatch_lloyd_nt2(p, pl, grid, mode, st);
+    case 3: return dispatch_lloyd_nt3(p, pl, grid, mode, st);
+    case 4: return dispatch_lloyd_nt4(p, pl, grid, mode, st);
+    case 5: return dispatch_lloyd_nt5(p, pl, grid, mode, st);
+    case 6: return dispatch_lloyd_nt6(p, pl, grid, mode, st);
+    case 7: return dispatch_lloyd_nt7(p, pl, grid, mode, st);
+    case 8: return dispatch_lloyd_nt8(p, pl, grid, mode, st);
   }
   set_error("k=%d outside the fp64 kernel range (max %d)", p.k, 64);
   return HKM_ERR_UNSUPPORTED;
@@ -95,13 +95,13 @@ int assign_pass(const AssignArgs& a, const char* who) {
   LloydParams p{};
   p.X = a.X; p.n = a.n; p.d = d; p.k = k; p.C = a.C; p.w = a.weights; p.partial_out = a.partial_out; p.labels_out = a.labels_out;
   p.mind2_out = a.mind2_out; p.skip = a.state ? &a.state->converged : nullptr; p.do_reduce = a.do_reduce;
-  p.out_mode = a.out_mode; p.label_base = a.label_base;
+  p.out_mode = a.out_mode; p.label_base = a.label_base; p.labels_in = a.labels_in; p.aux = a.aux;
   p.xnorm2_sum = a.xnorm2_sum; p.xx_mode = a.do_reduce == 1 ? a.xnorm2_mode : 0;
   p.counter = reinterpret_cast<unsigned int*>(a.scratch);
   p.cta_partials = a.scratch ? reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(a.scratch) + 256) : nullptr;
   p.stages = pl.stages; p.ks = (d + 3) / 4;
   const int grid = sm_count() * pl.ctas_per_sm;
-  return dispatch_lloyd(p, pl, grid, reinterpret_cast<cudaStream_t>(a.stream));
+  return dispatch_lloyd(p, pl, grid, a.mode, reinterpret_cast<cudaStream_t>(a.stream));
 }
 
 }  // namespace hkm
@@ -120,7 +120,7 @@ size_t hkm_assign_reduce_scratch_bytes(int d, int k) {
   const int k_pad = ((k + 7) / 8) * 8;
   LaunchPlan pl = plan_lloyd(d, k_pad);
   size_t grid = (size_t)sm_count() * pl.ctas_per_sm;
-  return 256 + grid * ((size_t)k * d + k + 2) * sizeof(double);
+  return 256 + grid * ((size_t)k * d + 2 * (size_t)k + 2) * sizeof(double);
 }
 
 int hkm_assign_reduce(const double* X, int64_t n, int d, const double* C, int k, const double* weights, double* partial_out,

@@ -43,6 +43,8 @@ struct LloydParams {
   double* mind2_out;       // nullable
   const int32_t* skip;     // nullable: device flag, nonzero => no-op
   int do_reduce;           // 0: labels/mind2 only; 1: sums + counts + cost; 2: cost only (partial_out[0])
+  const int32_t* labels_in;  // MODE 1/2 (silhouette): given cluster ids; ids outside [0, k) are ignored
+  const double* aux;         // MODE 2: [k] cluster weight sums N, then [k] Psi/N
   int out_mode;            // 0: labels/mind2 are written; 1: mind2_out = min(mind2_out, new), labels follow the winner
   int label_base;          // added to labels written in out_mode 1 (centre chunk offset)
   double* xnorm2_sum;      // see xx_mode
@@ -69,7 +71,7 @@ __host__ __device__ inline SmemLayout smem_layout(int d, int k_pad, int stages) 
   L.labels_off = o; o += 2 * kTileRows * 4;
   L.mind2_off = o; o += 2 * kTileRows * 8;
   L.cs_off = o; o += k_pad * cs_ld(d) * 8;
-  L.cn_off = o; o += k_pad * 8;
+  L.cn_off = o; o += 2 * k_pad * 8;
   L.red_off = o; o += 2 * kComputeWarps * 8 + 16;
   L.bar_off = o; o += kMaxStages * 8;
   L.list_off = o; o += kComputeWarps * list_entries(k_pad) * 4; o = (o + 15) & ~15;
@@ -83,7 +85,9 @@ __host__ __device__ inline SmemLayout smem_layout(int d, int k_pad, int stages) 
 // KS_T == 0: B-fragments are re-read from shared memory, runtime k-step count.
 // NT = ceil(k/8) score column tiles == clusters owned per warp in phase 2.
 // LPR = lanes per row in phase 2 (8/16/32), FPL = features per lane (d > 32).
-template <int KS_T, int NT, int LPR, int FPL, int MAXREG>
+// MODE 0: Lloyd / predict pass.  MODE 1: silhouette cluster statistics (labels given: per-cluster
+// sum w*x, sum w, sum w*|x|^2).  MODE 2: silhouette score pass (labels + statistics given).
+template <int KS_T, int NT, int LPR, int FPL, int MAXREG, int MODE = 0>
 __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kernel(const LloydParams p) {
   if (p.skip != nullptr && *p.skip != 0) return;
 
@@ -123,7 +127,15 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
   for (int j = tid; j < k_pad; j += kThreads) {
     double s = 0;
     for (int f = 0; f < d; ++f) s = fma(Cs[j * csld + f], Cs[j * csld + f], s);
-    cn_s[j] = j < k ? -0.5 * s : -__longlong_as_double(0x7ff0000000000000LL);
+    const double ninf = -__longlong_as_double(0x7ff0000000000000LL);
+    if (MODE == 2) {
+      // D(x, G) = |x|^2 + Psi_G/N_G - 2 x.(Y_G/N_G): same shape as the Lloyd score with -0.5*Psi_G/N_G as the constant
+      const double Nj = j < k ? p.aux[j] : 0.0;
+      cn_s[j] = (j < k && Nj > 0) ? -0.5 * p.aux[k + j] : ninf;
+      cn_s[k_pad + j] = Nj;
+    } else {
+      cn_s[j] = j < k ? -0.5 * s : ninf;
+    }
   }
   __syncthreads();
 
@@ -175,6 +187,10 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
   const int sub = lane / LPR, fl = lane % LPR;
   constexpr int RPS = 32 / LPR;  // rows handled per warp load step
   const bool has_w = p.w != nullptr;
+  const bool extras = has_w || MODE == 1;   // phase 2 needs per-row scalars (weight, |x|^2) next to the row itself
+  double psi[NT];                            // MODE 1: sum of w*|x|^2 per owned cluster (lane fl == 0 only)
+#pragma unroll
+  for (int m = 0; m < NT; ++m) psi[m] = 0;
   uint32_t* list_w = reinterpret_cast<uint32_t*>(smem + L.list_off) + warp * list_entries(k_pad);
   const unsigned lt_mask = (1u << lane) - 1u;
   const int row_bytes = d * 8;
@@ -204,7 +220,7 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
         double a0 = ok ? xa0[4 * s] : 0.0, a1 = ok ? xa1[4 * s] : 0.0;
         if (NEED_XX) { xx0 = fma(a0, a0, xx0); xx1 = fma(a1, a1, xx1); }
 #pragma unroll
-        for (int nt = 0; nt < NT; ++nt) { dmma884(s0[nt][0], s0[nt][1], a0, breg[s * NT + nt]); dmma884(s1[nt][0], s1[nt][1], a1, breg[s * NT + nt]); }
+        for (int nt = 0; nt < NT; ++nt) { if (MODE != 1) { dmma884(s0[nt][0], s0[nt][1], a0, breg[s * NT + nt]); dmma884(s1[nt][0], s1[nt][1], a1, breg[s * NT + nt]); } }
       }
     } else {
       const double* cb = Cs + r * csld + q;
@@ -214,61 +230,121 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
         if (NEED_XX) { xx0 = fma(a0, a0, xx0); xx1 = fma(a1, a1, xx1); }
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) {
-          double b = cb[(8 * nt) * csld + 4 * s];
-          dmma884(s0[nt][0], s0[nt][1], a0, b); dmma884(s1[nt][0], s1[nt][1], a1, b);
+          if (MODE != 1) {
+            double b = cb[(8 * nt) * csld + 4 * s];
+            dmma884(s0[nt][0], s0[nt][1], a0, b); dmma884(s1[nt][0], s1[nt][1], a1, b);
+          }
         }
       }
     }
-    // argmax over this lane's columns (ascending index), then across the 4 lanes of the row
-    double b0 = s0[0][0], b1 = s1[0][0]; int j0 = 2 * q, j1 = 2 * q;
+    const int t0 = r * kChunkRows + i0, t1 = r * kChunkRows + i1;
+    if constexpr (MODE == 1) {
+      // ---- silhouette statistics: labels are given; phase 1 only supplies |x|^2 per row
 #pragma unroll
-    for (int nt = 0; nt < NT; ++nt)
-#pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        if (nt == 0 && e == 0) continue;
-        const int j = 8 * nt + 2 * q + e;
-        if (s0[nt][e] > b0) { b0 = s0[nt][e]; j0 = j; }
-        if (s1[nt][e] > b1) { b1 = s1[nt][e]; j1 = j; }
+      for (int msk = 1; msk <= 2; msk <<= 1) { xx0 += shfl_xor_d(xx0, msk); xx1 += shfl_xor_d(xx1, msk); }
+      if (q == 0) {
+        const bool v0 = t0 < rows_valid, v1 = t1 < rows_valid;
+        int l0 = v0 ? p.labels_in[row0 + t0] : -1, l1 = v1 ? p.labels_in[row0 + t1] : -1;
+        if (l0 >= k) l0 = -1;
+        if (l1 >= k) l1 = -1;
+        labels_s[buf * kTileRows + t0] = l0; labels_s[buf * kTileRows + t1] = l1;
+        w_s[buf * kTileRows + t0] = (v0 && has_w) ? p.w[row0 + t0] : 1.0;
+        w_s[buf * kTileRows + t1] = (v1 && has_w) ? p.w[row0 + t1] : 1.0;
+        // ClusteringMetrics: squaredNorm = math.pow(Vectors.norm(features, 2.0), 2.0)
+        const double n0 = sqrt(xx0), n1 = sqrt(xx1);
+        mind2_s[buf * kTileRows + t0] = n0 * n0; mind2_s[buf * kTileRows + t1] = n1 * n1;
       }
-#pragma unroll
-    for (int msk = 1; msk <= 2; msk <<= 1) {
-      double o0 = shfl_xor_d(b0, msk), o1 = shfl_xor_d(b1, msk);
-      int oj0 = __shfl_xor_sync(0xffffffffu, j0, msk), oj1 = __shfl_xor_sync(0xffffffffu, j1, msk);
-      if (o0 > b0 || (o0 == b0 && oj0 < j0)) { b0 = o0; j0 = oj0; }
-      if (o1 > b1 || (o1 == b1 && oj1 < j1)) { b1 = o1; j1 = oj1; }
-      if (NEED_XX) { xx0 += shfl_xor_d(xx0, msk); xx1 += shfl_xor_d(xx1, msk); }
-    }
-    if (q == 0) {
-      const int t0 = r * kChunkRows + i0, t1 = r * kChunkRows + i1;
+    } else if constexpr (MODE == 2) {
+      // ---- silhouette score (ClusteringMetrics.pointSilhouetteCoefficient), one value per row
       const bool v0 = t0 < rows_valid, v1 = t1 < rows_valid;
-      // per-row term of the cost: the clamped distance, or (mode 2) the score itself, folded
-      // against the stored sum of |x|^2 by the last CTA
-      double d0 = b0, d1 = b1;
-      if (NEED_XX) {
-        d0 = fmax(fma(-2.0, b0, xx0), 0.0); d1 = fmax(fma(-2.0, b1, xx1), 0.0);
+      int a0l = v0 ? p.labels_in[row0 + t0] : -1, a1l = v1 ? p.labels_in[row0 + t1] : -1;   // same address on the 4 lanes of a row
+      if (a0l >= k) a0l = -1;
+      if (a1l >= k) a1l = -1;
+      const double ninf = -__longlong_as_double(0x7ff0000000000000LL);
+      double own0 = ninf, own1 = ninf, oth0 = ninf, oth1 = ninf;
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int j = 8 * nt + 2 * q + e;
+          if (j == a0l) own0 = s0[nt][e]; else oth0 = fmax(oth0, s0[nt][e]);
+          if (j == a1l) own1 = s1[nt][e]; else oth1 = fmax(oth1, s1[nt][e]);
+        }
+#pragma unroll
+      for (int msk = 1; msk <= 2; msk <<= 1) {
+        own0 = fmax(own0, shfl_xor_d(own0, msk)); own1 = fmax(own1, shfl_xor_d(own1, msk));
+        oth0 = fmax(oth0, shfl_xor_d(oth0, msk)); oth1 = fmax(oth1, shfl_xor_d(oth1, msk));
+        xx0 += shfl_xor_d(xx0, msk); xx1 += shfl_xor_d(xx1, msk);
       }
-      const double c0 = (NEED_XX && xx_mode == 2) ? b0 : d0, c1 = (NEED_XX && xx_mode == 2) ? b1 : d1;
-      if (p.out_mode != 0) {
-        // min-merge mode: the output threads below own the cost
-      } else if (has_w) {
-        const double w0 = v0 ? p.w[row0 + t0] : 0.0, w1 = v1 ? p.w[row0 + t1] : 0.0;
-        cost = fma(c0, w0, cost); cost = fma(c1, w1, cost);
-        if (NEED_XX && xx_mode == 1) { xxs = fma(xx0, w0, xxs); xxs = fma(xx1, w1, xxs); }
-        w_s[buf * kTileRows + t0] = w0; w_s[buf * kTileRows + t1] = w1;
-      } else {
-        if (v0) cost += c0;
-        if (v1) cost += c1;
-        if (NEED_XX && xx_mode == 1) { if (v0) xxs += xx0; if (v1) xxs += xx1; }
+      if (q == 0) {
+        auto point = [&](bool valid, int a, double xx, double own, double oth, int64_t row) {
+          if (!valid || a < 0) return;
+          const double wv = has_w ? p.w[row] : 1.0;
+          const double nrm = sqrt(xx), sn = nrm * nrm;
+          const double NA = cn_s[k_pad + a];
+          double sil = 0.0;
+          if (NA != wv) {                                  // single-element clusters have silhouette 0
+            const double cur = fma(-2.0, own, sn) * NA / (NA - wv);
+            const double nb = fma(-2.0, oth, sn);
+            if (cur < nb) sil = 1.0 - (cur / nb); else if (cur > nb) sil = (nb / cur) - 1.0;
+          }
+          cost = fma(sil, wv, cost); xxs += wv;
+        };
+        point(v0, a0l, xx0, own0, oth0, row0 + t0);
+        point(v1, a1l, xx1, own1, oth1, row0 + t1);
       }
-      labels_s[buf * kTileRows + t0] = v0 ? j0 : -1;
-      labels_s[buf * kTileRows + t1] = v1 ? j1 : -1;
-      if (NEED_XX && p.mind2_out != nullptr) { mind2_s[buf * kTileRows + t0] = d0; mind2_s[buf * kTileRows + t1] = d1; }
+    } else {
+      // argmax over this lane's columns (ascending index), then across the 4 lanes of the row
+      double b0 = s0[0][0], b1 = s1[0][0]; int j0 = 2 * q, j1 = 2 * q;
+  #pragma unroll
+      for (int nt = 0; nt < NT; ++nt)
+  #pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          if (nt == 0 && e == 0) continue;
+          const int j = 8 * nt + 2 * q + e;
+          if (s0[nt][e] > b0) { b0 = s0[nt][e]; j0 = j; }
+          if (s1[nt][e] > b1) { b1 = s1[nt][e]; j1 = j; }
+        }
+  #pragma unroll
+      for (int msk = 1; msk <= 2; msk <<= 1) {
+        double o0 = shfl_xor_d(b0, msk), o1 = shfl_xor_d(b1, msk);
+        int oj0 = __shfl_xor_sync(0xffffffffu, j0, msk), oj1 = __shfl_xor_sync(0xffffffffu, j1, msk);
+        if (o0 > b0 || (o0 == b0 && oj0 < j0)) { b0 = o0; j0 = oj0; }
+        if (o1 > b1 || (o1 == b1 && oj1 < j1)) { b1 = o1; j1 = oj1; }
+        if (NEED_XX) { xx0 += shfl_xor_d(xx0, msk); xx1 += shfl_xor_d(xx1, msk); }
+      }
+      if (q == 0) {
+        const bool v0 = t0 < rows_valid, v1 = t1 < rows_valid;
+        // per-row term of the cost: the clamped distance, or (mode 2) the score itself, folded
+        // against the stored sum of |x|^2 by the last CTA
+        double d0 = b0, d1 = b1;
+        if (NEED_XX) {
+          d0 = fmax(fma(-2.0, b0, xx0), 0.0); d1 = fmax(fma(-2.0, b1, xx1), 0.0);
+        }
+        const double c0 = (NEED_XX && xx_mode == 2) ? b0 : d0, c1 = (NEED_XX && xx_mode == 2) ? b1 : d1;
+        if (p.out_mode != 0) {
+          // min-merge mode: the output threads below own the cost
+        } else if (has_w) {
+          const double w0 = v0 ? p.w[row0 + t0] : 0.0, w1 = v1 ? p.w[row0 + t1] : 0.0;
+          cost = fma(c0, w0, cost); cost = fma(c1, w1, cost);
+          if (NEED_XX && xx_mode == 1) { xxs = fma(xx0, w0, xxs); xxs = fma(xx1, w1, xxs); }
+          w_s[buf * kTileRows + t0] = w0; w_s[buf * kTileRows + t1] = w1;
+        } else {
+          if (v0) cost += c0;
+          if (v1) cost += c1;
+          if (NEED_XX && xx_mode == 1) { if (v0) xxs += xx0; if (v1) xxs += xx1; }
+        }
+        labels_s[buf * kTileRows + t0] = v0 ? j0 : -1;
+        labels_s[buf * kTileRows + t1] = v1 ? j1 : -1;
+        if (NEED_XX && p.mind2_out != nullptr) { mind2_s[buf * kTileRows + t0] = d0; mind2_s[buf * kTileRows + t1] = d1; }
+      }
     }
     __syncthreads();
     if (tid == 0 && refill >= 0) issue_tile(refill);  // the previous tile's stage is free now
 
     // ---------------- outputs (coalesced from smem)
-    if (p.out_mode == 0) {
+    if (MODE != 0) {
+    } else if (p.out_mode == 0) {
       if (p.labels_out != nullptr && tid < kTileRows && tid < rows_valid) p.labels_out[row0 + tid] = labels_s[buf * kTileRows + tid];
       if (p.mind2_out != nullptr && tid >= kTileRows && (tid - kTileRows) < rows_valid)
         p.mind2_out[row0 + tid - kTileRows] = mind2_s[buf * kTileRows + tid - kTileRows];
@@ -289,7 +365,7 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
     // a multiple of 4 with the offset of an all-zero row, then streams the list: one
     // broadcast LDS.128 of four offsets, four row loads, four adds -- no per-row bit
     // twiddling, no predication, fixed order.
-    if (p.do_reduce == 1) {
+    if (p.do_reduce == 1 && MODE != 2) {
       const uint32_t stage_off = (uint32_t)(xs - smem);
       int lab[kTileRows / 32];
 #pragma unroll
@@ -306,7 +382,7 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
           const unsigned mask = __ballot_sync(0xffffffffu, mine);
           if (mine) {
             uint32_t e = stage_off + off_lane + g * group_stride;
-            if (has_w) { e |= (uint32_t)(g * 32 + lane) << 20; }
+            if (extras) { e |= (uint32_t)(g * 32 + lane) << 20; }
             list_w[pos + __popc(mask & lt_mask)] = e;
           }
           pos += __popc(mask);
@@ -321,7 +397,7 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
         cnt[m] += seg_cnt[m];
         const uint32_t* lp = list_w + seg_begin[m];
         const unsigned nquad = (seg_cnt[m] + 3) >> 2;
-        if (!has_w) {
+        if (!extras) {
 #pragma unroll 2
           for (unsigned i = 0; i < nquad; ++i) {
             const uint4 o = *reinterpret_cast<const uint4*>(lp + 4 * i);
@@ -351,7 +427,10 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
               const double* xr = reinterpret_cast<const double*>(smem_lane + (osel & 0xFFFFFu));
               const bool pad = (osel & 0xFFFFFu) == (uint32_t)L.zero_off;
               const double wv = pad ? 0.0 : w_s[buf * kTileRows + (osel >> 20)];
-              if (fl == 0) wacc[m] += wv;
+              if (fl == 0) {
+                wacc[m] += wv;
+                if (MODE == 1) psi[m] = fma(wv, pad ? 0.0 : mind2_s[buf * kTileRows + (osel >> 20)], psi[m]);
+              }
 #pragma unroll
               for (int e = 0; e < FPL; ++e) {
                 const double v = (fl + 32 * e) < d ? xr[32 * e] : 0.0;  // keep 0*garbage out of the fma
@@ -392,6 +471,7 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
     }
   }
   if (!p.do_reduce) return;
+  if (MODE == 2) { /* the score pass reduces (sum s*w, sum w) through the cost / xxs slots */ }
 
   // ===================================================================== CTA-level combine
   const int P = k * d + k + 1;
@@ -409,14 +489,16 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
       for (int msk = LPR; msk < 32; msk <<= 1) v += shfl_xor_d(v, msk);
       acc_a[m][e] = v;
     }
-    if (has_w) {
-      double c = wacc[m];
+    if (extras) {
+      double c = wacc[m], ps = psi[m];
 #pragma unroll
-      for (int msk = 16; msk >= 1; msk >>= 1) c += shfl_xor_d(c, msk);
-      wacc[m] = c;
+      for (int msk = 16; msk >= 1; msk >>= 1) { c += shfl_xor_d(c, msk); ps += shfl_xor_d(ps, msk); }
+      wacc[m] = c; psi[m] = ps;
     } else wacc[m] = (double)cnt[m];
   }
-  double* out = p.cta_partials + (size_t)blockIdx.x * (P + 1);
+  // per-CTA slot: [k*d sums][k weights][cost][sum w|x|^2][k psi (MODE 1)]
+  const int S = P + 1 + k;
+  double* out = p.cta_partials + (size_t)blockIdx.x * S;
 #pragma unroll
   for (int m = 0; m < NT; ++m) {
     const int j = warp + 8 * m;
@@ -425,7 +507,7 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
 #pragma unroll
         for (int e = 0; e < FPL; ++e) { const int f = fl + 32 * e; if (f < d) out[(size_t)j * d + f] = acc_a[m][e]; }
       }
-      if (lane == 0) out[(size_t)k * d + j] = wacc[m];
+      if (lane == 0) { out[(size_t)k * d + j] = wacc[m]; if (MODE == 1) out[P + 1 + j] = psi[m]; }
     }
   }
   __syncthreads();
@@ -443,13 +525,17 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
   __syncthreads();
   if (s_ticket == gridDim.x - 1) {
     __threadfence();
-    for (int i = (p.do_reduce == 2 ? P - 1 + tid : tid); i < (p.do_reduce == 2 ? P : P + 1); i += kComputeThreads) {
+    const int i_lo = (MODE == 2 || p.do_reduce == 2) ? P - 1 : 0;
+    const int i_hi = MODE == 2 ? P + 1 : (p.do_reduce == 2 ? P : (MODE == 1 ? S : P + 1));
+    for (int i = i_lo + tid; i < i_hi; i += kComputeThreads) {
       double s = 0;
-      for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(p.cta_partials + (size_t)b * (P + 1) + i);
+      for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(p.cta_partials + (size_t)b * S + i);
       if (i == P - 1 && xx_mode == 2) s = fmax(fma(-2.0, s, *p.xnorm2_sum), 0.0);  // cost = sum w|x|^2 - 2 sum w*score
-      if (p.do_reduce == 2) p.partial_out[0] = s;
+      if (MODE == 2) p.partial_out[i - (P - 1)] = s;           // [sum s*w, sum w]
+      else if (p.do_reduce == 2) p.partial_out[0] = s;
       else if (i < P) p.partial_out[i] = s;
-      else if (xx_mode == 1) *p.xnorm2_sum = s;
+      else if (i == P) { if (xx_mode == 1) *p.xnorm2_sum = s; }
+      else p.partial_out[i - 1] = s;                           // MODE 1: psi follows [sums][N][cost]
     }
     if (tid == 0) *p.counter = 0u;
   }

@@ -8,9 +8,9 @@
 
 namespace hkm {
 
-template <int KS_T, int NT, int LPR, int FPL, int MAXREG>
+template <int KS_T, int NT, int LPR, int FPL, int MAXREG, int MODE = 0>
 static int launch_lloyd(const LloydParams& p, const LaunchPlan& pl, int grid, cudaStream_t st) {
-  auto kern = lloyd_pass_kernel<KS_T, NT, LPR, FPL, MAXREG>;
+  auto kern = lloyd_pass_kernel<KS_T, NT, LPR, FPL, MAXREG, MODE>;
   static int attr_smem[64];  // per device: largest dynamic smem opted into so far
   int dev = 0; HKM_CUDA_TRY(cudaGetDevice(&dev));
   if (dev >= 64 || attr_smem[dev] < pl.smem) {
@@ -31,24 +31,27 @@ static int launch_regb(const LloydParams& p, const LaunchPlan& pl, int grid, cud
   constexpr int MAXREG = (KS_T * NT <= 16 && NT <= 2) ? 128 : 255;
   return launch_lloyd<KS_T, NT, LPR, FPL, MAXREG>(p, pl, grid, st);
 }
-template <int NT>
+template <int NT, int MODE = 0>
 static int launch_smemb(const LloydParams& p, const LaunchPlan& pl, int grid, cudaStream_t st) {
   const int d = p.d;
   constexpr int MINB = NT <= 2 ? 128 : 255;
-  if (d <= 8) return launch_lloyd<0, NT, 8, 1, MINB>(p, pl, grid, st);
-  if (d <= 16) return launch_lloyd<0, NT, 16, 1, MINB>(p, pl, grid, st);
-  if (d <= 32) return launch_lloyd<0, NT, 32, 1, MINB>(p, pl, grid, st);
-  if (d <= 64) return launch_lloyd<0, NT, 32, 2, MINB>(p, pl, grid, st);
-  if (d <= 96) return launch_lloyd<0, NT, 32, 3, 255>(p, pl, grid, st);
-  return launch_lloyd<0, NT, 32, 4, 255>(p, pl, grid, st);
+  if (d <= 8) return launch_lloyd<0, NT, 8, 1, MINB, MODE>(p, pl, grid, st);
+  if (d <= 16) return launch_lloyd<0, NT, 16, 1, MINB, MODE>(p, pl, grid, st);
+  if (d <= 32) return launch_lloyd<0, NT, 32, 1, MINB, MODE>(p, pl, grid, st);
+  if (d <= 64) return launch_lloyd<0, NT, 32, 2, MINB, MODE>(p, pl, grid, st);
+  if (d <= 96) return launch_lloyd<0, NT, 32, 3, 255, MODE>(p, pl, grid, st);
+  return launch_lloyd<0, NT, 32, 4, 255, MODE>(p, pl, grid, st);
 }
 
 #define HKM_CAT2(a, b) a##b
 #define HKM_CAT(a, b) HKM_CAT2(a, b)
 
-int HKM_CAT(dispatch_lloyd_nt, HKM_NT)(const LloydParams& p, const LaunchPlan& pl, int grid, cudaStream_t st) {
+int HKM_CAT(dispatch_lloyd_nt, HKM_NT)(const LloydParams& p, const LaunchPlan& pl, int grid, int mode, cudaStream_t st) {
   constexpr int NT = HKM_NT;
   const int ks = p.ks;
+  // silhouette passes use the generic shared-memory-B kernel
+  if (mode == 1) return launch_smemb<NT, 1>(p, pl, grid, st);
+  if (mode == 2) return launch_smemb<NT, 2>(p, pl, grid, st);
   // register-resident B fragments while KS*NT doubles per lane stay affordable
 #define HKM_REGB(KS) if constexpr (KS * NT <= 32) { if (ks == KS) return launch_regb<KS, NT>(p, pl, grid, st); }
 #ifndef HKM_DEV_FAST

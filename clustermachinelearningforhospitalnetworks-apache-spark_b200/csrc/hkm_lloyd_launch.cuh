@@ -29,18 +29,19 @@ struct AssignArgs {
   const double* X; int64_t n; int d; const double* C; int k; const double* weights;
   double* partial_out; int32_t* labels_out; double* mind2_out; double* xnorm2_sum; int xnorm2_mode;
   const hkm_lloyd_state* state; int do_reduce; int out_mode; int label_base;
+  int mode; const int32_t* labels_in; const double* aux;   // mode 1/2: silhouette statistics / score pass
   void* scratch; size_t scratch_bytes; void* stream;
 };
 int assign_pass(const AssignArgs& a, const char* who);
 
 // one function per NT, defined in hkm_lloyd_inst.cu
-int dispatch_lloyd_nt1(const LloydParams&, const LaunchPlan&, int grid, cudaStream_t);
-int dispatch_lloyd_nt2(const LloydParams&, const LaunchPlan&, int grid, cudaStream_t);
-int dispatch_lloyd_nt3(const LloydParams&, const LaunchPlan&, int grid, cudaStream_t);
-int dispatch_lloyd_nt4(const LloydParams&, const LaunchPlan&, int grid, cudaStream_t);
-int dispatch_lloyd_nt5(const LloydParams&, const LaunchPlan&, int grid, cudaStream_t);
-int dispatch_lloyd_nt6(const LloydParams&, const LaunchPlan&, int grid, cudaStream_t);
-int dispatch_lloyd_nt7(const LloydParams&, const LaunchPlan&, int grid, cudaStream_t);
-int dispatch_lloyd_nt8(const LloydParams&, const LaunchPlan&, int grid, cudaStream_t);
+int dispatch_lloyd_nt1(const LloydParams&, const LaunchPlan&, int grid, int mode, cudaStream_t);
+int dispatch_lloyd_nt2(const LloydParams&, const LaunchPlan&, int grid, int mode, cudaStream_t);
+int dispatch_lloyd_nt3(const LloydParams&, const LaunchPlan&, int grid, int mode, cudaStream_t);
+int dispatch_lloyd_nt4(const LloydParams&, const LaunchPlan&, int grid, int mode, cudaStream_t);
+int dispatch_lloyd_nt5(const LloydParams&, const LaunchPlan&, int grid, int mode, cudaStream_t);
+int dispatch_lloyd_nt6(const LloydParams&, const LaunchPlan&, int grid, int mode, cudaStream_t);
+int dispatch_lloyd_nt7(const LloydParams&, const LaunchPlan&, int grid, int mode, cudaStream_t);
+int dispatch_lloyd_nt8(const LloydParams&, const LaunchPlan&, int grid, int mode, cudaStream_t);
 
 }  // namespace hkm

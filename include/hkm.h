@@ -162,6 +162,29 @@ HKM_API int hkm_kmpar_strip_rows(void);
 HKM_API int hkm_closest_counts(const double* X, int64_t n, int d, const double* cand, int m, int32_t* labels_work,
                                double* mind2_work, unsigned long long* counts_out, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * ClusteringEvaluator silhouette, squared Euclidean (ml/evaluation/ClusteringMetrics.scala,
+ * SURVEY 8a-10 / 8a-11).  Scratch: hkm_assign_reduce_scratch_bytes(d, k).
+ * ------------------------------------------------------------------------------------------- */
+
+/*
+ * computeClusterStats: for every cluster id G in [0, k): Y_G = sum w x, N_G = sum w, Psi_G = sum w |x|^2
+ * (|x|^2 as pow(norm(x, 2), 2), like the Scala UDF).  labels outside [0, k) are ignored.
+ * stats_out [k*d + 2k + 1]: Y (k x d), N (k), one unused slot, Psi (k).  All-reduce it across ranks
+ * before the score pass.
+ */
+HKM_API int hkm_silhouette_stats(const double* X, const int32_t* labels, const double* weights, int64_t n, int d, int k,
+                                 double* stats_out, void* scratch, size_t scratch_bytes, void* stream);
+
+/*
+ * computeSilhouetteCoefficient + overallScore: out2[0] = sum_i s_i w_i, out2[1] = sum_i w_i over this
+ * rank's rows (score = out2[0] / out2[1] after an all-reduce).  Only clusters with N_G > 0 take part;
+ * s_i = 0 when the point is alone in its cluster (N_A == w_i).  work: k*d + 2k doubles.
+ */
+HKM_API int hkm_silhouette_score(const double* X, const int32_t* labels, const double* weights, int64_t n, int d, int k,
+                                 const double* stats, double* work, double* out2, void* scratch, size_t scratch_bytes,
+                                 void* stream);
+
 #ifdef __cplusplus
 }
 #endif
