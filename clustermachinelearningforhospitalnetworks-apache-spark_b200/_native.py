@@ -18,6 +18,7 @@ EXPORTS = (
     "hkm_assign_reduce_scratch_bytes", "hkm_assign_reduce", "hkm_update_centers",
     "hkm_kmpar_scratch_bytes", "hkm_kmpar_cost_update", "hkm_kmpar_sample", "hkm_kmpar_strip_rows", "hkm_closest_counts",
     "hkm_silhouette_stats", "hkm_silhouette_score",
+    "hkm_assemble_scratch_bytes", "hkm_assemble", "hkm_moments_scratch_bytes", "hkm_moments", "hkm_column_moments", "hkm_scale_rows",
 )
 
 _lib = None
@@ -54,6 +55,14 @@ def load() -> ctypes.CDLL:
         L.hkm_kmpar_cost_update.argtypes = [vp, i64, i32, vp, i32, vp, vp, vp, sz, vp]
         L.hkm_kmpar_sample.argtypes = [vp, i64, vp, vp, i64, i32, i32, ctypes.c_int32, i32, i32, vp, vp, i32, vp, vp]
         L.hkm_closest_counts.argtypes = [vp, i64, i32, vp, i32, vp, vp, vp, vp]
+        L.hkm_assemble_scratch_bytes.restype = sz
+        L.hkm_assemble_scratch_bytes.argtypes = [i64]
+        L.hkm_assemble.argtypes = [vp, vp, vp, vp, i32, i64, vp, vp, i32, vp, vp, vp, vp, sz, vp]
+        L.hkm_moments_scratch_bytes.restype = sz
+        L.hkm_moments_scratch_bytes.argtypes = [i32]
+        L.hkm_moments.argtypes = [vp, i64, i32, vp, vp, vp, sz, vp]
+        L.hkm_column_moments.argtypes = [vp, vp, vp, vp, i32, i64, vp, vp, vp, sz, vp]
+        L.hkm_scale_rows.argtypes = [vp, vp, i64, i32, vp, vp, vp]
         L.hkm_silhouette_stats.argtypes = [vp, vp, vp, i64, i32, i32, vp, vp, sz, vp]
         L.hkm_silhouette_score.argtypes = [vp, vp, vp, i64, i32, i32, vp, vp, vp, vp, sz, vp]
         _lib = L
@@ -177,3 +186,91 @@ def silhouette_score(X, labels, k, stats, work, out2, scratch, weights=None):
         rc = load().hkm_silhouette_score(_ptr(X), _ptr(labels), _ptr(weights), n, d, k, _ptr(stats), _ptr(work), _ptr(out2),
                                          _ptr(scratch), scratch.numel() * scratch.element_size(), _stream())
     _check(rc)
+
+
+DTYPE_CODES = {torch.float64: 0, torch.float32: 1, torch.int32: 2, torch.int64: 3, torch.int16: 4, torch.int8: 5, torch.uint8: 6, torch.bool: 6}
+
+
+def _col_tables(cols, valids):
+    """HOST arrays of DEVICE pointers / dtype codes / validity kinds for the loader entry points."""
+    d = len(cols)
+    PtrArr, IntArr = ctypes.c_void_p * d, ctypes.c_int32 * d
+    ptrs, dts, vptrs, vk = PtrArr(), IntArr(), PtrArr(), IntArr()
+    for i, (c, v) in enumerate(zip(cols, valids)):
+        require_cuda(c, f"column {i}")
+        if c.dtype not in DTYPE_CODES:
+            raise HkmError(f"column {i}: unsupported dtype {c.dtype}")
+        ptrs[i], dts[i] = c.data_ptr(), DTYPE_CODES[c.dtype]
+        if v is not None:
+            require_cuda(v, f"validity {i}")
+            vptrs[i], vk[i] = v.data_ptr(), 1      # HKM_VALID_BYTES
+        else:
+            vptrs[i], vk[i] = None, 0
+    return ptrs, dts, vptrs, vk
+
+
+def assemble(cols, valids, n, shift=None, scale=None, skip_invalid=False):
+    """hkm_assemble: typed device columns -> row-major fp64 X (optionally standardised, optionally
+    compacted).  Returns (X, n_out, invalid_rows)."""
+    d = len(cols)
+    dev = cols[0].device
+    ptrs, dts, vptrs, vk = _col_tables(cols, valids)
+    X = torch.empty((n, d), dtype=torch.float64, device=dev)
+    n_out = torch.zeros(1, dtype=torch.int64, device=dev)
+    invalid = torch.zeros(1, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        sb = int(load().hkm_assemble_scratch_bytes(n)) if skip_invalid else 0
+        scratch = torch.empty((sb + 7) // 8, dtype=torch.int64, device=dev) if sb else None
+        rc = load().hkm_assemble(ptrs, dts, vptrs, vk, d, n, _ptr(shift), _ptr(scale), int(skip_invalid), _ptr(X), _ptr(n_out),
+                                 _ptr(invalid), _ptr(scratch), sb, _stream())
+    _check(rc)
+    n_keep, bad = int(n_out.item()), int(invalid.item())
+    return (X[:n_keep] if skip_invalid else X), n_keep, bad
+
+
+def count_invalid_rows(cols, valids, n) -> int:
+    """Rows holding a null or NaN (hkm_assemble in count-only mode: no matrix is written)."""
+    d = len(cols)
+    dev = cols[0].device
+    ptrs, dts, vptrs, vk = _col_tables(cols, valids)
+    n_out = torch.zeros(1, dtype=torch.int64, device=dev)
+    invalid = torch.zeros(1, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        rc = load().hkm_assemble(ptrs, dts, vptrs, vk, d, n, None, None, 0, None, _ptr(n_out), _ptr(invalid), None, 0, _stream())
+    _check(rc)
+    return int(invalid.item())
+
+
+def moments(X, pivot):
+    """hkm_moments -> tensor [d, 2] of (sum (x-K), sum (x-K)^2)."""
+    require_cuda(X, "X", torch.float64)
+    n, d = X.shape
+    out = torch.zeros(2 * d, dtype=torch.float64, device=X.device)
+    with torch.cuda.device(X.device):
+        sb = int(load().hkm_moments_scratch_bytes(d))
+        scratch = torch.empty((sb + 7) // 8, dtype=torch.int64, device=X.device)
+        rc = load().hkm_moments(_ptr(X), n, d, _ptr(pivot), _ptr(out), _ptr(scratch), sb, _stream())
+    _check(rc)
+    return out.view(d, 2)
+
+
+def column_moments(cols, valids, n, pivot):
+    d = len(cols)
+    dev = cols[0].device
+    ptrs, dts, vptrs, vk = _col_tables(cols, valids)
+    out = torch.zeros(2 * d, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        sb = int(load().hkm_moments_scratch_bytes(d))
+        scratch = torch.empty((sb + 7) // 8, dtype=torch.int64, device=dev)
+        rc = load().hkm_column_moments(ptrs, dts, vptrs, vk, d, n, _ptr(pivot), _ptr(out), _ptr(scratch), sb, _stream())
+    _check(rc)
+    return out.view(d, 2)
+
+
+def scale_rows(X, shift, scale):
+    require_cuda(X, "X", torch.float64)
+    out = torch.empty_like(X)
+    with torch.cuda.device(X.device):
+        rc = load().hkm_scale_rows(_ptr(X), _ptr(out), X.shape[0], X.shape[1], _ptr(shift), _ptr(scale), _stream())
+    _check(rc)
+    return out

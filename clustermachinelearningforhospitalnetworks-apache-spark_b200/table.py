@@ -38,6 +38,40 @@ class DeviceMatrix:
         return self.X.detach().cpu().numpy()
 
 
+class AssembledColumn:
+    """Lazy VectorAssembler output: references to the typed source columns (already on the device)
+    plus an optional (shift, scale) from StandardScalerModel.transform.  Materialised by ONE
+    hkm_assemble launch when a consumer needs the row-major matrix, so assemble -> scale -> fit writes
+    the standardised matrix to HBM exactly once."""
+
+    def __init__(self, cols, valids, names, n, shift=None, scale=None):
+        self.cols, self.valids, self.names, self.n = cols, valids, names, n
+        self.shift, self.scale = shift, scale
+        self._mat = None
+
+    @property
+    def shape(self):
+        return (self.n, len(self.cols))
+
+    def __len__(self):
+        return self.n
+
+    def with_scaling(self, shift, scale) -> "AssembledColumn":
+        if self.shift is not None or self.scale is not None:
+            raise ValueError("column is already scaled; materialise it first")
+        return AssembledColumn(self.cols, self.valids, self.names, self.n, shift, scale)
+
+    def materialize(self) -> "DeviceMatrix":
+        if self._mat is None:
+            from . import _native as N
+            X, _, _ = N.assemble(self.cols, self.valids, self.n, self.shift, self.scale, skip_invalid=False)
+            self._mat = DeviceMatrix(X)
+        return self._mat
+
+    def numpy(self):
+        return self.materialize().numpy()
+
+
 class Column:
     """One scalar column: values plus an optional validity mask (True = present)."""
 
@@ -52,7 +86,7 @@ class Column:
 
 
 def _as_column(v) -> Any:
-    if isinstance(v, (Column, DeviceMatrix)):
+    if isinstance(v, (Column, DeviceMatrix, AssembledColumn)):
         return v
     try:
         import pyarrow as pa
@@ -87,7 +121,7 @@ def _as_column(v) -> Any:
 
 
 def _nrows(c) -> int:
-    if isinstance(c, DeviceMatrix):
+    if isinstance(c, (DeviceMatrix, AssembledColumn)):
         return len(c)
     if isinstance(c, Column):
         return len(c.values)
@@ -96,6 +130,8 @@ def _nrows(c) -> int:
 
 def _take(c, mask_np: np.ndarray):
     """Row filter by boolean mask (host mask; device columns get a device copy of it)."""
+    if isinstance(c, AssembledColumn):
+        c = c.materialize()
     if isinstance(c, DeviceMatrix):
         m = torch.from_numpy(mask_np).to(c.X.device)
         return DeviceMatrix(c.X[m].contiguous())
@@ -230,7 +266,7 @@ class Table:
 
     def to_numpy(self, name: str) -> np.ndarray:
         c = self[name]
-        if isinstance(c, DeviceMatrix):
+        if isinstance(c, (DeviceMatrix, AssembledColumn)):
             return c.numpy()
         if isinstance(c, Column):
             v = c.values.cpu().numpy() if isinstance(c.values, torch.Tensor) else np.asarray(c.values)
@@ -260,6 +296,8 @@ def features_to_device(col, device) -> DeviceMatrix:
     """A 'features' column in any accepted form -> DeviceMatrix (H2D copy if it lives on host)."""
     if isinstance(col, DeviceMatrix):
         return col
+    if isinstance(col, AssembledColumn):
+        return col.materialize()
     if isinstance(col, Column):
         raise TypeError("features column must be a vector column (2-D array or VectorAssembler output), got a scalar column")
     if isinstance(col, torch.Tensor):

@@ -185,6 +185,53 @@ HKM_API int hkm_silhouette_score(const double* X, const int32_t* labels, const d
                                  const double* stats, double* work, double* out2, void* scratch, size_t scratch_bytes,
                                  void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Loader: VectorAssembler + StandardScaler (ml/feature/{VectorAssembler,StandardScaler}.scala,
+ * SURVEY 8a-1 / 8a-2).  Column pointer tables (`*_host`) are HOST arrays of DEVICE pointers.
+ * ------------------------------------------------------------------------------------------- */
+#define HKM_DTYPE_F64 0
+#define HKM_DTYPE_F32 1
+#define HKM_DTYPE_I32 2
+#define HKM_DTYPE_I64 3
+#define HKM_DTYPE_I16 4
+#define HKM_DTYPE_I8 5
+#define HKM_DTYPE_U8 6 /* also bool */
+#define HKM_VALID_NONE 0
+#define HKM_VALID_BYTES 1 /* one byte per row, non-zero = present */
+#define HKM_VALID_BITS 2  /* Arrow validity bitmap, LSB first */
+
+HKM_API size_t hkm_assemble_scratch_bytes(int64_t n);
+
+/*
+ * VectorAssembler.transform (ref:L134-136) with StandardScalerModel.transform fused in:
+ * X_out[r, c] = (col_c[r] - shift[c]) * scale[c]  (shift / scale nullable), row-major fp64, written once.
+ * A row is invalid when any column is null or NaN.  skip_invalid = 0: every row is written (nulls as
+ * NaN) and *invalid_count tells the caller whether handleInvalid='error' must raise;
+ * skip_invalid = 1 (handleInvalid='skip' / DataFrame.na.drop, ref:L128): valid rows are compacted in
+ * order; *n_out = rows written.  scratch (hkm_assemble_scratch_bytes(n)) is needed for skip only.
+ * X_out = NULL with skip_invalid = 0 only counts the invalid rows (nothing is written).
+ */
+HKM_API int hkm_assemble(const void* const* cols_host, const int32_t* dtypes_host, const void* const* valid_host,
+                         const int32_t* vkind_host, int d, int64_t n, const double* shift, const double* scale,
+                         int skip_invalid, double* X_out, int64_t* n_out, unsigned long long* invalid_count,
+                         void* scratch, size_t scratch_bytes, void* stream);
+
+/*
+ * Moments for StandardScaler.fit (Summarizer mean/std): out2d[2c] = sum_r (x_rc - pivot_c),
+ * out2d[2c+1] = sum_r (x_rc - pivot_c)^2.  The pivot (any row of the data) keeps the sums free of
+ * cancellation; mean = pivot + s1/n, var = (s2 - s1^2/n)/(n-1).  All-reduce out2d across ranks.
+ */
+HKM_API size_t hkm_moments_scratch_bytes(int d);
+HKM_API int hkm_moments(const double* X, int64_t n, int d, const double* pivot, double* out2d, void* scratch,
+                        size_t scratch_bytes, void* stream);
+HKM_API int hkm_column_moments(const void* const* cols_host, const int32_t* dtypes_host, const void* const* valid_host,
+                               const int32_t* vkind_host, int d, int64_t n, const double* pivot, double* out2d,
+                               void* scratch, size_t scratch_bytes, void* stream);
+
+/* StandardScalerModel.transform on an existing matrix: out = (in - shift) * scale (in place allowed). */
+HKM_API int hkm_scale_rows(const double* X_in, double* X_out, int64_t n, int d, const double* shift, const double* scale,
+                           void* stream);
+
 #ifdef __cplusplus
 }
 #endif
