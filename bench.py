@@ -222,7 +222,7 @@ def main():
             ev[1].record()
         if world > 1:
             dist.all_reduce(partial)
-        N.update_centers(partial, C, 0.0, state)   # tol = 0: every step does full work (rows*iter well defined)
+        N.update_centers(partial, C, -1.0, state)  # tol < 0: never "converged", every step does full work (rows*iter well defined)
 
     def barrier():
         if world > 1:
@@ -299,7 +299,7 @@ def main():
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": args.workload, "description": desc, "rows_per_gpu": n, "d": d, "k": k,
                    "cache": f"inputs ({alg_bytes / 1e9:.2f} GB per GPU) are larger than the 126 MB L2; no flush needed",
-                   "step": "hkm_assign_reduce (xnorm2 REUSE) + allreduce(k*(d+1)+1 f64) + hkm_update_centers, tol=0"},
+                   "step": "hkm_assign_reduce (xnorm2 REUSE) + allreduce(k*(d+1)+1 f64) + hkm_update_centers, convergence test off"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})", "kernel": "lloyd_pass_kernel",
                      "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": alg_bytes, "traffic": ncu_traffic(args.workload)},

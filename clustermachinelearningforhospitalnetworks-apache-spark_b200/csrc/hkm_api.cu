@@ -101,7 +101,8 @@ int assign_pass(const AssignArgs& a, const char* who) {
   p.cta_partials = a.scratch ? reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(a.scratch) + 256) : nullptr;
   p.stages = pl.stages; p.ks = (d + 3) / 4;
   const int grid = sm_count() * pl.ctas_per_sm;
-  return dispatch_lloyd(p, pl, grid, a.mode, reinterpret_cast<cudaStream_t>(a.stream));
+  const int mode = (a.mode == 0 && a.weights != nullptr) ? 3 : a.mode;   // weights are a compile-time property of the Lloyd kernels
+  return dispatch_lloyd(p, pl, grid, mode, reinterpret_cast<cudaStream_t>(a.stream));
 }
 
 }  // namespace hkm
@@ -135,7 +136,7 @@ int hkm_assign_reduce(const double* X, int64_t n, int d, const double* C, int k,
 
 int hkm_update_centers(const double* partial, int k, int d, double* C_inout, double tol, hkm_lloyd_state* state, void* stream) {
   if (partial == nullptr || C_inout == nullptr || state == nullptr || k < 1 || k > hkm_max_k() || d < 1) { set_error("hkm_update_centers: bad arguments"); return HKM_ERR_INVALID; }
-  update_centers_kernel<<<1, 64, 0, reinterpret_cast<cudaStream_t>(stream)>>>(partial, k, d, C_inout, tol * tol, state);
+  update_centers_kernel<<<1, 64, 0, reinterpret_cast<cudaStream_t>(stream)>>>(partial, k, d, C_inout, tol < 0 ? -1.0 : tol * tol, state);
   HKM_CUDA_TRY(cudaGetLastError());
   return HKM_OK;
 }

@@ -85,36 +85,45 @@ __host__ __device__ inline SmemLayout smem_layout(int d, int k_pad, int stages) 
 // KS_T == 0: B-fragments are re-read from shared memory, runtime k-step count.
 // NT = ceil(k/8) score column tiles == clusters owned per warp in phase 2.
 // LPR = lanes per row in phase 2 (8/16/32), FPL = features per lane (d > 32).
-// MODE 0: Lloyd / predict pass.  MODE 1: silhouette cluster statistics (labels given: per-cluster
-// sum w*x, sum w, sum w*|x|^2).  MODE 2: silhouette score pass (labels + statistics given).
+// MODE 0: Lloyd / predict pass, unit weights.  MODE 3: the same with per-row weights.
+// MODE 1: silhouette cluster statistics (labels given: per-cluster sum w*x, sum w, sum w*|x|^2).
+// MODE 2: silhouette score pass (labels + statistics given).
+//
+// All hot-loop shared-memory traffic goes through 32-bit shared addresses (lds_*/sts_* helpers).
 template <int KS_T, int NT, int LPR, int FPL, int MAXREG, int MODE = 0>
 __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kernel(const LloydParams p) {
   if (p.skip != nullptr && *p.skip != 0) return;
 
   extern __shared__ __align__(128) unsigned char smem[];
   const int d = p.d, k = p.k;
-  const int k_pad = NT * 8;
+  constexpr int k_pad = NT * 8;
   const int KS = KS_T > 0 ? KS_T : p.ks;
   const SmemLayout L = smem_layout(d, k_pad, p.stages);
-  int* labels_s = reinterpret_cast<int*>(smem + L.labels_off);
-  double* mind2_s = reinterpret_cast<double*>(smem + L.mind2_off);
   double* Cs = reinterpret_cast<double*>(smem + L.cs_off);
   double* cn_s = reinterpret_cast<double*>(smem + L.cn_off);
   double* red_s = reinterpret_cast<double*>(smem + L.red_off);
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + L.bar_off);
-  double* w_s = reinterpret_cast<double*>(smem + L.w_off);
+
+  const uint32_t sb = smem_u32(smem);                 // shared-window address of the dynamic smem base
+  const uint32_t a_x = sb + L.x_off, a_labels = sb + L.labels_off, a_mind2 = sb + L.mind2_off, a_w = sb + L.w_off;
+  const uint32_t a_full = sb + L.bar_off, a_zero = sb + L.zero_off;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int stages = p.stages;
   const int csld = cs_ld(d);
-  const int cstride = chunk_stride_bytes(d);
-  const int sbytes = stage_bytes(d);
+  const uint32_t cstride = (uint32_t)chunk_stride_bytes(d);
+  const uint32_t sbytes = (uint32_t)stage_bytes(d);
+  const uint32_t row_bytes = (uint32_t)d * 8u;
 
   const int64_t full_tiles = p.n / kTileRows;
   const int tail_rows = (int)(p.n - full_tiles * kTileRows);
 
+  constexpr bool WEIGHTED = MODE == 3;
+  // weights are a compile-time fact on the Lloyd paths; the silhouette passes take them at run time
+  const bool has_w = WEIGHTED || ((MODE == 1 || MODE == 2) && p.w != nullptr);
+  constexpr bool EXTRAS = MODE == 1 || MODE == 3;   // phase 2 needs per-row scalars (weight, |x|^2) next to the row
+
   if (tid == 0) {
-    for (int s = 0; s < stages; ++s) mbar_init(&full[s], 1);
+    for (int s = 0; s < stages; ++s) mbar_init(reinterpret_cast<uint64_t*>(smem + L.bar_off) + s, 1);
     mbar_fence_init();
   }
   // stage centres: Cs[j][f] (zero padded), cn_s[j] = -0.5|c_j|^2 (-inf for padding)
@@ -139,26 +148,26 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
   }
   __syncthreads();
 
-  // ---- TMA producer (lane 0 of warp 0): fetch local tile `i` (global tile blockIdx.x + i*gridDim.x)
-  // into stage i % stages.  A stage is refilled right after the CTA barrier of the NEXT tile,
-  // which every warp reaches only after it has finished reading the stage -- so no "empty"
-  // mbarriers are needed.
-  const int64_t my_tiles = full_tiles > (int64_t)blockIdx.x ? (full_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
-  auto issue_tile = [&](int64_t i) {
-    const int s = (int)(i % stages);
-    const uint32_t cbytes = (uint32_t)(kChunkRows * d * 8);
-    const int64_t t = (int64_t)blockIdx.x + i * gridDim.x;
-    mbar_expect_tx(&full[s], cbytes * kChunks);
-    const unsigned char* src = reinterpret_cast<const unsigned char*>(p.X) + (size_t)t * kTileRows * d * 8;
-    unsigned char* dst = smem + L.x_off + (size_t)s * sbytes;
+  // ---- TMA producer (thread 0): local tile i of this CTA is global tile blockIdx.x + i*gridDim.x and lands in
+  // stage i % stages.  A stage is refilled right after the CTA barrier of the NEXT tile, which every warp reaches
+  // only after it has finished reading the stage -- so no "empty" mbarriers are needed.
+  const int my_tiles = full_tiles > (int64_t)blockIdx.x ? (int)((full_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
+  const uint32_t cbytes = (uint32_t)kChunkRows * row_bytes;
+  const size_t tile_gbytes = (size_t)kTileRows * row_bytes;
+  const unsigned char* src_next = reinterpret_cast<const unsigned char*>(p.X) + (size_t)blockIdx.x * tile_gbytes;  // next tile to fetch
+  const size_t src_step = (size_t)gridDim.x * tile_gbytes;
+  int next_fill = 0;                                   // local index of the next tile to fetch
+  auto issue_tile = [&](int s) {                       // fetch tile `next_fill` into stage s
+    const uint32_t bar = a_full + 8u * (uint32_t)s, dst = a_x + (uint32_t)s * sbytes;
+    mbar_expect_tx_a(bar, cbytes * kChunks);
 #pragma unroll
-    for (int c = 0; c < kChunks; ++c) bulk_g2s(dst + c * cstride, src + (size_t)c * cbytes, cbytes, &full[s]);
+    for (int c = 0; c < kChunks; ++c) bulk_g2s_a(dst + c * cstride, src_next + (size_t)c * cbytes, cbytes, bar);
+    src_next += src_step; ++next_fill;
   };
   if (tid == 0) {
-    for (int64_t i = 0; i < my_tiles && i < stages; ++i) issue_tile(i);
+    for (int s = 0; s < stages && next_fill < my_tiles; ++s) issue_tile(s);
   }
 
-  // ===================================================================== compute warps
   const int r = lane >> 2, q = lane & 3;
 
   // centre B-fragments: lane (n = r, q) holds C[8*nt + n][4*s + q]
@@ -172,43 +181,42 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
   double cinit[NT][2];
 #pragma unroll
   for (int nt = 0; nt < NT; ++nt) { cinit[nt][0] = cn_s[8 * nt + 2 * q]; cinit[nt][1] = cn_s[8 * nt + 2 * q + 1]; }
+  const uint32_t a_cb = sb + L.cs_off + (uint32_t)((r * csld + q) * 8);   // KS_T == 0: B fragments re-read from smem
+  const uint32_t a_nn = sb + L.cn_off + (uint32_t)k_pad * 8u;             // MODE 2: cluster weight sums
 
   // phase-2 register accumulators: cluster warp + 8*m, features (lane % LPR) + 32*e
   double acc_a[NT][FPL], acc_b[NT][FPL];
   double wacc[NT];        // weighted runs: per-lane partial weight sums
+  double psi[NT];         // MODE 1: sum of w*|x|^2 per owned cluster (lane fl == 0 only)
   unsigned cnt[NT];       // unweighted runs: rows per owned cluster (warp-uniform)
 #pragma unroll
   for (int m = 0; m < NT; ++m) {
-    cnt[m] = 0; wacc[m] = 0;
+    cnt[m] = 0; wacc[m] = 0; psi[m] = 0;
 #pragma unroll
     for (int e = 0; e < FPL; ++e) { acc_a[m][e] = 0; acc_b[m][e] = 0; }
   }
   double cost = 0;
+  double xxs = 0;  // xx_mode 1: sum of w*|x|^2 over this thread's rows;  MODE 2: sum of w
+  const int xx_mode = p.xx_mode;
   const int sub = lane / LPR, fl = lane % LPR;
   constexpr int RPS = 32 / LPR;  // rows handled per warp load step
-  const bool has_w = p.w != nullptr;
-  const bool extras = has_w || MODE == 1;   // phase 2 needs per-row scalars (weight, |x|^2) next to the row itself
-  double psi[NT];                            // MODE 1: sum of w*|x|^2 per owned cluster (lane fl == 0 only)
-#pragma unroll
-  for (int m = 0; m < NT; ++m) psi[m] = 0;
-  uint32_t* list_w = reinterpret_cast<uint32_t*>(smem + L.list_off) + warp * list_entries(k_pad);
+  const uint32_t a_list = sb + L.list_off + (uint32_t)(warp * list_entries(k_pad)) * 4u;
   const unsigned lt_mask = (1u << lane) - 1u;
-  const int row_bytes = d * 8;
   // byte offset (from the stage base) of tile row `lane`; row lane+32g adds g*group_stride
-  const uint32_t off_lane = (uint32_t)(lane * row_bytes + (lane >> 4) * kChunkPad);
-  const uint32_t group_stride = (uint32_t)(32 * row_bytes + 2 * kChunkPad);
-  const unsigned char* smem_lane = smem + fl * 8;
+  const uint32_t off_lane = (uint32_t)lane * row_bytes + (uint32_t)(lane >> 4) * kChunkPad;
+  const uint32_t group_stride = 32u * row_bytes + 2u * kChunkPad;
+  const uint32_t fl8 = (uint32_t)fl * 8u;
+  // A-fragment base of this lane inside a stage: chunk r, feature q; sub-tile i adds i*row_bytes
+  const uint32_t a_frag = (uint32_t)r * cstride + (uint32_t)q * 8u;
+  const int i0 = warp, i1 = warp + 8;
+  const int t0 = r * kChunkRows + i0, t1 = r * kChunkRows + i1;   // tile rows of this lane's two MMA rows
 
-  const int xx_mode = p.xx_mode;
-  double xxs = 0;  // mode 1: sum of w*|x|^2 over this thread's rows
-
-  auto process_tile = [&](auto need_xx_tag, const unsigned char* xs, int rows_valid, int64_t row0, int buf, int64_t refill) {
+  auto process_tile = [&](auto need_xx_tag, const uint32_t xs, const int rows_valid, const int64_t row0, const int buf, const int refill_stage) {
     constexpr bool NEED_XX = decltype(need_xx_tag)::value;
+    const uint32_t lab_b = a_labels + (uint32_t)buf * (kTileRows * 4), m2_b = a_mind2 + (uint32_t)buf * (kTileRows * 8),
+                   w_b = a_w + (uint32_t)buf * (kTileRows * 8);
     // ---------------- phase 1: two MMA sub-tiles per warp (rows i0 / i1 of every chunk)
-    const int i0 = warp, i1 = warp + 8;
-    const double* xa = reinterpret_cast<const double*>(xs + r * cstride) + q;
-    const double* xa0 = xa + i0 * d;
-    const double* xa1 = xa + i1 * d;
+    const uint32_t xa0 = xs + a_frag + (uint32_t)i0 * row_bytes, xa1 = xs + a_frag + (uint32_t)i1 * row_bytes;
     double s0[NT][2], s1[NT][2];
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) { s0[nt][0] = cinit[nt][0]; s0[nt][1] = cinit[nt][1]; s1[nt][0] = cinit[nt][0]; s1[nt][1] = cinit[nt][1]; }
@@ -217,27 +225,25 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
 #pragma unroll
       for (int s = 0; s < (KS_T > 0 ? KS_T : 1); ++s) {
         const bool ok = (s < KS_T - 1) || (4 * s + q < d);
-        double a0 = ok ? xa0[4 * s] : 0.0, a1 = ok ? xa1[4 * s] : 0.0;
+        const double a0 = ok ? lds_f64(xa0 + 32u * s) : 0.0, a1 = ok ? lds_f64(xa1 + 32u * s) : 0.0;
         if (NEED_XX) { xx0 = fma(a0, a0, xx0); xx1 = fma(a1, a1, xx1); }
 #pragma unroll
-        for (int nt = 0; nt < NT; ++nt) { if (MODE != 1) { dmma884(s0[nt][0], s0[nt][1], a0, breg[s * NT + nt]); dmma884(s1[nt][0], s1[nt][1], a1, breg[s * NT + nt]); } }
+        for (int nt = 0; nt < NT; ++nt) { if (MODE != 1) dmma1684(s0[nt][0], s0[nt][1], s1[nt][0], s1[nt][1], a0, a1, breg[s * NT + nt]); }
       }
     } else {
-      const double* cb = Cs + r * csld + q;
       for (int s = 0; s < KS; ++s) {
         const bool ok = 4 * s + q < d;
-        double a0 = ok ? xa0[4 * s] : 0.0, a1 = ok ? xa1[4 * s] : 0.0;
+        const double a0 = ok ? lds_f64(xa0 + 32u * s) : 0.0, a1 = ok ? lds_f64(xa1 + 32u * s) : 0.0;
         if (NEED_XX) { xx0 = fma(a0, a0, xx0); xx1 = fma(a1, a1, xx1); }
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt) {
           if (MODE != 1) {
-            double b = cb[(8 * nt) * csld + 4 * s];
-            dmma884(s0[nt][0], s0[nt][1], a0, b); dmma884(s1[nt][0], s1[nt][1], a1, b);
+            const double b = lds_f64(a_cb + (uint32_t)((8 * nt) * csld * 8) + 32u * s);
+            dmma1684(s0[nt][0], s0[nt][1], s1[nt][0], s1[nt][1], a0, a1, b);
           }
         }
       }
     }
-    const int t0 = r * kChunkRows + i0, t1 = r * kChunkRows + i1;
     if constexpr (MODE == 1) {
       // ---- silhouette statistics: labels are given; phase 1 only supplies |x|^2 per row
 #pragma unroll
@@ -247,12 +253,12 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
         int l0 = v0 ? p.labels_in[row0 + t0] : -1, l1 = v1 ? p.labels_in[row0 + t1] : -1;
         if (l0 >= k) l0 = -1;
         if (l1 >= k) l1 = -1;
-        labels_s[buf * kTileRows + t0] = l0; labels_s[buf * kTileRows + t1] = l1;
-        w_s[buf * kTileRows + t0] = (v0 && has_w) ? p.w[row0 + t0] : 1.0;
-        w_s[buf * kTileRows + t1] = (v1 && has_w) ? p.w[row0 + t1] : 1.0;
+        sts_u32(lab_b + 4u * t0, (uint32_t)l0); sts_u32(lab_b + 4u * t1, (uint32_t)l1);
+        sts_f64(w_b + 8u * t0, (v0 && has_w) ? p.w[row0 + t0] : 1.0);
+        sts_f64(w_b + 8u * t1, (v1 && has_w) ? p.w[row0 + t1] : 1.0);
         // ClusteringMetrics: squaredNorm = math.pow(Vectors.norm(features, 2.0), 2.0)
         const double n0 = sqrt(xx0), n1 = sqrt(xx1);
-        mind2_s[buf * kTileRows + t0] = n0 * n0; mind2_s[buf * kTileRows + t1] = n1 * n1;
+        sts_f64(m2_b + 8u * t0, n0 * n0); sts_f64(m2_b + 8u * t1, n1 * n1);
       }
     } else if constexpr (MODE == 2) {
       // ---- silhouette score (ClusteringMetrics.pointSilhouetteCoefficient), one value per row
@@ -281,7 +287,7 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
           if (!valid || a < 0) return;
           const double wv = has_w ? p.w[row] : 1.0;
           const double nrm = sqrt(xx), sn = nrm * nrm;
-          const double NA = cn_s[k_pad + a];
+          const double NA = lds_f64(a_nn + 8u * a);
           double sil = 0.0;
           if (NA != wv) {                                  // single-element clusters have silhouette 0
             const double cur = fma(-2.0, own, sn) * NA / (NA - wv);
@@ -296,80 +302,77 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
     } else {
       // argmax over this lane's columns (ascending index), then across the 4 lanes of the row
       double b0 = s0[0][0], b1 = s1[0][0]; int j0 = 2 * q, j1 = 2 * q;
-  #pragma unroll
+#pragma unroll
       for (int nt = 0; nt < NT; ++nt)
-  #pragma unroll
+#pragma unroll
         for (int e = 0; e < 2; ++e) {
           if (nt == 0 && e == 0) continue;
           const int j = 8 * nt + 2 * q + e;
           if (s0[nt][e] > b0) { b0 = s0[nt][e]; j0 = j; }
           if (s1[nt][e] > b1) { b1 = s1[nt][e]; j1 = j; }
         }
-  #pragma unroll
+#pragma unroll
       for (int msk = 1; msk <= 2; msk <<= 1) {
-        double o0 = shfl_xor_d(b0, msk), o1 = shfl_xor_d(b1, msk);
-        int oj0 = __shfl_xor_sync(0xffffffffu, j0, msk), oj1 = __shfl_xor_sync(0xffffffffu, j1, msk);
+        const double o0 = shfl_xor_d(b0, msk), o1 = shfl_xor_d(b1, msk);
+        const int oj0 = __shfl_xor_sync(0xffffffffu, j0, msk), oj1 = __shfl_xor_sync(0xffffffffu, j1, msk);
         if (o0 > b0 || (o0 == b0 && oj0 < j0)) { b0 = o0; j0 = oj0; }
         if (o1 > b1 || (o1 == b1 && oj1 < j1)) { b1 = o1; j1 = oj1; }
         if (NEED_XX) { xx0 += shfl_xor_d(xx0, msk); xx1 += shfl_xor_d(xx1, msk); }
       }
       if (q == 0) {
         const bool v0 = t0 < rows_valid, v1 = t1 < rows_valid;
-        // per-row term of the cost: the clamped distance, or (mode 2) the score itself, folded
+        // per-row term of the cost: the clamped distance, or (xx_mode 2) the score itself, folded
         // against the stored sum of |x|^2 by the last CTA
         double d0 = b0, d1 = b1;
-        if (NEED_XX) {
-          d0 = fmax(fma(-2.0, b0, xx0), 0.0); d1 = fmax(fma(-2.0, b1, xx1), 0.0);
-        }
+        if (NEED_XX) { d0 = fmax(fma(-2.0, b0, xx0), 0.0); d1 = fmax(fma(-2.0, b1, xx1), 0.0); }
         const double c0 = (NEED_XX && xx_mode == 2) ? b0 : d0, c1 = (NEED_XX && xx_mode == 2) ? b1 : d1;
         if (p.out_mode != 0) {
           // min-merge mode: the output threads below own the cost
-        } else if (has_w) {
+        } else if (WEIGHTED) {
           const double w0 = v0 ? p.w[row0 + t0] : 0.0, w1 = v1 ? p.w[row0 + t1] : 0.0;
           cost = fma(c0, w0, cost); cost = fma(c1, w1, cost);
           if (NEED_XX && xx_mode == 1) { xxs = fma(xx0, w0, xxs); xxs = fma(xx1, w1, xxs); }
-          w_s[buf * kTileRows + t0] = w0; w_s[buf * kTileRows + t1] = w1;
+          sts_f64(w_b + 8u * t0, w0); sts_f64(w_b + 8u * t1, w1);
         } else {
           if (v0) cost += c0;
           if (v1) cost += c1;
           if (NEED_XX && xx_mode == 1) { if (v0) xxs += xx0; if (v1) xxs += xx1; }
         }
-        labels_s[buf * kTileRows + t0] = v0 ? j0 : -1;
-        labels_s[buf * kTileRows + t1] = v1 ? j1 : -1;
-        if (NEED_XX && p.mind2_out != nullptr) { mind2_s[buf * kTileRows + t0] = d0; mind2_s[buf * kTileRows + t1] = d1; }
+        sts_u32(lab_b + 4u * t0, (uint32_t)(v0 ? j0 : -1));
+        sts_u32(lab_b + 4u * t1, (uint32_t)(v1 ? j1 : -1));
+        if (NEED_XX && p.mind2_out != nullptr) { sts_f64(m2_b + 8u * t0, d0); sts_f64(m2_b + 8u * t1, d1); }
       }
     }
     __syncthreads();
-    if (tid == 0 && refill >= 0) issue_tile(refill);  // the previous tile's stage is free now
+    if (tid == 0 && refill_stage >= 0 && next_fill < my_tiles) issue_tile(refill_stage);  // the previous tile's stage is free now
 
     // ---------------- outputs (coalesced from smem)
-    if (MODE != 0) {
+    if (MODE != 0 && MODE != 3) {
     } else if (p.out_mode == 0) {
-      if (p.labels_out != nullptr && tid < kTileRows && tid < rows_valid) p.labels_out[row0 + tid] = labels_s[buf * kTileRows + tid];
+      if (p.labels_out != nullptr && tid < kTileRows && tid < rows_valid) p.labels_out[row0 + tid] = (int)lds_u32(lab_b + 4u * tid);
       if (p.mind2_out != nullptr && tid >= kTileRows && (tid - kTileRows) < rows_valid)
-        p.mind2_out[row0 + tid - kTileRows] = mind2_s[buf * kTileRows + tid - kTileRows];
+        p.mind2_out[row0 + tid - kTileRows] = lds_f64(m2_b + 8u * (tid - kTileRows));
     } else if (tid < kTileRows && tid < rows_valid) {
       // running minimum over successive centre chunks (k-means|| cost update, candidate weights):
       // strict '<' keeps the earlier (lower-index) centre on ties, as findClosest does
-      const double nv = mind2_s[buf * kTileRows + tid], old = p.mind2_out[row0 + tid];
+      const double nv = lds_f64(m2_b + 8u * tid), old = p.mind2_out[row0 + tid];
       if (nv < old) {
         p.mind2_out[row0 + tid] = nv;
-        if (p.labels_out != nullptr) p.labels_out[row0 + tid] = labels_s[buf * kTileRows + tid] + p.label_base;
+        if (p.labels_out != nullptr) p.labels_out[row0 + tid] = (int)lds_u32(lab_b + 4u * tid) + p.label_base;
         cost += nv;
       } else cost += old;
     }
 
     // ---------------- phase 2: owner warps gather their clusters' rows
-    // Each owner warp compacts the smem byte offsets of its clusters' rows into a private
-    // list (ballot + prefix popcount, one predicated store per group), pads every segment to
-    // a multiple of 4 with the offset of an all-zero row, then streams the list: one
-    // broadcast LDS.128 of four offsets, four row loads, four adds -- no per-row bit
-    // twiddling, no predication, fixed order.
+    // Each owner warp compacts the shared addresses of its clusters' rows into a private list (ballot + prefix
+    // popcount, one predicated store per 32 rows), pads every segment to a multiple of 4 with the address of an
+    // all-zero row, then streams the list: one broadcast LDS.128 of four addresses, four row loads, four adds --
+    // no per-row bit twiddling, no predication, fixed order.
     if (p.do_reduce == 1 && MODE != 2) {
-      const uint32_t stage_off = (uint32_t)(xs - smem);
       int lab[kTileRows / 32];
 #pragma unroll
-      for (int g = 0; g < kTileRows / 32; ++g) lab[g] = labels_s[buf * kTileRows + g * 32 + lane];
+      for (int g = 0; g < kTileRows / 32; ++g) lab[g] = (int)lds_u32(lab_b + 4u * (g * 32 + lane));
+      const uint32_t e_lane = xs + off_lane;   // shared address of tile row `lane`
       unsigned seg_begin[NT], seg_cnt[NT];
       unsigned pos = 0;
 #pragma unroll
@@ -380,60 +383,57 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
         for (int g = 0; g < kTileRows / 32; ++g) {
           const bool mine = lab[g] == j;
           const unsigned mask = __ballot_sync(0xffffffffu, mine);
-          if (mine) {
-            uint32_t e = stage_off + off_lane + g * group_stride;
-            if (extras) { e |= (uint32_t)(g * 32 + lane) << 20; }
-            list_w[pos + __popc(mask & lt_mask)] = e;
-          }
+          uint32_t e = e_lane + g * group_stride;
+          if (EXTRAS) e |= (uint32_t)(g * 32 + lane) << 20;   // shared addresses stay below 2^20
+          sts_u32_if(a_list + 4u * (pos + __popc(mask & lt_mask)), e, mine);
           pos += __popc(mask);
         }
         seg_cnt[m] = pos - seg_begin[m];
-        if (lane < (int)((4u - (pos & 3u)) & 3u)) list_w[pos + lane] = (uint32_t)L.zero_off;  // padding -> zero row
+        sts_u32_if(a_list + 4u * (pos + lane), a_zero, lane < (int)((4u - (pos & 3u)) & 3u));  // padding -> zero row
         pos = (pos + 3) & ~3u;
       }
       __syncwarp();
 #pragma unroll
       for (int m = 0; m < NT; ++m) {
         cnt[m] += seg_cnt[m];
-        const uint32_t* lp = list_w + seg_begin[m];
+        const uint32_t lp = a_list + 4u * seg_begin[m];
         const unsigned nquad = (seg_cnt[m] + 3) >> 2;
-        if (!extras) {
+        if (!EXTRAS) {
 #pragma unroll 2
           for (unsigned i = 0; i < nquad; ++i) {
-            const uint4 o = *reinterpret_cast<const uint4*>(lp + 4 * i);
+            const uint4 o = lds_v4(lp + 16u * i);
             const uint32_t oo[4] = {o.x, o.y, o.z, o.w};
 #pragma unroll
             for (int u = 0; u < 4 / RPS; ++u) {
               uint32_t osel = oo[u * RPS];
 #pragma unroll
               for (int z = 1; z < RPS; ++z) osel = (sub == z) ? oo[u * RPS + z] : osel;
-              const double* xr = reinterpret_cast<const double*>(smem_lane + osel);
 #pragma unroll
               for (int e = 0; e < FPL; ++e) {
-                const double v = xr[32 * e];  // lanes past d read neighbouring smem into accumulators that are never stored
+                const double v = lds_f64(osel + fl8 + 256u * e);  // lanes past d read neighbouring smem into accumulators that are never stored
                 if (u & 1) acc_b[m][e] += v; else acc_a[m][e] += v;
               }
             }
           }
         } else {
           for (unsigned i = 0; i < nquad; ++i) {
-            const uint4 o = *reinterpret_cast<const uint4*>(lp + 4 * i);
+            const uint4 o = lds_v4(lp + 16u * i);
             const uint32_t oo[4] = {o.x, o.y, o.z, o.w};
 #pragma unroll
             for (int u = 0; u < 4 / RPS; ++u) {
               uint32_t osel = oo[u * RPS];
 #pragma unroll
               for (int z = 1; z < RPS; ++z) osel = (sub == z) ? oo[u * RPS + z] : osel;
-              const double* xr = reinterpret_cast<const double*>(smem_lane + (osel & 0xFFFFFu));
-              const bool pad = (osel & 0xFFFFFu) == (uint32_t)L.zero_off;
-              const double wv = pad ? 0.0 : w_s[buf * kTileRows + (osel >> 20)];
+              const uint32_t addr = osel & 0xFFFFFu, trow = osel >> 20;
+              const bool pad = addr == a_zero;
+              const double wv = pad ? 0.0 : lds_f64(w_b + 8u * trow);
               if (fl == 0) {
                 wacc[m] += wv;
-                if (MODE == 1) psi[m] = fma(wv, pad ? 0.0 : mind2_s[buf * kTileRows + (osel >> 20)], psi[m]);
+                if (MODE == 1) psi[m] = fma(wv, pad ? 0.0 : lds_f64(m2_b + 8u * trow), psi[m]);
               }
 #pragma unroll
               for (int e = 0; e < FPL; ++e) {
-                const double v = (fl + 32 * e) < d ? xr[32 * e] : 0.0;  // keep 0*garbage out of the fma
+                const double v = (fl + 32 * e) < d ? lds_f64(addr + fl8 + 256u * e) : 0.0;  // keep 0*garbage out of the fma
                 if (u & 1) acc_b[m][e] = fma(v, wv, acc_b[m][e]); else acc_a[m][e] = fma(v, wv, acc_a[m][e]);
               }
             }
@@ -446,32 +446,34 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
 
   // main loop over this CTA's full tiles
   {
-    int s = 0; uint32_t ph = 0; int buf = 0;
-    for (int64_t i = 0; i < my_tiles; ++i) {
-      const int64_t t = (int64_t)blockIdx.x + i * gridDim.x;
-      const int64_t refill = (i >= 1 && i - 1 + stages < my_tiles) ? i - 1 + stages : -1;
-      mbar_wait(&full[s], ph);
-      if (xx_mode != 2) process_tile(std::true_type{}, smem + L.x_off + (size_t)s * sbytes, kTileRows, t * kTileRows, buf, refill);
-      else process_tile(std::false_type{}, smem + L.x_off + (size_t)s * sbytes, kTileRows, t * kTileRows, buf, refill);
+    int s = 0, buf = 0; uint32_t ph = 0;
+    int64_t row0 = (int64_t)blockIdx.x * kTileRows;
+    const int64_t row_step = (int64_t)gridDim.x * kTileRows;
+    for (int i = 0; i < my_tiles; ++i) {
+      const int refill_stage = i == 0 ? -1 : (s == 0 ? stages - 1 : s - 1);   // stage of tile i-1
+      mbar_wait_a(a_full + 8u * (uint32_t)s, ph);
+      const uint32_t xs = a_x + (uint32_t)s * sbytes;
+      if (xx_mode != 2) process_tile(std::true_type{}, xs, kTileRows, row0, buf, refill_stage);
+      else process_tile(std::false_type{}, xs, kTileRows, row0, buf, refill_stage);
       if (++s == stages) { s = 0; ph ^= 1; }
       buf ^= 1;
+      row0 += row_step;
     }
     // ragged tail (< 128 rows): the CTA next in round-robin order loads it with plain loads
     if (tail_rows > 0 && (int)(full_tiles % gridDim.x) == (int)blockIdx.x) {
       __syncthreads();  // every warp is done with all stages
-      unsigned char* xs = smem + L.x_off;
+      unsigned char* xsp = smem + L.x_off;
       const double* src = p.X + (size_t)full_tiles * kTileRows * d;
       for (int i = tid; i < kTileRows * d; i += kComputeThreads) {
         int t = i / d, f = i - t * d;
         double v = t < tail_rows ? src[(size_t)t * d + f] : 0.0;
-        reinterpret_cast<double*>(xs + (t >> 4) * cstride)[(t & 15) * d + f] = v;
+        reinterpret_cast<double*>(xsp + (t >> 4) * cstride)[(t & 15) * d + f] = v;
       }
       __syncthreads();
-      process_tile(std::true_type{}, xs, tail_rows, full_tiles * kTileRows, buf, -1);
+      process_tile(std::true_type{}, a_x, tail_rows, full_tiles * kTileRows, buf, -1);
     }
   }
   if (!p.do_reduce) return;
-  if (MODE == 2) { /* the score pass reduces (sum s*w, sum w) through the cost / xxs slots */ }
 
   // ===================================================================== CTA-level combine
   const int P = k * d + k + 1;
@@ -489,7 +491,7 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
       for (int msk = LPR; msk < 32; msk <<= 1) v += shfl_xor_d(v, msk);
       acc_a[m][e] = v;
     }
-    if (extras) {
+    if (EXTRAS) {
       double c = wacc[m], ps = psi[m];
 #pragma unroll
       for (int msk = 16; msk >= 1; msk >>= 1) { c += shfl_xor_d(c, msk); ps += shfl_xor_d(ps, msk); }

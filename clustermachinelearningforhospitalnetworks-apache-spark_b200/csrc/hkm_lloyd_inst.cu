@@ -52,6 +52,7 @@ int HKM_CAT(dispatch_lloyd_nt, HKM_NT)(const LloydParams& p, const LaunchPlan& p
   // silhouette passes use the generic shared-memory-B kernel
   if (mode == 1) return launch_smemb<NT, 1>(p, pl, grid, st);
   if (mode == 2) return launch_smemb<NT, 2>(p, pl, grid, st);
+  if (mode == 3) return launch_smemb<NT, 3>(p, pl, grid, st);   // weighted Lloyd pass (weightCol)
   // register-resident B fragments while KS*NT doubles per lane stay affordable
 #define HKM_REGB(KS) if constexpr (KS * NT <= 32) { if (ks == KS) return launch_regb<KS, NT>(p, pl, grid, st); }
 #ifndef HKM_DEV_FAST

@@ -121,6 +121,7 @@ HKM_API int hkm_assign_reduce_noalloc(const double* X, int64_t n, int d, const d
  * new_j = sums_j * (1/w_j) for clusters with w_j > 0 (others keep their centre), converged iff
  * every updated centre moved by sqdist <= tol^2; state->cost/iter/converged updated.
  * `partial` is the (all-reduced) vector hkm_assign_reduce produced.  No-op once converged.
+ * tol < 0 never converges (fixed iteration count; Spark itself requires tol >= 0).
  */
 HKM_API int hkm_update_centers(const double* partial, int k, int d, double* C_inout, double tol,
                        hkm_lloyd_state* state, void* stream);
