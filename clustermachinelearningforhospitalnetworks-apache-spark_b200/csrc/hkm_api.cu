@@ -2,6 +2,7 @@
 #include "../../include/hkm.h"
 #include "hkm_lloyd_launch.cuh"
 #include <cstring>
+#include <cstdlib>
 #include <mutex>
 
 namespace hkm {
@@ -13,6 +14,14 @@ void set_error(const char* fmt, ...) {
 int cuda_fail(cudaError_t e, const char* what) {
   set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
   return HKM_ERR_CUDA;
+}
+int lloyd_variant_override() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("HKM_LLOYD_VARIANT");
+    v = e == nullptr ? 0 : (strcmp(e, "gather") == 0 ? 1 : (strcmp(e, "mma") == 0 ? 2 : 0));
+  }
+  return v;
 }
 int sm_count() {
   static int cached[64]; static bool have[64];

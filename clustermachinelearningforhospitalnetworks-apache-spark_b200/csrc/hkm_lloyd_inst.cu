@@ -43,6 +43,23 @@ static int launch_smemb(const LloydParams& p, const LaunchPlan& pl, int grid, cu
   return launch_lloyd<0, NT, 32, 4, 255, MODE>(p, pl, grid, st);
 }
 
+// small-k tensor-pipe variant (assign + reduce on DMMA, no CTA barrier)
+template <int KS_T, int NT>
+static int launch_mma(LloydParams p, int grid, cudaStream_t st) {
+  const LaunchPlan pl = plan_lloyd_mma(p.d, NT * 8);
+  p.stages = pl.stages;
+  auto kern = lloyd_mma_kernel<KS_T, NT, 96>;
+  static int attr_smem[64];
+  int dev = 0; HKM_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev >= 64 || attr_smem[dev] < pl.smem) {
+    HKM_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.smem));
+    if (dev < 64) attr_smem[dev] = pl.smem;
+  }
+  kern<<<grid, kMmaThreads, pl.smem, st>>>(p);
+  HKM_CUDA_TRY(cudaGetLastError());
+  return HKM_OK;
+}
+
 #define HKM_CAT2(a, b) a##b
 #define HKM_CAT(a, b) HKM_CAT2(a, b)
 
@@ -53,6 +70,19 @@ int HKM_CAT(dispatch_lloyd_nt, HKM_NT)(const LloydParams& p, const LaunchPlan& p
   if (mode == 1) return launch_smemb<NT, 1>(p, pl, grid, st);
   if (mode == 2) return launch_smemb<NT, 2>(p, pl, grid, st);
   if (mode == 3) return launch_smemb<NT, 3>(p, pl, grid, st);   // weighted Lloyd pass (weightCol)
+  if constexpr (NT <= 2) {
+    // k <= 16: reduce on the tensor pipe as well (see hkm_lloyd_mma.cuh) when the pass is a plain Lloyd step
+    const int variant = lloyd_variant_override();
+    const bool eligible = p.do_reduce == 1 && p.out_mode == 0 && ks <= 16 && ks * NT <= 32 && plan_lloyd_mma(p.d, NT * 8).stages >= 3;
+    if (eligible && variant != 1 && pl.ctas_per_sm == 2) {
+#define HKM_MMA(KS) if (ks == KS) return launch_mma<KS, NT>(p, grid, st);
+#ifndef HKM_DEV_FAST
+      HKM_MMA(1) HKM_MMA(2) HKM_MMA(3) HKM_MMA(5) HKM_MMA(7) HKM_MMA(10) HKM_MMA(12) HKM_MMA(16)
+#endif
+      HKM_MMA(4) HKM_MMA(6) HKM_MMA(8)
+#undef HKM_MMA
+    }
+  }
   // register-resident B fragments while KS*NT doubles per lane stay affordable
 #define HKM_REGB(KS) if constexpr (KS * NT <= 32) { if (ks == KS) return launch_regb<KS, NT>(p, pl, grid, st); }
 #ifndef HKM_DEV_FAST

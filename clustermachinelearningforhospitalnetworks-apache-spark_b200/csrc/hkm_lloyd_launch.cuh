@@ -4,6 +4,7 @@
 #pragma once
 #include "../../include/hkm.h"
 #include "hkm_lloyd.cuh"
+#include "hkm_lloyd_mma.cuh"
 
 namespace hkm {
 
@@ -23,6 +24,20 @@ inline LaunchPlan plan_lloyd(int d, int k_pad) {
   pl.smem = smem_layout(d, k_pad, pl.stages).total;
   return pl;
 }
+
+// Plan for the small-k tensor-pipe variant (hkm_lloyd_mma.cuh): always two CTAs of 9 warps per SM.
+inline LaunchPlan plan_lloyd_mma(int d, int k_pad) {
+  LaunchPlan pl{};
+  const int budget2 = 112 * 1024;
+  const int fixed = mma_smem_layout(d, k_pad, 0).total;
+  int st = (budget2 - fixed) / stage_bytes(d);
+  pl.stages = st > kMaxStages ? kMaxStages : st;
+  pl.ctas_per_sm = 2;
+  pl.smem = mma_smem_layout(d, k_pad, pl.stages > 0 ? pl.stages : 0).total;
+  return pl;
+}
+// 0: pick per shape (default); 1: always the gather variant; 2: the tensor-pipe variant wherever it is built.
+int lloyd_variant_override();
 
 // Validated, dispatched Lloyd data pass shared by the C entry points (hkm_api.cu).
 struct AssignArgs {

@@ -11,9 +11,11 @@ C = X[:k].clone()
 partial = torch.empty(k * d + k + 1, dtype=torch.float64, device="cuda")
 scratch = N.new_scratch(d, k, "cuda")
 e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-for _ in range(2): N.assign_reduce(X, C, partial, scratch=scratch)
+xs = torch.zeros(1, dtype=torch.float64, device="cuda")
+mode = int(os.environ.get("HKM_XMODE", "2"))
+for _ in range(2): N.assign_reduce(X, C, partial, scratch=scratch, xnorm2_sum=xs, xnorm2_mode=1)
 torch.cuda.synchronize(); e0.record()
-for _ in range(reps): N.assign_reduce(X, C, partial, scratch=scratch)
+for _ in range(reps): N.assign_reduce(X, C, partial, scratch=scratch, xnorm2_sum=xs, xnorm2_mode=mode)
 e1.record(); torch.cuda.synchronize()
 ms = e0.elapsed_time(e1) / reps
 print(f"n={n} d={d} k={k} ms={ms:.4f} GB/s={n*d*8/ms*1e-6:.1f}")
