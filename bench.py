@@ -217,12 +217,17 @@ def main():
     def step(mode, ev=None):
         if ev is not None:
             ev[0].record()
+        # tol < 0: never "converged", every step does full work (rows*iter well defined)
+        if world == 1:
+            N.lloyd_step(X, C, partial, -1.0, state, scratch, xnorm2_sum=xsum, xnorm2_mode=mode)   # pass + centre update, one launch
+            if ev is not None:
+                ev[1].record()
+            return
         N.assign_reduce(X, C, partial, state=state, scratch=scratch, xnorm2_sum=xsum, xnorm2_mode=mode)
         if ev is not None:
             ev[1].record()
-        if world > 1:
-            dist.all_reduce(partial)
-        N.update_centers(partial, C, -1.0, state)  # tol < 0: never "converged", every step does full work (rows*iter well defined)
+        dist.all_reduce(partial)
+        N.update_centers(partial, C, -1.0, state)
 
     def barrier():
         if world > 1:
@@ -232,7 +237,8 @@ def main():
     step(1)                                  # STORE pass: sum |x|^2 (outside the timed region, like the first Lloyd iteration)
     for _ in range(args.warmup):
         step(2)
-    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    # N == 1: a step IS one launch of the kernel, so the region's own events time it; N > 1: bracket each launch
+    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)] if world > 1 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sampler = make_sampler(local_rank) if rank == 0 else None
     barrier()
@@ -240,12 +246,12 @@ def main():
         sampler.start()
     e0.record()
     for i in range(args.steps):
-        step(2, kev[i])
+        step(2, kev[i] if kev else None)
     e1.record()
     barrier()
     clocks = sampler.stop() if sampler else None
     ms_total = e0.elapsed_time(e1)
-    kernel_ms = sum(a.elapsed_time(b) for a, b in kev) / args.steps
+    kernel_ms = (sum(a.elapsed_time(b) for a, b in kev) / args.steps) if kev else ms_total / args.steps
     t = torch.tensor([ms_total, kernel_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -299,11 +305,11 @@ def main():
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": args.workload, "description": desc, "rows_per_gpu": n, "d": d, "k": k,
                    "cache": f"inputs ({alg_bytes / 1e9:.2f} GB per GPU) are larger than the 126 MB L2; no flush needed",
-                   "step": "hkm_assign_reduce (xnorm2 REUSE) + allreduce(k*(d+1)+1 f64) + hkm_update_centers, convergence test off"},
+                   "step": ("hkm_lloyd_step (assign + reduce + centre update in one launch, xnorm2 REUSE)" if world == 1 else "hkm_assign_reduce (xnorm2 REUSE) + allreduce(k*(d+1)+1 f64) + hkm_update_centers") + ", convergence test off"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})", "kernel": "lloyd_pass_kernel",
+                     "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})", "kernel": "lloyd_mma_kernel (hkm_lloyd_mma.cuh)",
                      "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": alg_bytes, "traffic": ncu_traffic(args.workload)},
-        "gpu_launches": 2 * args.steps,
+        "gpu_launches": (1 if world == 1 else 2) * args.steps,
         "clocks": clocks,
     }
     if e2e:

@@ -56,32 +56,7 @@ __global__ void update_centers_kernel(const double* __restrict__ partial, int k,
                                       hkm_lloyd_state* __restrict__ state) {
   if (state->converged != 0) return;
   __shared__ double s_shift[64];
-  const int j = threadIdx.x;  // one thread per cluster (k <= 64)
-  double shift = -1.0;
-  if (j < k) {
-    const double wsum = partial[(size_t)k * d + j];
-    if (wsum > 0) {
-      const double inv = 1.0 / wsum;  // scal(1.0 / weightSum, sum)
-      double s = 0;
-      for (int f = 0; f < d; ++f) {
-        const double nc = partial[(size_t)j * d + f] * inv;
-        const double df = nc - C[(size_t)j * d + f];
-        s = fma(df, df, s);
-        C[(size_t)j * d + f] = nc;
-      }
-      shift = s;
-    }
-  }
-  s_shift[j] = shift;
-  __syncthreads();
-  if (j == 0) {
-    double mx = -1.0;
-    for (int i = 0; i < k; ++i) mx = fmax(mx, s_shift[i]);
-    state->cost = partial[(size_t)k * d + k];
-    state->iter += 1;
-    state->max_shift2 = mx < 0 ? 0.0 : mx;
-    state->converged = (mx <= tol2) ? 1 : 0;  // every updated centre within tol (none updated => converged)
-  }
+  update_centers_body(partial, k, d, C, tol2, state, s_shift, threadIdx.x);
 }
 
 }  // namespace hkm
@@ -105,6 +80,7 @@ int assign_pass(const AssignArgs& a, const char* who) {
   p.X = a.X; p.n = a.n; p.d = d; p.k = k; p.C = a.C; p.w = a.weights; p.partial_out = a.partial_out; p.labels_out = a.labels_out;
   p.mind2_out = a.mind2_out; p.skip = a.state ? &a.state->converged : nullptr; p.do_reduce = a.do_reduce;
   p.out_mode = a.out_mode; p.label_base = a.label_base; p.labels_in = a.labels_in; p.aux = a.aux;
+  p.C_update = a.C_update; p.tol2 = a.tol < 0 ? -1.0 : a.tol * a.tol; p.state_rw = a.state_rw;
   p.xnorm2_sum = a.xnorm2_sum; p.xx_mode = a.do_reduce == 1 ? a.xnorm2_mode : 0;
   p.counter = reinterpret_cast<unsigned int*>(a.scratch);
   p.cta_partials = a.scratch ? reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(a.scratch) + 256) : nullptr;
@@ -141,6 +117,17 @@ int hkm_assign_reduce(const double* X, int64_t n, int d, const double* C, int k,
   a.mind2_out = mind2_out; a.xnorm2_sum = xnorm2_sum; a.xnorm2_mode = xnorm2_mode; a.state = state; a.do_reduce = do_reduce ? 1 : 0;
   a.scratch = scratch; a.scratch_bytes = scratch_bytes; a.stream = stream;
   return assign_pass(a, "hkm_assign_reduce");
+}
+
+int hkm_lloyd_step(const double* X, int64_t n, int d, double* C_inout, int k, const double* weights, double* partial_out,
+                   double* xnorm2_sum, int xnorm2_mode, double tol, hkm_lloyd_state* state, void* scratch, size_t scratch_bytes,
+                   void* stream) {
+  if (state == nullptr || C_inout == nullptr || k > 64) { set_error("hkm_lloyd_step: bad arguments"); return HKM_ERR_INVALID; }
+  AssignArgs a{};
+  a.X = X; a.n = n; a.d = d; a.C = C_inout; a.k = k; a.weights = weights; a.partial_out = partial_out; a.xnorm2_sum = xnorm2_sum;
+  a.xnorm2_mode = xnorm2_mode; a.state = state; a.do_reduce = 1; a.scratch = scratch; a.scratch_bytes = scratch_bytes; a.stream = stream;
+  a.C_update = C_inout; a.tol = tol; a.state_rw = state;
+  return assign_pass(a, "hkm_lloyd_step");
 }
 
 int hkm_update_centers(const double* partial, int k, int d, double* C_inout, double tol, hkm_lloyd_state* state, void* stream) {

@@ -49,11 +49,46 @@ struct LloydParams {
   int label_base;          // added to labels written in out_mode 1 (centre chunk offset)
   double* xnorm2_sum;      // see xx_mode
   int xx_mode;             // 0: per-row |x|^2 in-pass; 1: same, and store sum_w|x|^2; 2: reuse stored sum, skip per-row norms
-  double* cta_partials;    // scratch: [gridDim.x][k*d + k + 2]
+  double* C_update;        // nullable: fused driver step -- the last CTA also updates these centres in place
+  double tol2;             //   convergence threshold (squared); < 0 never converges
+  hkm_lloyd_state* state_rw;  // state written by the fused update
+  double* cta_partials;    // scratch: [gridDim.x][k*d + 2k + 2]
   unsigned int* counter;   // scratch: zero before launch; left zero
   int stages;
   int ks;                  // ceil(d/4)
 };
+
+// Driver side of one Lloyd iteration (KMeans.runAlgorithmWithWeight after collectAsMap): new_j = sums_j * (1/w_j)
+// for clusters with w_j > 0, others keep their centre; converged iff every updated centre moved <= tol^2.
+// Called by one CTA (any blockDim >= 64 threads participate as j = tid < k); s_shift: >= 64 doubles of smem.
+__device__ __forceinline__ void update_centers_body(const double* partial, int k, int d, double* C, double tol2,
+                                                    hkm_lloyd_state* state, double* s_shift, int tid) {
+  double shift = -1.0;
+  if (tid < k) {
+    const double wsum = partial[(size_t)k * d + tid];
+    if (wsum > 0) {
+      const double inv = 1.0 / wsum;  // scal(1.0 / weightSum, sum)
+      double s = 0;
+      for (int f = 0; f < d; ++f) {
+        const double nc = partial[(size_t)tid * d + f] * inv;
+        const double df = nc - C[(size_t)tid * d + f];
+        s = fma(df, df, s);
+        C[(size_t)tid * d + f] = nc;
+      }
+      shift = s;
+    }
+  }
+  if (tid < 64) s_shift[tid] = shift;
+  __syncthreads();
+  if (tid == 0) {
+    double mx = -1.0;
+    for (int i = 0; i < k; ++i) mx = fmax(mx, s_shift[i]);
+    state->cost = partial[(size_t)k * d + k];
+    state->iter += 1;
+    state->max_shift2 = mx < 0 ? 0.0 : mx;
+    state->converged = (mx <= tol2) ? 1 : 0;  // every updated centre within tol (none updated => converged)
+  }
+}
 
 __host__ __device__ inline int chunk_stride_bytes(int d) { return kChunkRows * d * 8 + kChunkPad; }
 __host__ __device__ inline int stage_bytes(int d) { return kChunks * chunk_stride_bytes(d); }
@@ -540,6 +575,11 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
       else p.partial_out[i - 1] = s;                           // MODE 1: psi follows [sums][N][cost]
     }
     if (tid == 0) *p.counter = 0u;
+    if (p.C_update != nullptr) {                               // fused driver step (single rank): uniform branch
+      __threadfence_block();
+      __syncthreads();
+      update_centers_body(p.partial_out, k, d, p.C_update, p.tol2, p.state_rw, red_s, tid);
+    }
   }
 }
 

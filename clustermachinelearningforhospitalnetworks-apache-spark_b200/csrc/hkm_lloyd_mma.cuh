@@ -274,6 +274,35 @@ __global__ void __launch_bounds__(kMmaThreads) __maxnreg__(MAXREG) lloyd_mma_ker
         else if (xx_mode == 1) *p.xnorm2_sum = s;
       }
       if (tid == 0) *p.counter = 0u;
+      if (p.C_update != nullptr) {                             // fused driver step (single rank): compute warps only
+        __threadfence_block();
+        named_bar_sync(1, kComputeThreads);
+        double shift = -1.0;
+        if (tid < k) {
+          const double wsum = p.partial_out[(size_t)k * d + tid];
+          if (wsum > 0) {
+            const double inv = 1.0 / wsum;
+            double sft = 0;
+            for (int f = 0; f < d; ++f) {
+              const double nc = p.partial_out[(size_t)tid * d + f] * inv;
+              const double df = nc - p.C_update[(size_t)tid * d + f];
+              sft = fma(df, df, sft);
+              p.C_update[(size_t)tid * d + f] = nc;
+            }
+            shift = sft;
+          }
+        }
+        if (tid < 16) red_s[tid] = shift;
+        named_bar_sync(1, kComputeThreads);
+        if (tid == 0) {
+          double mx = -1.0;
+          for (int i = 0; i < k; ++i) mx = fmax(mx, red_s[i]);
+          p.state_rw->cost = p.partial_out[(size_t)k * d + k];
+          p.state_rw->iter += 1;
+          p.state_rw->max_shift2 = mx < 0 ? 0.0 : mx;
+          p.state_rw->converged = (mx <= p.tol2) ? 1 : 0;
+        }
+      }
     }
   }
 }

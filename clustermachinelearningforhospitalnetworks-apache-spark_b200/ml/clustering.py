@@ -296,9 +296,11 @@ def lloyd(X: torch.Tensor, C0: np.ndarray, w: Optional[torch.Tensor], max_iter: 
     world = RT.dist_info()[1]
 
     def one_iter(mode):
+        if world == 1:   # one launch: the last CTA of the pass also updates the centres
+            N.lloyd_step(X, C, partial, tol, state, scratch, weights=w, xnorm2_sum=xsum, xnorm2_mode=mode)
+            return
         N.assign_reduce(X, C, partial, weights=w, state=state, scratch=scratch, xnorm2_sum=xsum, xnorm2_mode=mode)
-        if world > 1:
-            RT.all_reduce_sum(partial)
+        RT.all_reduce_sum(partial)
         N.update_centers(partial, C, tol, state)
 
     one_iter(1)  # HKM_XNORM_STORE: exact per-row cost, and sum w|x|^2 for the later passes

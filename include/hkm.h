@@ -89,6 +89,16 @@ HKM_API int hkm_assign_reduce(const double* X, int64_t n, int d, const double* C
                       void* scratch, size_t scratch_bytes, void* stream);
 
 /*
+ * One whole Lloyd iteration on a single rank in ONE launch: hkm_assign_reduce followed by the centre update of
+ * hkm_update_centers, the latter done by the last CTA to finish (no second launch, no gap).  C_inout is read at
+ * the start of the pass and overwritten at its end; state as in hkm_update_centers.  Ranks > 1 need the
+ * all-reduce in between and use the two separate entry points.
+ */
+HKM_API int hkm_lloyd_step(const double* X, int64_t n, int d, double* C_inout, int k, const double* weights,
+                           double* partial_out, double* xnorm2_sum, int xnorm2_mode, double tol,
+                           hkm_lloyd_state* state, void* scratch, size_t scratch_bytes, void* stream);
+
+/*
  * hkm_assign_reduce for callers that cannot allocate device memory.  (No counterpart in the
  * reference or in Spark: it exists for the way this library gets embedded.)
  *
