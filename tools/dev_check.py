@@ -63,4 +63,4 @@ if __name__ == "__main__":
     ok &= check(50000, 16, 16, weights=True)
     print("ALL OK" if ok else "SOME FAILED")
     if "--bench" in sys.argv:
-        bench(10_000_000, 32, 8); bench(20_000_000, 16, 16); bench(5_000_000, 24, 8); bench(5_000_000, 24, 32); bench(5_000_000, 64, 16)
+        bench(10_000_000, 32, 8); bench(20_000_000, 16, 16); bench(5_000_000, 24, 8); bench(5_000_000, 24, 16); bench(5_000_000, 24, 32); bench(5_000_000, 64, 16); bench(5_000_000, 64, 64); bench(20_000_000, 8, 5)
