@@ -87,6 +87,8 @@ int assign_pass(const AssignArgs& a, const char* who) {
   p.stages = pl.stages; p.ks = (d + 3) / 4;
   const int grid = sm_count() * pl.ctas_per_sm;
   const int mode = (a.mode == 0 && a.weights != nullptr) ? 3 : a.mode;   // weights are a compile-time property of the Lloyd kernels
+  if (lloyd_tc_eligible(p, mode) && lloyd_variant_override() != 1)       // large k*d: tensor-core screening + fp64 refinement
+    return launch_lloyd_tc(p, reinterpret_cast<cudaStream_t>(a.stream));
   return dispatch_lloyd(p, pl, grid, mode, reinterpret_cast<cudaStream_t>(a.stream));
 }
 

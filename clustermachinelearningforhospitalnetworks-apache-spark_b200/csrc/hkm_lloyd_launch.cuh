@@ -36,6 +36,9 @@ inline LaunchPlan plan_lloyd_mma(int d, int k_pad) {
   pl.smem = mma_smem_layout(d, k_pad, pl.stages > 0 ? pl.stages : 0).total;
   return pl;
 }
+// tcgen05 screening variant (hkm_lloyd_tc.cuh): 16 < k <= 64, even 32 < d <= 64, plain Lloyd / predict passes
+bool lloyd_tc_eligible(const LloydParams& p, int mode);
+int launch_lloyd_tc(const LloydParams& p, cudaStream_t st);
 // 0: pick per shape (default); 1: always the gather variant; 2: the tensor-pipe variant wherever it is built.
 int lloyd_variant_override();
 
