@@ -166,3 +166,44 @@ def test_full_size_properties(hkm):
         acc += p2
     assert torch.equal(acc[k * d:k * d + k], p1[k * d:k * d + k])
     assert torch.allclose(acc, p1, rtol=1e-10, atol=1e-8)
+
+
+# ---------------------------------------------------------------------------------------------
+# tcgen05 screening variant (k > 32, even 32 < d <= 64): the approximate tensor-core scores only
+# pre-select; labels, sums and cost must still match the fp64 oracle.
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n,d,k,offset,spread", [
+    (40_000, 64, 64, 0.0, 2.0),      # well separated: almost every row has one candidate
+    (40_000, 64, 64, 0.0, 0.05),     # centres nearly coincide: most rows are ambiguous and re-scored exactly
+    (30_000, 64, 40, 25.0, 1.0),     # large common offset (withMean=False data): bound is loose, still exact
+    (30_000, 34, 33, 0.0, 1.0),      # smallest eligible shape, padded K and N
+    (20_011, 50, 64, 3.0, 0.5),      # ragged tail tile
+])
+def test_tensor_core_variant_matches_oracle(hkm, oracle, n, d, k, offset, spread):
+    rng = np.random.default_rng(n + d + k)
+    prof = rng.normal(size=(k, d)) * spread + offset
+    X = prof[rng.integers(0, k, size=n)] + rng.normal(size=(n, d))
+    C = prof + 0.05 * rng.normal(size=(k, d))
+    g = _pass(hkm._native, X, C)
+    sums, wsum, cost, lab = oracle.lloyd_pass(X, C, P=1, want_labels=True)
+    _, dist = oracle.predict(X, C, want_dist=True)
+    assert np.array_equal(g["labels"], lab)
+    _check(g, sums, wsum, cost, lab, dist, scale=float((X * X).sum(1).max()))
+    # steady-state mode (xnorm2 REUSE: winner scores come from the gather) gives the same sums and cost
+    xs = torch.zeros(1, dtype=torch.float64, device="cuda")
+    a = _pass(hkm._native, X, C, want=(), mode=1, xs=xs)
+    b = _pass(hkm._native, X, C, want=(), mode=2, xs=xs)
+    assert np.array_equal(a["sums"], b["sums"]) and np.array_equal(a["wsum"], b["wsum"]) and np.array_equal(a["sums"], g["sums"])
+    assert b["cost"] == pytest.approx(cost, rel=1e-9, abs=1e-9 * float((X * X).sum()))
+
+
+def test_tensor_core_variant_exact_ties(hkm, oracle):
+    rng = np.random.default_rng(3)
+    d, k = 40, 48
+    X = rng.integers(-2, 3, size=(30_000, d)).astype(np.float64)
+    C = rng.integers(-2, 3, size=(k, d)).astype(np.float64)
+    C[7] = C[3]; C[40] = C[3]; C[20] = C[11]           # duplicated centres: ties must go to the lowest index
+    g = _pass(hkm._native, X, C)
+    sums, wsum, cost, lab = oracle.lloyd_pass(X, C, P=1, want_labels=True)
+    assert np.array_equal(g["labels"], lab) and wsum[7] == 0 and wsum[40] == 0 and wsum[20] == 0
+    assert np.array_equal(g["sums"], sums) and np.array_equal(g["wsum"], wsum) and g["cost"] == cost
