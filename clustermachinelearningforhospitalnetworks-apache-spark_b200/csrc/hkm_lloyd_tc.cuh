@@ -159,7 +159,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) lloyd_tc_kernel(const LloydPara
     double dotacc = 0;           // sum over this warp's rows of x[f] * c_label[f] for this lane's features
     double cost = 0, xxs = 0;
     const int xx_mode = p.xx_mode;
-    const bool refine_all = xx_mode != 2 || p.mind2_out != nullptr;   // per-row distances wanted: every row is re-scored exactly
+    // per-row distances wanted (first Lloyd pass, mind2_out): every row is re-scored exactly; label-only passes
+    // (predict) and steady-state Lloyd passes only re-score the ambiguous rows
+    const bool refine_all = p.mind2_out != nullptr || (p.do_reduce == 1 && xx_mode != 2);
     const uint32_t group_stride = 32u * row_bytes + 2u * kChunkPad;
     // conversion / cooperative refine: lane l owns features 2l, 2l+1 of the row the warp is working on
     const bool conv_ok = 2 * lane < d;
