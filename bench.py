@@ -214,12 +214,19 @@ def main():
     xsum = torch.zeros(1, dtype=torch.float64, device=dev)
     C = C0.clone()
 
+    xchg = hkm_b200._runtime.PeerExchange.get(dev) if world > 1 else None
+
     def step(mode, ev=None):
         if ev is not None:
             ev[0].record()
         # tol < 0: never "converged", every step does full work (rows*iter well defined)
         if world == 1:
             N.lloyd_step(X, C, partial, -1.0, state, scratch, xnorm2_sum=xsum, xnorm2_mode=mode)   # pass + centre update, one launch
+            if ev is not None:
+                ev[1].record()
+            return
+        if xchg is not None:     # ranks > 1: still one launch, the k*(d+1)+1 sums cross NVLink inside the kernel tail
+            N.lloyd_step_peer(X, C, partial, -1.0, state, scratch, xchg, xnorm2_sum=xsum, xnorm2_mode=mode)
             if ev is not None:
                 ev[1].record()
             return
@@ -305,11 +312,11 @@ def main():
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": args.workload, "description": desc, "rows_per_gpu": n, "d": d, "k": k,
                    "cache": f"inputs ({alg_bytes / 1e9:.2f} GB per GPU) are larger than the 126 MB L2; no flush needed",
-                   "step": ("hkm_lloyd_step (assign + reduce + centre update in one launch, xnorm2 REUSE)" if world == 1 else "hkm_assign_reduce (xnorm2 REUSE) + allreduce(k*(d+1)+1 f64) + hkm_update_centers") + ", convergence test off"},
+                   "step": ("hkm_lloyd_step (assign + reduce + centre update in one launch, xnorm2 REUSE)" if world == 1 else ("hkm_lloyd_step_peer (one launch: pass + NVLink peer-memory sum of k*(d+1)+1 f64 + centre update)" if xchg is not None else "hkm_assign_reduce (xnorm2 REUSE) + NCCL allreduce(k*(d+1)+1 f64) + hkm_update_centers")) + ", convergence test off"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})", "kernel": "lloyd_mma_kernel (hkm_lloyd_mma.cuh)",
                      "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": alg_bytes, "traffic": ncu_traffic(args.workload)},
-        "gpu_launches": (1 if world == 1 else 2) * args.steps,
+        "gpu_launches": (1 if (world == 1 or xchg is not None) else 2) * args.steps,
         "clocks": clocks,
     }
     if e2e:

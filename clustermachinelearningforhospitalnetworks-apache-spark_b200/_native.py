@@ -15,7 +15,7 @@ SO_PATH = os.path.join(_HERE, "csrc", "libhkm.so")
 
 EXPORTS = (
     "hkm_last_error", "hkm_version", "hkm_max_k", "hkm_max_d",
-    "hkm_assign_reduce_scratch_bytes", "hkm_assign_reduce", "hkm_update_centers", "hkm_lloyd_step",
+    "hkm_assign_reduce_scratch_bytes", "hkm_assign_reduce", "hkm_update_centers", "hkm_lloyd_step", "hkm_lloyd_step_peer", "hkm_peer_exchange_bytes",
     "hkm_kmpar_scratch_bytes", "hkm_kmpar_cost_update", "hkm_kmpar_sample", "hkm_kmpar_strip_rows", "hkm_closest_counts",
     "hkm_silhouette_stats", "hkm_silhouette_score",
     "hkm_assemble_scratch_bytes", "hkm_assemble", "hkm_moments_scratch_bytes", "hkm_moments", "hkm_column_moments", "hkm_scale_rows",
@@ -51,6 +51,10 @@ def load() -> ctypes.CDLL:
         L.hkm_assign_reduce.argtypes = [vp, i64, i32, vp, i32, vp, vp, vp, vp, vp, i32, vp, i32, vp, sz, vp]
         L.hkm_update_centers.argtypes = [vp, i32, i32, vp, ctypes.c_double, vp, vp]
         L.hkm_lloyd_step.argtypes = [vp, i64, i32, vp, i32, vp, vp, vp, i32, ctypes.c_double, vp, vp, sz, vp]
+        L.hkm_peer_exchange_bytes.restype = sz
+        L.hkm_peer_exchange_bytes.argtypes = [i32]
+        L.hkm_lloyd_step_peer.argtypes = [vp, i64, i32, vp, i32, vp, vp, vp, i32, ctypes.c_double, vp, vp, sz, vp, i32, i32,
+                                          ctypes.c_uint64, vp, vp]
         L.hkm_kmpar_scratch_bytes.restype = sz
         L.hkm_kmpar_scratch_bytes.argtypes = [i32]
         L.hkm_kmpar_cost_update.argtypes = [vp, i64, i32, vp, i32, vp, vp, vp, sz, vp]
@@ -134,6 +138,20 @@ def lloyd_step(X, C, partial, tol: float, state, scratch, weights=None, xnorm2_s
     with torch.cuda.device(X.device):
         rc = load().hkm_lloyd_step(_ptr(X), n, d, _ptr(C), k, _ptr(weights), _ptr(partial), _ptr(xnorm2_sum), int(xnorm2_mode),
                                    float(tol), _ptr(state), _ptr(scratch), scratch.numel() * scratch.element_size(), _stream())
+    _check(rc)
+
+
+def lloyd_step_peer(X, C, partial, tol: float, state, scratch, xchg, weights=None, xnorm2_sum=None, xnorm2_mode=0):
+    """hkm_lloyd_step_peer: one launch per Lloyd iteration on ranks > 1 (cross-GPU sum over NVLink peer memory)."""
+    require_cuda(X, "X", torch.float64)
+    require_cuda(C, "C", torch.float64)
+    n, d = X.shape
+    k = C.shape[0]
+    xchg.epoch += 1
+    with torch.cuda.device(X.device):
+        rc = load().hkm_lloyd_step_peer(_ptr(X), n, d, _ptr(C), k, _ptr(weights), _ptr(partial), _ptr(xnorm2_sum), int(xnorm2_mode),
+                                        float(tol), _ptr(state), _ptr(scratch), scratch.numel() * scratch.element_size(),
+                                        ctypes.c_void_p(xchg.ptrs_dev), xchg.rank, xchg.world, xchg.epoch, _ptr(xchg.err), _stream())
     _check(rc)
 
 

@@ -35,3 +35,46 @@ def all_gather_object(obj):
         dist.all_gather_object(out, obj)
         return out
     return [obj]
+
+
+class PeerExchange:
+    """Per-process-group NVLink exchange buffers for hkm_lloyd_step_peer.
+
+    torch's symmetric memory does the allocation and the peer mapping (plumbing); the data movement itself is
+    plain peer stores / loads issued by the Lloyd kernel's last CTA."""
+
+    _cached = None
+
+    def __init__(self, dev: torch.device):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        from . import _native as N
+        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+        nbytes = int(N.load().hkm_peer_exchange_bytes(self.world))
+        self.buf = symm.empty((nbytes + 7) // 8, dtype=torch.int64, device=dev)
+        self.buf.zero_()
+        self.handle = symm.rendezvous(self.buf, dist.group.WORLD)
+        self.ptrs_dev = int(self.handle.buffer_ptrs_dev)
+        self.err = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.epoch = 0
+        torch.cuda.synchronize(dev)
+        dist.barrier()          # every rank has zeroed its buffer before anyone writes into it
+
+    @classmethod
+    def get(cls, dev: torch.device):
+        """The shared instance, or None when peer memory is unavailable (then the NCCL path is used)."""
+        import os
+        if os.environ.get("HKM_NO_PEER_EXCHANGE") == "1":
+            return None
+        if cls._cached is None:
+            try:
+                cls._cached = cls(dev)
+            except Exception as e:  # noqa: BLE001  (no symmetric memory on this platform / build)
+                cls._cached = False
+                import warnings
+                warnings.warn(f"NVLink peer exchange unavailable ({type(e).__name__}: {e}); using NCCL all-reduce")
+        return cls._cached or None
+
+    def check(self):
+        if int(self.err.item()) != 0:
+            raise HkmError("hkm_lloyd_step_peer: a peer rank never arrived at the exchange (time-out)")

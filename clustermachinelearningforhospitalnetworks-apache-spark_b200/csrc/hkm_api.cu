@@ -81,6 +81,7 @@ int assign_pass(const AssignArgs& a, const char* who) {
   p.mind2_out = a.mind2_out; p.skip = a.state ? &a.state->converged : nullptr; p.do_reduce = a.do_reduce;
   p.out_mode = a.out_mode; p.label_base = a.label_base; p.labels_in = a.labels_in; p.aux = a.aux;
   p.C_update = a.C_update; p.tol2 = a.tol < 0 ? -1.0 : a.tol * a.tol; p.state_rw = a.state_rw;
+  p.peer_bufs = a.peer_bufs; p.xrank = a.xrank; p.xworld = a.xworld; p.xepoch = a.xepoch; p.xerr = a.xerr;
   p.xnorm2_sum = a.xnorm2_sum; p.xx_mode = a.do_reduce == 1 ? a.xnorm2_mode : 0;
   p.counter = reinterpret_cast<unsigned int*>(a.scratch);
   p.cta_partials = a.scratch ? reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(a.scratch) + 256) : nullptr;
@@ -130,6 +131,23 @@ int hkm_lloyd_step(const double* X, int64_t n, int d, double* C_inout, int k, co
   a.xnorm2_mode = xnorm2_mode; a.state = state; a.do_reduce = 1; a.scratch = scratch; a.scratch_bytes = scratch_bytes; a.stream = stream;
   a.C_update = C_inout; a.tol = tol; a.state_rw = state;
   return assign_pass(a, "hkm_lloyd_step");
+}
+
+size_t hkm_peer_exchange_bytes(int world) { return world < 1 ? 0 : xchg_buffer_bytes(world); }
+
+int hkm_lloyd_step_peer(const double* X, int64_t n, int d, double* C_inout, int k, const double* weights, double* partial_out,
+                        double* xnorm2_sum, int xnorm2_mode, double tol, hkm_lloyd_state* state, void* scratch, size_t scratch_bytes,
+                        void* const* peer_bufs_dev, int rank, int world, unsigned long long epoch, int* err_flag, void* stream) {
+  if (state == nullptr || C_inout == nullptr || k > 64 || peer_bufs_dev == nullptr || world < 2 || world > 64 || rank < 0 || rank >= world || epoch == 0) {
+    set_error("hkm_lloyd_step_peer: bad arguments"); return HKM_ERR_INVALID;
+  }
+  if ((size_t)k * d + k + 1 > (size_t)kXchgSlot) { set_error("hkm_lloyd_step_peer: k*d + k + 1 exceeds the exchange slot (%d doubles)", kXchgSlot); return HKM_ERR_UNSUPPORTED; }
+  AssignArgs a{};
+  a.X = X; a.n = n; a.d = d; a.C = C_inout; a.k = k; a.weights = weights; a.partial_out = partial_out; a.xnorm2_sum = xnorm2_sum;
+  a.xnorm2_mode = xnorm2_mode; a.state = state; a.do_reduce = 1; a.scratch = scratch; a.scratch_bytes = scratch_bytes; a.stream = stream;
+  a.C_update = C_inout; a.tol = tol; a.state_rw = state;
+  a.peer_bufs = peer_bufs_dev; a.xrank = rank; a.xworld = world; a.xepoch = epoch; a.xerr = err_flag;
+  return assign_pass(a, "hkm_lloyd_step_peer");
 }
 
 int hkm_update_centers(const double* partial, int k, int d, double* C_inout, double tol, hkm_lloyd_state* state, void* stream) {

@@ -52,6 +52,11 @@ struct LloydParams {
   double* C_update;        // nullable: fused driver step -- the last CTA also updates these centres in place
   double tol2;             //   convergence threshold (squared); < 0 never converges
   hkm_lloyd_state* state_rw;  // state written by the fused update
+  // fused cross-GPU reduction (hkm_lloyd_step_peer): peer-mapped exchange buffers, one per rank
+  void* const* peer_bufs;  // nullable: device array [xworld] of buffer base addresses (this rank's own at [xrank])
+  int xrank, xworld;
+  unsigned long long xepoch;  // strictly increasing call counter, identical on every rank
+  int* xerr;               // set to 1 if a peer never showed up (spin time-out)
   double* cta_partials;    // scratch: [gridDim.x][k*d + 2k + 2]
   unsigned int* counter;   // scratch: zero before launch; left zero
   int stages;
@@ -87,6 +92,46 @@ __device__ __forceinline__ void update_centers_body(const double* partial, int k
     state->iter += 1;
     state->max_shift2 = mx < 0 ? 0.0 : mx;
     state->converged = (mx <= tol2) ? 1 : 0;  // every updated centre within tol (none updated => converged)
+  }
+}
+
+// ---- one-shot all-reduce of a small fp64 vector over NVLink peer memory, run by the last CTA of every rank's pass.
+// Each rank owns an exchange buffer mapped into every peer: slots[2][world][kXchgSlot] doubles, then flags[2][world].
+// A rank stores its vector into slot [epoch&1][rank] of EVERY peer (plain stores through the peer mapping), fences,
+// raises flag [epoch&1][rank] = epoch on every peer, waits until all `world` flags of its own buffer carry `epoch`,
+// and sums the `world` slots in rank order -- so every rank obtains the bit-identical total without a collective
+// launch.  Two slot sets (epoch parity) keep a fast rank's next step from overwriting what a slow rank still reads.
+constexpr int kXchgSlot = 4352;   // doubles per slot: >= 64*65 + 64 + 2
+__host__ __device__ inline size_t xchg_flags_offset(int world) { return (size_t)2 * world * kXchgSlot * sizeof(double); }
+__host__ __device__ inline size_t xchg_buffer_bytes(int world) { return xchg_flags_offset(world) + (size_t)2 * world * sizeof(unsigned long long) + 64; }
+
+template <class Sync>
+__device__ __forceinline__ void peer_allreduce(const LloydParams& p, double* vec, int len, int tid, int nthreads, Sync sync) {
+  const int world = p.xworld, rank = p.xrank, set = (int)(p.xepoch & 1ull);
+  const size_t slot_off = ((size_t)set * world + rank) * kXchgSlot;
+  for (int q = 0; q < world; ++q) {
+    double* dst = reinterpret_cast<double*>(p.peer_bufs[q]) + slot_off;
+    for (int i = tid; i < len; i += nthreads) dst[i] = vec[i];
+  }
+  __threadfence_system();
+  sync();
+  if (tid < world) {
+    unsigned long long* f = reinterpret_cast<unsigned long long*>(reinterpret_cast<unsigned char*>(p.peer_bufs[tid]) + xchg_flags_offset(world)) + set * world + rank;
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(f), "l"(p.xepoch) : "memory");
+    const unsigned long long* mine = reinterpret_cast<const unsigned long long*>(reinterpret_cast<const unsigned char*>(p.peer_bufs[rank]) + xchg_flags_offset(world)) + set * world + tid;
+    unsigned long long v = 0;
+    const long long t0 = clock64();
+    do {
+      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(mine) : "memory");
+      if (v != p.xepoch && clock64() - t0 > 8000000000LL) { if (p.xerr != nullptr) *p.xerr = 1; break; }   // ~4 s: a peer is missing, do not hang the GPU
+    } while (v != p.xepoch);
+  }
+  sync();
+  const double* base = reinterpret_cast<const double*>(p.peer_bufs[rank]) + (size_t)set * world * kXchgSlot;
+  for (int i = tid; i < len; i += nthreads) {
+    double s = 0;
+    for (int q = 0; q < world; ++q) s += __ldcv(base + (size_t)q * kXchgSlot + i);
+    vec[i] = s;
   }
 }
 
@@ -575,7 +620,12 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
       else p.partial_out[i - 1] = s;                           // MODE 1: psi follows [sums][N][cost]
     }
     if (tid == 0) *p.counter = 0u;
-    if (p.C_update != nullptr) {                               // fused driver step (single rank): uniform branch
+    if (p.peer_bufs != nullptr) {                              // ranks > 1: sum the vector over NVLink peer memory right here
+      __threadfence_block();
+      __syncthreads();
+      peer_allreduce(p, p.partial_out, P, tid, kComputeThreads, [] { __syncthreads(); });
+    }
+    if (p.C_update != nullptr) {                               // fused driver step: uniform branch
       __threadfence_block();
       __syncthreads();
       update_centers_body(p.partial_out, k, d, p.C_update, p.tol2, p.state_rw, red_s, tid);

@@ -48,6 +48,7 @@ struct AssignArgs {
   double* partial_out; int32_t* labels_out; double* mind2_out; double* xnorm2_sum; int xnorm2_mode;
   const hkm_lloyd_state* state; int do_reduce; int out_mode; int label_base;
   double* C_update; double tol; hkm_lloyd_state* state_rw;   // fused single-rank driver step (hkm_lloyd_step)
+  void* const* peer_bufs; int xrank, xworld; unsigned long long xepoch; int* xerr;   // hkm_lloyd_step_peer
   int mode; const int32_t* labels_in; const double* aux;   // mode 1/2: silhouette statistics / score pass
   void* scratch; size_t scratch_bytes; void* stream;
 };

@@ -274,7 +274,12 @@ __global__ void __launch_bounds__(kMmaThreads) __maxnreg__(MAXREG) lloyd_mma_ker
         else if (xx_mode == 1) *p.xnorm2_sum = s;
       }
       if (tid == 0) *p.counter = 0u;
-      if (p.C_update != nullptr) {                             // fused driver step (single rank): compute warps only
+      if (p.peer_bufs != nullptr) {                            // ranks > 1: sum the vector over NVLink peer memory right here
+        __threadfence_block();
+        named_bar_sync(1, kComputeThreads);
+        peer_allreduce(p, p.partial_out, P, tid, kComputeThreads, [] { named_bar_sync(1, kComputeThreads); });
+      }
+      if (p.C_update != nullptr) {                             // fused driver step: compute warps only
         __threadfence_block();
         named_bar_sync(1, kComputeThreads);
         double shift = -1.0;

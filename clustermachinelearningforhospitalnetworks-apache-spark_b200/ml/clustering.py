@@ -295,9 +295,14 @@ def lloyd(X: torch.Tensor, C0: np.ndarray, w: Optional[torch.Tensor], max_iter: 
     xsum = torch.zeros(1, dtype=torch.float64, device=dev)
     world = RT.dist_info()[1]
 
+    xchg = RT.PeerExchange.get(dev) if world > 1 else None
+
     def one_iter(mode):
         if world == 1:   # one launch: the last CTA of the pass also updates the centres
             N.lloyd_step(X, C, partial, tol, state, scratch, weights=w, xnorm2_sum=xsum, xnorm2_mode=mode)
+            return
+        if xchg is not None:   # one launch too: the cross-GPU sum runs over NVLink peer memory inside the kernel tail
+            N.lloyd_step_peer(X, C, partial, tol, state, scratch, xchg, weights=w, xnorm2_sum=xsum, xnorm2_mode=mode)
             return
         N.assign_reduce(X, C, partial, weights=w, state=state, scratch=scratch, xnorm2_sum=xsum, xnorm2_mode=mode)
         RT.all_reduce_sum(partial)
@@ -318,6 +323,8 @@ def lloyd(X: torch.Tensor, C0: np.ndarray, w: Optional[torch.Tensor], max_iter: 
             one_iter(mode)
         st = N.read_state(state)
         it = st.iter
+    if xchg is not None:
+        xchg.check()
     return C.cpu().numpy(), int(st.iter), float(st.cost)
 
 

@@ -99,6 +99,24 @@ HKM_API int hkm_lloyd_step(const double* X, int64_t n, int d, double* C_inout, i
                            hkm_lloyd_state* state, void* scratch, size_t scratch_bytes, void* stream);
 
 /*
+ * hkm_lloyd_step for ranks > 1: the k*(d+1)+1 partial sums are all-reduced INSIDE the same launch, over NVLink
+ * peer memory, instead of by a separate NCCL call (Spark: reduceByKey + collectAsMap + broadcast per iteration).
+ * Every rank owns an exchange buffer of hkm_peer_exchange_bytes(world) bytes that is mapped into all peers
+ * (CUDA IPC / symmetric memory; zero it once).  peer_bufs_dev is a DEVICE array of the `world` buffer addresses
+ * as seen from this rank.  The last CTA of the pass stores this rank's vector into every peer's buffer, raises a
+ * flag, waits for the other ranks' flags and sums the slots in rank order, so all ranks get the bit-identical
+ * total and update their (replicated) centres identically -- one launch per Lloyd iteration, no collective.
+ * `epoch` must be 1, 2, 3, ... on successive calls and equal on all ranks; all ranks must make the call (a rank
+ * that never arrives makes the others give up after a few seconds and set *err_flag = 1).
+ */
+HKM_API size_t hkm_peer_exchange_bytes(int world);
+HKM_API int hkm_lloyd_step_peer(const double* X, int64_t n, int d, double* C_inout, int k, const double* weights,
+                                double* partial_out, double* xnorm2_sum, int xnorm2_mode, double tol,
+                                hkm_lloyd_state* state, void* scratch, size_t scratch_bytes,
+                                void* const* peer_bufs_dev, int rank, int world, unsigned long long epoch,
+                                int* err_flag, void* stream);
+
+/*
  * hkm_assign_reduce for callers that cannot allocate device memory.  (No counterpart in the
  * reference or in Spark: it exists for the way this library gets embedded.)
  *
