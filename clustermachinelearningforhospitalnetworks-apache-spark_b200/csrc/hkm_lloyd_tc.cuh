@@ -29,7 +29,7 @@ __host__ __device__ inline TcSmemLayout tc_smem_layout(int d, int k_pad, int sta
   L.x_off = o; o += stages * stage_bytes(d); o = (o + 1023) & ~1023;
   L.a_off = o; o += kchunks * tc_lbo_a(); o = (o + 127) & ~127;
   L.b_off = o; o += kchunks * tc_lbo_b(k_pad); o = (o + 127) & ~127;
-  L.cs_off = o; o += k_pad * 64 * 8;                           // fp64 centres, dense 512-byte rows (refine reads them rotated)
+  L.cs_off = o; o += k_pad * 64 * 8;                           // fp64 per-cluster sums of this CTA, dense 512-byte rows (+ counts below)
   L.mu_off = o; o += 64 * 8;
   L.h_off = o; o += k_pad * 4;                                 // float -0.5|c-mu|^2
   L.cn_off = o; o += k_pad * 8;                                // double -0.5|c|^2
@@ -37,7 +37,7 @@ __host__ __device__ inline TcSmemLayout tc_smem_layout(int d, int k_pad, int sta
   L.labels_off = o; o += 2 * kTileRows * 4;
   L.pair_off = o; o += kTileRows * 2 * 16;                     // per (row, half): {double score, int idx}
   L.list_off = o; o += kComputeWarps * list_entries(k_pad) * 4; o = (o + 15) & ~15;
-  L.zero_off = o; o += 64 * 8;
+  L.zero_off = o; o += 64 * 8;                                 // per-cluster row counts (unsigned, k_pad <= 64 entries)
   L.red_off = o; o += 2 * kComputeWarps * 8 + 64 * 8;
   L.bar_off = o; o += (2 * kMaxStages + 2) * 8;
   L.tmem_off = o; o += 16;
@@ -93,15 +93,14 @@ __global__ void __launch_bounds__(kTcThreads, 1) lloyd_tc_kernel(const LloydPara
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 64;" ::"r"(sb + L.tmem_off) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  for (int i = tid; i < k_pad * 64; i += kTcThreads) { const int j = i >> 6, f = i & 63; Cs[i] = (j < k && f < d) ? p.C[(size_t)j * d + f] : 0.0; }
-  for (int i = tid; i < 64; i += kTcThreads) reinterpret_cast<double*>(smem + L.zero_off)[i] = 0.0;
+  for (int i = tid; i < k_pad * 64; i += kTcThreads) Cs[i] = 0.0;             // Cs doubles as the per-cluster accumulator block
+  for (int i = tid; i < 64; i += kTcThreads) reinterpret_cast<unsigned int*>(smem + L.zero_off)[i] = 0u;
   if (tid == 0) *reinterpret_cast<unsigned int*>(smem + L.tmem_off + 8) = 0u;   // ambiguous-row counter
-  __syncthreads();
-  if (tid < 64) { double s = 0; for (int j = 0; j < k; ++j) s += Cs[j * 64 + tid]; mu_s[tid] = tid < d ? s / k : 0.0; }   // mu = mean of the centres
+  if (tid < 64) { double s = 0; if (tid < d) for (int j = 0; j < k; ++j) s += p.C[(size_t)j * d + tid]; mu_s[tid] = tid < d ? s / k : 0.0; }   // mu = mean of the centres
   __syncthreads();
   if (tid < k_pad) {
     double s = 0, sc = 0;
-    for (int f = 0; f < d; ++f) { const double c = Cs[tid * 64 + f], cc = c - mu_s[f]; s = fma(c, c, s); sc = fma(cc, cc, sc); }
+    if (tid < k) for (int f = 0; f < d; ++f) { const double c = p.C[(size_t)tid * d + f], cc = c - mu_s[f]; s = fma(c, c, s); sc = fma(cc, cc, sc); }
     cn_s[tid] = tid < k ? -0.5 * s : -__longlong_as_double(0x7ff0000000000000LL);
     h_s[tid] = tid < k ? (float)(-0.5 * sc) : -__int_as_float(0x7f800000);
     red_s[2 * kComputeWarps + tid] = tid < k ? sc : 0.0;
@@ -109,12 +108,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) lloyd_tc_kernel(const LloydPara
   // B operand: tf32(c - mu), canonical K-major layout; padded centres / features are zero
   for (int i = tid; i < k_pad * kchunks; i += kTcThreads) {
     const int j = i % k_pad, c = i / k_pad;
-    float4 v;
-    v.x = (float)(Cs[j * 64 + 4 * c + 0] - mu_s[4 * c + 0]); v.y = (float)(Cs[j * 64 + 4 * c + 1] - mu_s[4 * c + 1]);
-    v.z = (float)(Cs[j * 64 + 4 * c + 2] - mu_s[4 * c + 2]); v.w = (float)(Cs[j * 64 + 4 * c + 3] - mu_s[4 * c + 3]);
-    if (j >= k) v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (4 * c + 0 >= d) v.x = 0.f; if (4 * c + 1 >= d) v.y = 0.f; if (4 * c + 2 >= d) v.z = 0.f; if (4 * c + 3 >= d) v.w = 0.f;
-    *reinterpret_cast<float4*>(smem + L.b_off + c * LBO_B + (j >> 3) * 128 + (j & 7) * 16) = v;
+    float vv[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) { const int f = 4 * c + e; vv[e] = (j < k && f < d) ? (float)(p.C[(size_t)j * d + f] - mu_s[f]) : 0.f; }
+    *reinterpret_cast<float4*>(smem + L.b_off + c * LBO_B + (j >> 3) * 128 + (j & 7) * 16) = make_float4(vv[0], vv[1], vv[2], vv[3]);
   }
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -148,16 +145,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) lloyd_tc_kernel(const LloydPara
     const int fl = lane;
     const uint32_t fl8 = (uint32_t)fl * 8u;
     // gather: warp w owns clusters w, w+8, ... (slot m = label >> 3); lane = feature (and feature + 32)
-    double acc[NT][FPL], creg[NT][FPL];
-    unsigned cnt[NT];
-#pragma unroll
-    for (int m = 0; m < NT; ++m) {
-      cnt[m] = 0;
-#pragma unroll
-      for (int e = 0; e < FPL; ++e) { acc[m][e] = 0; creg[m][e] = Cs[(warp + 8 * m) * 64 + fl + 32 * e]; }
-    }
-    double dotacc = 0;           // sum over this warp's rows of x[f] * c_label[f] for this lane's features
     double cost = 0, xxs = 0;
+    const uint32_t a_acc = a_cs + fl8;                       // per-cluster sums in shared memory: row j at j*512, this lane's feature
+    const uint32_t a_cnt = sb + L.zero_off;
     const int xx_mode = p.xx_mode;
     // per-row distances wanted (first Lloyd pass, mind2_out): every row is re-scored exactly; label-only passes
     // (predict) and steady-state Lloyd passes only re-score the ambiguous rows
@@ -212,8 +202,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) lloyd_tc_kernel(const LloydPara
       }
     };
 
-    // per-cluster sums: one ballot per 32 rows finds this warp's rows; each is added to its cluster's register
-    // accumulators through a warp-uniform switch, and its exact winner score x.c_label is folded into dotacc.
+    // per-cluster sums: one ballot per 32 rows finds this warp's rows (label & 7 == warp, so no two warps ever touch
+    // the same cluster); each row is added to its cluster's shared-memory accumulator row, one feature (pair) per lane.
+    // Two rows are in flight per step; equal labels are merged first so the read-modify-write stays race free.
     auto gather_tile = [&](const uint32_t xs, const uint32_t lab_b) {
 #pragma unroll 1
       for (int g = 0; g < kTileRows / 32; ++g) {
@@ -221,15 +212,31 @@ __global__ void __launch_bounds__(kTcThreads, 1) lloyd_tc_kernel(const LloydPara
         unsigned mask = __ballot_sync(0xffffffffu, lab >= 0 && (lab & 7) == warp);
         const uint32_t gbase = xs + (uint32_t)g * group_stride + fl8;
         while (mask) {
-          const int r = __ffs(mask) - 1; mask &= mask - 1;
-          const int m = __shfl_sync(0xffffffffu, lab, r) >> 3;
-          const uint32_t ra = gbase + (uint32_t)r * row_bytes + (uint32_t)(r >> 4) * kChunkPad;
-          double v[FPL];
+          const int r0 = __ffs(mask) - 1; mask &= mask - 1;
+          bool two = mask != 0;
+          const int r1 = two ? __ffs(mask) - 1 : r0; mask &= mask - 1;
+          const int l0 = __shfl_sync(0xffffffffu, lab, r0), l1 = __shfl_sync(0xffffffffu, lab, r1);
+          const uint32_t ra0 = gbase + (uint32_t)r0 * row_bytes + (uint32_t)(r0 >> 4) * kChunkPad;
+          const uint32_t ra1 = gbase + (uint32_t)r1 * row_bytes + (uint32_t)(r1 >> 4) * kChunkPad;
+          double v0[FPL], v1[FPL];
 #pragma unroll
-          for (int e = 0; e < FPL; ++e) v[e] = lds_f64(ra + 256u * e);   // lanes past d read neighbouring smem into accumulators that are never stored
-#define HKM_TC_CASE(M) case M: if (M < NT) { _Pragma("unroll") for (int e = 0; e < FPL; ++e) { acc[M < NT ? M : 0][e] += v[e]; dotacc = fma(v[e], creg[M < NT ? M : 0][e], dotacc); } cnt[M < NT ? M : 0] += 1; } break;
-          switch (m) { HKM_TC_CASE(0) HKM_TC_CASE(1) HKM_TC_CASE(2) HKM_TC_CASE(3) HKM_TC_CASE(4) HKM_TC_CASE(5) HKM_TC_CASE(6) HKM_TC_CASE(7) default: break; }
-#undef HKM_TC_CASE
+          for (int e = 0; e < FPL; ++e) { v0[e] = lds_f64(ra0 + 256u * e); v1[e] = two ? lds_f64(ra1 + 256u * e) : 0.0; }   // lanes past d touch padding columns that are never stored
+          unsigned n0 = 1;
+          if (two && l1 == l0) {
+#pragma unroll
+            for (int e = 0; e < FPL; ++e) v0[e] += v1[e];
+            two = false; n0 = 2;
+          }
+          const uint32_t aa0 = a_acc + (uint32_t)l0 * 512u, aa1 = a_acc + (uint32_t)l1 * 512u;
+          double s0[FPL], s1[FPL];
+#pragma unroll
+          for (int e = 0; e < FPL; ++e) { s0[e] = lds_f64(aa0 + 256u * e); if (two) s1[e] = lds_f64(aa1 + 256u * e); }
+#pragma unroll
+          for (int e = 0; e < FPL; ++e) { sts_f64(aa0 + 256u * e, s0[e] + v0[e]); if (two) sts_f64(aa1 + 256u * e, s1[e] + v1[e]); }
+          if (lane == 0) {
+            sts_u32(a_cnt + 4u * (uint32_t)l0, lds_u32(a_cnt + 4u * (uint32_t)l0) + n0);
+            if (two) sts_u32(a_cnt + 4u * (uint32_t)l1, lds_u32(a_cnt + 4u * (uint32_t)l1) + 1u);
+          }
         }
       }
     };
@@ -245,8 +252,8 @@ __global__ void __launch_bounds__(kTcThreads, 1) lloyd_tc_kernel(const LloydPara
         uint32_t msk = h == 0 ? mlo : mhi;
         while (msk) {                                            // ascending index: strict '>' keeps the lowest index on ties
           const int j = h * HALF + __ffs(msk) - 1; msk &= msk - 1;
-          double2 c;
-          asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(c.x), "=d"(c.y) : "r"(a_cs + (uint32_t)j * 512u + 16u * lane));
+          double2 c = make_double2(0.0, 0.0);
+          if (conv_ok) c = __ldg(reinterpret_cast<const double2*>(p.C + (size_t)j * d) + lane);   // centres stay in L1/L2; only ambiguous rows get here
           double sdot = fma(x.x, c.x, x.y * c.y);
 #pragma unroll
           for (int mk = 16; mk >= 1; mk >>= 1) sdot += shfl_xor_d(sdot, mk);
@@ -312,7 +319,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) lloyd_tc_kernel(const LloydPara
       const bool valid = erow < rows_valid;
       if (!refine_all && hf == 1) {
         // steady state: a row with a single candidate is decided here; its exact score reaches the cost through the
-        // gather (dotacc).  Rows with two or more candidates go to the cooperative exact re-scoring below.
+        // gather (sum_j S_j . c_j).  Rows with two or more candidates go to the cooperative exact re-scoring below.
         const uint32_t olo = lds_u32(pair_ot + 4u);
         const int total = __popc(olo) + __popc(cand);
         if (!valid) sts_u32(lab_b + 4u * (uint32_t)erow, 0xffffffffu);
@@ -397,25 +404,20 @@ __global__ void __launch_bounds__(kTcThreads, 1) lloyd_tc_kernel(const LloydPara
       const int P = k * d + k + 1;
       const int S = P + 1 + k;
       double* out = p.cta_partials + (size_t)blockIdx.x * S;
+      named_bar_sync(1, kComputeThreads);                     // every warp's gather has landed in shared memory
       if (!refine_all) {
-        // steady state: sum of exact winner scores = sum_rows x.c_label - 0.5 sum_j n_j |c_j|^2 (the fold turns it into the cost)
-        cost = dotacc;
-        if (lane == 0) {
-#pragma unroll
-          for (int m = 0; m < NT; ++m) if (warp + 8 * m < k) cost = fma((double)cnt[m], cn_s[warp + 8 * m], cost);
-        }
+        // steady state: the sum of the exact winner scores needs no per-row work at all:
+        //   sum_rows (x.c_label - 0.5|c_label|^2) = sum_j S_j . c_j - 0.5 sum_j n_j |c_j|^2      (the fold turns it into the cost)
+        cost = 0;
+        for (int i = tid; i < k * d; i += kComputeThreads) { const int j = i / d, f = i - j * d; cost = fma(Cs[j * 64 + f], p.C[i], cost); }
+        if (tid < k) cost = fma((double)reinterpret_cast<const unsigned int*>(smem + L.zero_off)[tid], cn_s[tid], cost);
       }
 #pragma unroll
       for (int msk = 16; msk >= 1; msk >>= 1) { cost += shfl_xor_d(cost, msk); xxs += shfl_xor_d(xxs, msk); }
       if (lane == 0) { red_s[warp] = cost; red_s[kComputeWarps + warp] = xxs; }
-#pragma unroll
-      for (int m = 0; m < NT; ++m) {
-        const int j = warp + 8 * m;
-        if (j < k && p.do_reduce == 1) {
-#pragma unroll
-          for (int e = 0; e < FPL; ++e) { const int f = fl + 32 * e; if (f < d) out[(size_t)j * d + f] = acc[m][e]; }
-          if (lane == 0) out[(size_t)k * d + j] = (double)cnt[m];
-        }
+      if (p.do_reduce == 1) {
+        for (int i = tid; i < k * d; i += kComputeThreads) { const int j = i / d, f = i - j * d; out[i] = Cs[j * 64 + f]; }
+        if (tid < k) out[(size_t)k * d + tid] = (double)reinterpret_cast<const unsigned int*>(smem + L.zero_off)[tid];
       }
       named_bar_sync(1, kComputeThreads);
       if (tid == 0) {
