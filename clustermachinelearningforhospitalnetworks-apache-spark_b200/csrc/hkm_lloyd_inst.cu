@@ -44,11 +44,11 @@ static int launch_smemb(const LloydParams& p, const LaunchPlan& pl, int grid, cu
 }
 
 // small-k tensor-pipe variant (assign + reduce on DMMA, no CTA barrier)
-template <int KS_T, int NT>
+template <int KS_T, int NT, int MODE = 0>
 static int launch_mma(LloydParams p, int grid, cudaStream_t st) {
   const LaunchPlan pl = plan_lloyd_mma(p.d, NT * 8);
   p.stages = pl.stages;
-  auto kern = lloyd_mma_kernel<KS_T, NT, 96>;
+  auto kern = lloyd_mma_kernel<KS_T, NT, 96, MODE>;
   static int attr_smem[64];
   int dev = 0; HKM_CUDA_TRY(cudaGetDevice(&dev));
   if (dev >= 64 || attr_smem[dev] < pl.smem) {
@@ -66,7 +66,18 @@ static int launch_mma(LloydParams p, int grid, cudaStream_t st) {
 int HKM_CAT(dispatch_lloyd_nt, HKM_NT)(const LloydParams& p, const LaunchPlan& pl, int grid, int mode, cudaStream_t st) {
   constexpr int NT = HKM_NT;
   const int ks = p.ks;
-  // silhouette passes use the generic shared-memory-B kernel
+  // silhouette passes: k <= 16 on the barrier-free tensor-pipe kernel, larger k on the gather kernel
+  if constexpr (NT <= 2) {
+    if ((mode == 1 || mode == 2) && ks <= 16 && ks * NT <= 32 && pl.ctas_per_sm == 2 && plan_lloyd_mma(p.d, NT * 8).stages >= 3 &&
+        lloyd_variant_override() != 1 && (mode == 2 || NT * ((ks + 1) / 2 + 1) <= 14)) {
+#define HKM_SIL(KS) if (ks == KS) return mode == 1 ? launch_mma<KS, NT, 1>(p, grid, st) : launch_mma<KS, NT, 2>(p, grid, st);
+#ifndef HKM_DEV_FAST
+      HKM_SIL(1) HKM_SIL(2) HKM_SIL(3) HKM_SIL(5) HKM_SIL(7) HKM_SIL(10) HKM_SIL(12) HKM_SIL(16)
+#endif
+      HKM_SIL(4) HKM_SIL(6) HKM_SIL(8)
+#undef HKM_SIL
+    }
+  }
   if (mode == 1) return launch_smemb<NT, 1>(p, pl, grid, st);
   if (mode == 2) return launch_smemb<NT, 2>(p, pl, grid, st);
   if (mode == 3) return launch_smemb<NT, 3>(p, pl, grid, st);   // weighted Lloyd pass (weightCol)

@@ -25,17 +25,20 @@ __host__ __device__ inline MmaSmemLayout mma_smem_layout(int d, int k_pad, int s
   L.x_off = o; o += stages * stage_bytes(d); o = (o + 127) & ~127;
   L.bar_off = o; o += 2 * kMaxStages * 8;
   L.cs_off = o; o += k_pad * cs_ld(d) * 8;
-  L.cn_off = o; o += k_pad * 8;
+  L.cn_off = o; o += 2 * k_pad * 8;                       // second half: cluster weight sums (silhouette score pass)
   L.red_off = o; o += 2 * kComputeWarps * 8 + 16;
   L.total = o;
   return L;
 }
 
 // KS_T = ceil(d/4) (score k-steps), NT = ceil(k/8) (1 or 2), ND = ceil(d/8) feature tiles of the reduce product.
-template <int KS_T, int NT, int MAXREG>
+// MODE 0: Lloyd / predict pass.  MODE 1: silhouette cluster statistics (labels given; the one-hot product also
+// carries the weights, and one extra feature tile accumulates Psi = sum w|x|^2).  MODE 2: silhouette score pass.
+template <int KS_T, int NT, int MAXREG, int MODE = 0>
 __global__ void __launch_bounds__(kMmaThreads) __maxnreg__(MAXREG) lloyd_mma_kernel(const LloydParams p) {
   if (p.skip != nullptr && *p.skip != 0) return;
   constexpr int ND = (KS_T + 1) / 2;
+  constexpr int NDX = MODE == 1 ? ND + 1 : ND;   // accumulator feature tiles (one more for Psi)
   constexpr int k_pad = NT * 8;
 
   extern __shared__ __align__(128) unsigned char smem[];
@@ -72,7 +75,12 @@ __global__ void __launch_bounds__(kMmaThreads) __maxnreg__(MAXREG) lloyd_mma_ker
   for (int j = tid; j < k_pad; j += kMmaThreads) {
     double s = 0;
     for (int f = 0; f < d; ++f) s = fma(Cs[j * csld + f], Cs[j * csld + f], s);
-    cn_s[j] = j < k ? -0.5 * s : -__longlong_as_double(0x7ff0000000000000LL);
+    const double ninf = -__longlong_as_double(0x7ff0000000000000LL);
+    if (MODE == 2) {   // D(x, G) = |x|^2 + Psi_G/N_G - 2 x.(Y_G/N_G): the Lloyd score with -0.5*Psi_G/N_G as the constant
+      const double Nj = j < k ? p.aux[j] : 0.0;
+      cn_s[j] = (j < k && Nj > 0) ? -0.5 * p.aux[k + j] : ninf;
+      cn_s[k_pad + j] = Nj;
+    } else cn_s[j] = j < k ? -0.5 * s : ninf;
   }
   __syncthreads();
 
@@ -109,14 +117,16 @@ __global__ void __launch_bounds__(kMmaThreads) __maxnreg__(MAXREG) lloyd_mma_ker
     for (int nt = 0; nt < NT; ++nt) { cinit[nt][0] = cn_s[8 * nt + 2 * t]; cinit[nt][1] = cn_s[8 * nt + 2 * t + 1]; }
 
     // private partial sums: acc[mt][nd][e] = S[8*mt + g][8*nd + 2*t + e]
-    double acc[NT][ND][2];
+    double acc[NT][NDX][2];
     unsigned cnt[NT];
+    double wcnt[NT];                              // MODE 1: weighted counts
 #pragma unroll
     for (int mt = 0; mt < NT; ++mt) {
-      cnt[mt] = 0;
+      cnt[mt] = 0; wcnt[mt] = 0;
 #pragma unroll
-      for (int nd = 0; nd < ND; ++nd) { acc[mt][nd][0] = 0; acc[mt][nd][1] = 0; }
+      for (int nd = 0; nd < NDX; ++nd) { acc[mt][nd][0] = 0; acc[mt][nd][1] = 0; }
     }
+    const bool has_w = p.w != nullptr;
     double cost = 0, xxs = 0;
     const int xx_mode = p.xx_mode;
     const uint32_t a_frag = (uint32_t)g * cstride + (uint32_t)t * 8u;        // score A-fragment: chunk g, feature t (+4s)
@@ -138,7 +148,82 @@ __global__ void __launch_bounds__(kMmaThreads) __maxnreg__(MAXREG) lloyd_mma_ker
         const double a0 = ok ? lds_f64(xa0 + 32u * s) : 0.0, a1 = ok ? lds_f64(xa1 + 32u * s) : 0.0;
         if (NEED_XX) { xx0 = fma(a0, a0, xx0); xx1 = fma(a1, a1, xx1); }
 #pragma unroll
-        for (int nt = 0; nt < NT; ++nt) dmma1684(s0[nt][0], s0[nt][1], s1[nt][0], s1[nt][1], a0, a1, breg[s * NT + nt]);
+        for (int nt = 0; nt < NT; ++nt) { if (MODE != 1) dmma1684(s0[nt][0], s0[nt][1], s1[nt][0], s1[nt][1], a0, a1, breg[s * NT + nt]); }
+      }
+      if constexpr (MODE == 2) {
+        // ---------------- silhouette score (ClusteringMetrics.pointSilhouetteCoefficient), one value per row
+        const bool v0 = t0 < rows_valid, v1 = t1 < rows_valid;
+        int a0l = v0 ? p.labels_in[row0 + t0] : -1, a1l = v1 ? p.labels_in[row0 + t1] : -1;
+        if (a0l >= k) a0l = -1;
+        if (a1l >= k) a1l = -1;
+        const double ninf = -__longlong_as_double(0x7ff0000000000000LL);
+        double own0 = ninf, own1 = ninf, oth0 = ninf, oth1 = ninf;
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const int j = 8 * nt + 2 * t + e;
+            if (j == a0l) own0 = s0[nt][e]; else oth0 = fmax(oth0, s0[nt][e]);
+            if (j == a1l) own1 = s1[nt][e]; else oth1 = fmax(oth1, s1[nt][e]);
+          }
+#pragma unroll
+        for (int msk = 1; msk <= 2; msk <<= 1) {
+          own0 = fmax(own0, shfl_xor_d(own0, msk)); own1 = fmax(own1, shfl_xor_d(own1, msk));
+          oth0 = fmax(oth0, shfl_xor_d(oth0, msk)); oth1 = fmax(oth1, shfl_xor_d(oth1, msk));
+          xx0 += shfl_xor_d(xx0, msk); xx1 += shfl_xor_d(xx1, msk);
+        }
+        if (t == 0) {
+          auto point = [&](bool valid, int a, double xx, double own, double oth, int64_t row) {
+            if (!valid || a < 0) return;
+            const double wv = has_w ? p.w[row] : 1.0;
+            const double nrm = sqrt(xx), sn = nrm * nrm;
+            const double NA = cn_s[k_pad + a];
+            double sil = 0.0;
+            if (NA != wv) {                                  // single-element clusters have silhouette 0
+              const double cur = fma(-2.0, own, sn) * NA / (NA - wv);
+              const double nb = fma(-2.0, oth, sn);
+              if (cur < nb) sil = 1.0 - (cur / nb); else if (cur > nb) sil = (nb / cur) - 1.0;
+            }
+            cost = fma(sil, wv, cost); xxs += wv;
+          };
+          point(v0, a0l, xx0, own0, oth0, row0 + t0);
+          point(v1, a1l, xx1, own1, oth1, row0 + t1);
+        }
+        return;
+      }
+      if constexpr (MODE == 1) {
+        // ---------------- silhouette statistics: labels and weights are given, phase 1 only supplied |x|^2
+#pragma unroll
+        for (int msk = 1; msk <= 2; msk <<= 1) { xx0 += shfl_xor_d(xx0, msk); xx1 += shfl_xor_d(xx1, msk); }
+        const bool v0 = t0 < rows_valid, v1 = t1 < rows_valid;
+        int l0 = v0 ? p.labels_in[row0 + t0] : -1, l1 = v1 ? p.labels_in[row0 + t1] : -1;
+        if (l0 >= k) l0 = -1;
+        if (l1 >= k) l1 = -1;
+        const double w0 = (v0 && has_w) ? p.w[row0 + t0] : 1.0, w1 = (v1 && has_w) ? p.w[row0 + t1] : 1.0;
+        const double n0 = sqrt(xx0), n1 = sqrt(xx1);           // squaredNorm = math.pow(Vectors.norm(features, 2.0), 2.0)
+        xx0 = n0 * n0; xx1 = n1 * n1;
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks) {
+          const int src = (t + 4 * (ks & 1)) * 4;
+          const int labt = __shfl_sync(0xffffffffu, (ks < 2) ? l0 : l1, src);
+          const double wt = __shfl_sync(0xffffffffu, (ks < 2) ? w0 : w1, src);
+          const double xxt = __shfl_sync(0xffffffffu, (ks < 2) ? xx0 : xx1, src);
+          double a2[NT];
+#pragma unroll
+          for (int mt = 0; mt < NT; ++mt) { a2[mt] = (labt == g + 8 * mt) ? wt : 0.0; wcnt[mt] += a2[mt]; }
+          const uint32_t xb = xs + b_frag + (uint32_t)(4 * (ks & 1)) * cstride + (uint32_t)((ks < 2) ? i0 : i1) * row_bytes;
+#pragma unroll
+          for (int nd = 0; nd < ND; ++nd) {
+            const bool ok = (nd < ND - 1) || (8 * nd + g < d);
+            const double b2 = ok ? lds_f64(xb + 64u * nd) : 0.0;
+#pragma unroll
+            for (int mt = 0; mt < NT; ++mt) dmma884(acc[mt][nd][0], acc[mt][nd][1], a2[mt], b2);
+          }
+          const double bx = g == 0 ? xxt : 0.0;                // extra feature tile: column 0 carries |x|^2 -> Psi
+#pragma unroll
+          for (int mt = 0; mt < NT; ++mt) dmma884(acc[mt][NDX - 1][0], acc[mt][NDX - 1][1], a2[mt], bx);
+        }
+        return;
       }
       // ---------------- argmax (lowest index wins ties)
       double b0 = s0[0][0], b1 = s1[0][0]; int j0 = 2 * t, j1 = 2 * t;
@@ -229,29 +314,32 @@ __global__ void __launch_bounds__(kMmaThreads) __maxnreg__(MAXREG) lloyd_mma_ker
     if (lane == 0) { red_s[warp] = cost; red_s[kComputeWarps + warp] = xxs; }
     // counts: every lane of a (g, *) group saw the same hits per k-step? no -- lane (g, t) counted row t only: fold over t
 #pragma unroll
-    for (int mt = 0; mt < NT; ++mt) { cnt[mt] += __shfl_xor_sync(0xffffffffu, cnt[mt], 1); cnt[mt] += __shfl_xor_sync(0xffffffffu, cnt[mt], 2); }
+    for (int mt = 0; mt < NT; ++mt) {
+      cnt[mt] += __shfl_xor_sync(0xffffffffu, cnt[mt], 1); cnt[mt] += __shfl_xor_sync(0xffffffffu, cnt[mt], 2);
+      if (MODE == 1) { wcnt[mt] += shfl_xor_d(wcnt[mt], 1); wcnt[mt] += shfl_xor_d(wcnt[mt], 2); } else wcnt[mt] = (double)cnt[mt];
+    }
     // sums: warps take turns adding their fragments into a [k_pad][d_pad8] buffer that aliases stage 0
     named_bar_sync(1, kComputeThreads);
     double* comb = reinterpret_cast<double*>(smem + L.x_off);       // [k_pad][8*ND] sums, then [k_pad] counts
-    const int ldc = 8 * ND;
+    const int ldc = 8 * NDX;
     double* ccnt = comb + k_pad * ldc;
     for (int w = 0; w < kComputeWarps; ++w) {
       if (warp == w) {
 #pragma unroll
         for (int mt = 0; mt < NT; ++mt) {
 #pragma unroll
-          for (int nd = 0; nd < ND; ++nd) {
+          for (int nd = 0; nd < NDX; ++nd) {
             double* c2 = comb + (8 * mt + g) * ldc + 8 * nd + 2 * t;
             if (w == 0) { c2[0] = acc[mt][nd][0]; c2[1] = acc[mt][nd][1]; }
             else { c2[0] += acc[mt][nd][0]; c2[1] += acc[mt][nd][1]; }
           }
-          if (t == 0) { if (w == 0) ccnt[8 * mt + g] = (double)cnt[mt]; else ccnt[8 * mt + g] += (double)cnt[mt]; }
+          if (t == 0) { if (w == 0) ccnt[8 * mt + g] = wcnt[mt]; else ccnt[8 * mt + g] += wcnt[mt]; }
         }
       }
       named_bar_sync(1, kComputeThreads);
     }
     for (int i = tid; i < k * d; i += kComputeThreads) { const int j = i / d, f = i - j * d; out[i] = comb[j * ldc + f]; }
-    for (int j = tid; j < k; j += kComputeThreads) out[(size_t)k * d + j] = ccnt[j];
+    for (int j = tid; j < k; j += kComputeThreads) { out[(size_t)k * d + j] = ccnt[j]; if (MODE == 1) out[P + 1 + j] = comb[j * ldc + 8 * ND]; }
     if (tid == 0) {
       double c = 0, x2 = 0;
 #pragma unroll
@@ -266,12 +354,15 @@ __global__ void __launch_bounds__(kMmaThreads) __maxnreg__(MAXREG) lloyd_mma_ker
     named_bar_sync(1, kComputeThreads);
     if (s_ticket == gridDim.x - 1) {
       __threadfence();
-      for (int i = tid; i < P + 1; i += kComputeThreads) {
+      const int i_lo = MODE == 2 ? P - 1 : 0, i_hi = MODE == 1 ? S : P + 1;
+      for (int i = i_lo + tid; i < i_hi; i += kComputeThreads) {
         double s = 0;
         for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(p.cta_partials + (size_t)b * S + i);
         if (i == P - 1 && xx_mode == 2) s = fmax(fma(-2.0, s, *p.xnorm2_sum), 0.0);  // cost = sum |x|^2 - 2 sum score
-        if (i < P) p.partial_out[i] = s;
-        else if (xx_mode == 1) *p.xnorm2_sum = s;
+        if (MODE == 2) p.partial_out[i - (P - 1)] = s;           // [sum s*w, sum w]
+        else if (i < P) p.partial_out[i] = s;
+        else if (i == P) { if (xx_mode == 1) *p.xnorm2_sum = s; }
+        else p.partial_out[i - 1] = s;                           // MODE 1: psi follows [sums][N][cost]
       }
       if (tid == 0) *p.counter = 0u;
       if (p.peer_bufs != nullptr) {                            // ranks > 1: sum the vector over NVLink peer memory right here
