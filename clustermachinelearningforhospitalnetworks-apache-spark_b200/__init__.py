@@ -11,7 +11,7 @@ from .table import Table, DeviceMatrix, Column, AssembledColumn  # noqa: F401
 from .ml import param, linalg, feature, clustering, evaluation, _kmeans_init  # noqa: F401
 from .ml.feature import VectorAssembler, StandardScaler, StandardScalerModel, SparkException  # noqa: F401
 from .ml.evaluation import ClusteringEvaluator  # noqa: F401
-from . import datagen  # noqa: F401
+from . import datagen, io  # noqa: F401
 from .ml.clustering import KMeans, KMeansModel, KMeansSummary  # noqa: F401
 from .ml.param import IllegalArgumentException  # noqa: F401
 from ._native import HkmError  # noqa: F401

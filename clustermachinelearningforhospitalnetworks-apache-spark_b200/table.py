@@ -98,10 +98,12 @@ def _as_column(v) -> Any:
                 valid = np.asarray(arr.is_valid())
                 if pa.types.is_floating(arr.type) or pa.types.is_integer(arr.type):
                     vals = arr.fill_null(0).to_numpy(zero_copy_only=False)
+                elif pa.types.is_timestamp(arr.type):
+                    vals = arr.to_numpy(zero_copy_only=False)
                 else:
                     vals = np.asarray(arr.to_pylist(), dtype=object)
                 return Column(vals, valid)
-            if pa.types.is_floating(arr.type) or pa.types.is_integer(arr.type) or pa.types.is_boolean(arr.type):
+            if pa.types.is_floating(arr.type) or pa.types.is_integer(arr.type) or pa.types.is_boolean(arr.type) or pa.types.is_timestamp(arr.type):
                 return Column(arr.to_numpy(zero_copy_only=False))
             return Column(np.asarray(arr.to_pylist(), dtype=object))
     except ImportError:

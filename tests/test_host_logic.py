@@ -163,3 +163,29 @@ def test_datagen_schema(hkm):
     X = datagen.hospital_matrix(2000, d=8, profiles=5, seed=1)
     assert X.shape == (2000, 8) and np.allclose(X.std(0, ddof=1), 1.0)
     assert np.array_equal(X, datagen.hospital_matrix(2000, d=8, profiles=5, seed=1))
+
+
+def test_ingest_csv_window_and_na_drop(hkm, tmp_path):
+    """The steps right before the hot path in the reference: CSV with the hospital schema (ref:L64-78), the
+    training time window (ref:L123-127) and na.drop (ref:L128)."""
+    from hkm_b200 import io
+    p = tmp_path / "hospitals"
+    p.mkdir()
+    (p / "a.csv").write_text(
+        "hospital_id,event_time,admission_count,current_occupancy,emergency_visits,seasonality_index,length_of_stay\n"
+        "h1,2025-03-31 21:59:59,10,100,3,1.0,4.5\n"
+        "h1,2025-03-31 22:00:00,11,101,4,1.1,5.5\n"
+        "h2,2025-03-31 22:30:00,12,,5,1.2,6.5\n"
+        "h2,2025-03-31 23:00:00,13,103,6,,7.5\n")
+    (p / "b.csv").write_text(
+        "hospital_id,event_time,admission_count,current_occupancy,emergency_visits,seasonality_index,length_of_stay\n"
+        "h3,2025-03-31 22:45:00,14,104,7,1.4,8.5\n"
+        "h3,2025-03-31 23:00:01,15,105,8,1.5,9.5\n")
+    t = io.read_csv(str(p))
+    assert t.columns == [n for n, _ in io.HOSPITAL_SCHEMA] and t.count() == 6
+    assert np.asarray(t["admission_count"].values).dtype == np.int32
+    w = io.between(t, "event_time", "2025-03-31 22:00:00", "2025-03-31 23:00:00")   # BETWEEN is inclusive on both ends
+    assert w.count() == 4 and w.to_numpy("hospital_id").tolist() == ["h1", "h2", "h2", "h3"]
+    clean = w.na.drop()
+    assert clean.count() == 2 and clean.to_numpy("admission_count").tolist() == [11, 14]
+    assert clean.to_numpy("length_of_stay").tolist() == [5.5, 8.5]
