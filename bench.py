@@ -26,6 +26,7 @@ sys.path.insert(0, ROOT)
 WORKLOADS = {
     # name: (rows per GPU, d, k, description)
     "cfg2": (10_000_000, 32, 8, "KMeans k=8, 10M rows x 32 features fp64, maxIter=20 (BASELINE configs[1])"),
+    "cfg3": (100_000_000, 64, 64, "KMeans k=64, 100M rows x 64 features fp64 (BASELINE configs[2]; tcgen05 screening variant); rows are the 1-GPU total, divided by N"),
     "cfg4": (125_000_000, 16, 16, "KMeans k=16, 125M rows x 16 features fp64 per GPU (BASELINE configs[3] shard)"),
     "cfg5": (5_000_000, 24, 16, "KMeans k=16, 5M rows x 24 features fp64 (BASELINE configs[4], mid sweep)"),
 }
@@ -200,6 +201,8 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
     n, d, k, desc = WORKLOADS[args.workload]
+    if args.workload == "cfg3":
+        n //= world                       # configs[2] is a fixed 100M-row table sharded over the GPUs (strong scaling)
     if args.rows:
         n = args.rows
 
@@ -309,13 +312,13 @@ def main():
     achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9
     line = {
         "metric": "kmeans_rows_iter_per_sec", "value": value, "unit": "rows*iter/s", "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong" if args.workload == "cfg3" else "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": args.workload, "description": desc, "rows_per_gpu": n, "d": d, "k": k,
                    "cache": f"inputs ({alg_bytes / 1e9:.2f} GB per GPU) are larger than the 126 MB L2; no flush needed",
                    "step": ("hkm_lloyd_step (assign + reduce + centre update in one launch, xnorm2 REUSE)" if world == 1 else ("hkm_lloyd_step_peer (one launch: pass + NVLink peer-memory sum of k*(d+1)+1 f64 + centre update)" if xchg is not None else "hkm_assign_reduce (xnorm2 REUSE) + NCCL allreduce(k*(d+1)+1 f64) + hkm_update_centers")) + ", convergence test off"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})", "kernel": "lloyd_mma_kernel (hkm_lloyd_mma.cuh)",
+                     "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})", "kernel": "lloyd_tc_kernel (hkm_lloyd_tc.cuh)" if (k > 32 and d > 32) else ("lloyd_mma_kernel (hkm_lloyd_mma.cuh)" if k <= 16 else "lloyd_pass_kernel (hkm_lloyd.cuh)"),
                      "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": alg_bytes, "traffic": ncu_traffic(args.workload)},
         "gpu_launches": (1 if (world == 1 or xchg is not None) else 2) * args.steps,
         "clocks": clocks,

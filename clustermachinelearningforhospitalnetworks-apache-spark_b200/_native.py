@@ -255,8 +255,10 @@ def assemble(cols, valids, n, shift=None, scale=None, skip_invalid=False):
         rc = load().hkm_assemble(ptrs, dts, vptrs, vk, d, n, _ptr(shift), _ptr(scale), int(skip_invalid), _ptr(X), _ptr(n_out),
                                  _ptr(invalid), _ptr(scratch), sb, _stream())
     _check(rc)
+    if not skip_invalid:
+        return X, n, invalid          # no host sync: every row is kept; `invalid` is a device counter the caller may read
     n_keep, bad = int(n_out.item()), int(invalid.item())
-    return (X[:n_keep] if skip_invalid else X), n_keep, bad
+    return X[:n_keep], n_keep, bad
 
 
 def count_invalid_rows(cols, valids, n) -> int:

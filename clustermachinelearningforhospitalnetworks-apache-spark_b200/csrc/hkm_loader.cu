@@ -12,7 +12,8 @@
 namespace hkm {
 
 constexpr int kMaxCols = 64;
-constexpr int kRowsPerBlock = 128;
+constexpr int kRowsPerBlockSmall = 128, kRowsPerBlockBig = 256;
+inline int assemble_rows_per_block(int d) { (void)d; return kRowsPerBlockSmall; }   // measured: 256-row blocks are slower (fewer resident blocks, longer per-thread column loop)
 
 struct ColDesc { const void* data; const void* valid; int dtype; int vkind; };
 struct AssembleParams {
@@ -44,19 +45,24 @@ __device__ __forceinline__ double load_col(const ColDesc& c, int64_t i, bool& ok
   return ok ? v : __longlong_as_double(0x7ff8000000000000LL);
 }
 
+// ROWS rows per block (256 threads): 256 -> one row per thread, every column read is a 1-2 KB contiguous burst;
+// 128 -> two columns in flight (used when 256 rows of d doubles would not leave room for two blocks per SM).
+template <int ROWS>
 __global__ void __launch_bounds__(256) assemble_kernel(const AssembleParams p) {
-  extern __shared__ double tile[];            // [kRowsPerBlock][ld], ld odd -> conflict-free transposed stores
-  __shared__ int s_rank[kRowsPerBlock];
-  __shared__ int s_bad[kRowsPerBlock];
-  __shared__ int s_wsum[4];
+  extern __shared__ double tile[];            // [ROWS][ld], ld odd -> conflict-free transposed stores
+  __shared__ int s_rank[ROWS];
+  __shared__ int s_bad[ROWS];
+  __shared__ int s_wsum[ROWS / 32];
+  constexpr int kRowsPerBlock = ROWS;
+  constexpr int STEP = 256 / ROWS;            // columns in flight per step
   const int d = p.d, ld = d | 1;
   const int64_t row0 = (int64_t)blockIdx.x * kRowsPerBlock;
   const int rows = (int)min((int64_t)kRowsPerBlock, p.n - row0);
-  const int t = threadIdx.x & (kRowsPerBlock - 1), half = threadIdx.x >> 7;  // two columns in flight per step
+  const int t = threadIdx.x & (kRowsPerBlock - 1), half = threadIdx.x / ROWS;
   if (threadIdx.x < kRowsPerBlock) s_bad[threadIdx.x] = 0;
   __syncthreads();
   int bad = 0;
-  for (int c = half; c < d; c += 2) {
+  for (int c = half; c < d; c += STEP) {
     if (t < rows) {
       bool ok;
       double v = load_col(p.cols[c], row0 + t, ok);
@@ -77,7 +83,9 @@ __global__ void __launch_bounds__(256) assemble_kernel(const AssembleParams p) {
     if ((threadIdx.x & 31) == 0) s_wsum[threadIdx.x >> 5] = __popc(m);
   }
   __syncthreads();
-  int nvalid = s_wsum[0] + s_wsum[1] + s_wsum[2] + s_wsum[3];
+  int nvalid = 0;
+#pragma unroll
+  for (int w = 0; w < ROWS / 32; ++w) nvalid += s_wsum[w];
   if (threadIdx.x < kRowsPerBlock) {
     for (int w = 0; w < (threadIdx.x >> 5); ++w) rank += s_wsum[w];
     s_rank[threadIdx.x] = valid ? rank : -1;
@@ -89,8 +97,15 @@ __global__ void __launch_bounds__(256) assemble_kernel(const AssembleParams p) {
   if (p.mode == 2) return;
   __syncthreads();
   if (p.mode == 0) {
+    // contiguous, coalesced write of rows*d doubles; (row, column) advance incrementally -- no division per element
     double* out = p.X + row0 * d;
-    for (int i = threadIdx.x; i < rows * d; i += blockDim.x) { const int rr = i / d, c = i - rr * d; out[i] = tile[rr * ld + c]; }
+    int rr = threadIdx.x / d, c = threadIdx.x - rr * d;
+    const int dr = blockDim.x / d, dc = blockDim.x - dr * d;
+    for (int i = threadIdx.x; i < rows * d; i += blockDim.x) {
+      out[i] = tile[rr * ld + c];
+      rr += dr; c += dc;
+      if (c >= d) { c -= d; ++rr; }
+    }
   } else {
     // compaction: scatter inside shared memory is avoided by reading through the rank table
     double* out = p.X + p.block_base[blockIdx.x] * d;
@@ -206,7 +221,7 @@ using namespace hkm;
 extern "C" {
 
 size_t hkm_assemble_scratch_bytes(int64_t n) {
-  const int64_t nb = (n + kRowsPerBlock - 1) / kRowsPerBlock;
+  const int64_t nb = (n + kRowsPerBlockSmall - 1) / kRowsPerBlockSmall;   // sized for the smaller block
   return (size_t)(2 * nb + 4) * sizeof(int64_t);
 }
 
@@ -219,20 +234,25 @@ int hkm_assemble(const void* const* cols_host, const int32_t* dtypes_host, const
   if (invalid_count == nullptr || n_out == nullptr || (X_out == nullptr && skip_invalid)) { set_error("hkm_assemble: null output"); return HKM_ERR_INVALID; }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   HKM_CUDA_TRY(cudaMemsetAsync(invalid_count, 0, sizeof(unsigned long long), st));
-  const int64_t nb = (n + kRowsPerBlock - 1) / kRowsPerBlock;
+  const int rpb = assemble_rows_per_block(d);
+  const int64_t nb = (n + rpb - 1) / rpb;
   p.X = X_out; p.shift = shift; p.scale = scale; p.invalid_count = invalid_count;
-  const size_t smem = (size_t)kRowsPerBlock * (d | 1) * sizeof(double);
+  const size_t smem = (size_t)rpb * (d | 1) * sizeof(double);
   static bool attr_done[64];
   int dev = 0; HKM_CUDA_TRY(cudaGetDevice(&dev));
   if (dev >= 64 || !attr_done[dev]) {
-    HKM_CUDA_TRY(cudaFuncSetAttribute(assemble_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kRowsPerBlock * (kMaxCols | 1) * (int)sizeof(double)));
+    HKM_CUDA_TRY(cudaFuncSetAttribute(assemble_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * (kMaxCols | 1) * (int)sizeof(double)));
+    HKM_CUDA_TRY(cudaFuncSetAttribute(assemble_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, 256 * 41 * (int)sizeof(double)));
     if (dev < 64) attr_done[dev] = true;
   }
+  auto launch = [&](const AssembleParams& q) {
+    if (rpb == 256) assemble_kernel<256><<<(unsigned)nb, 256, smem, st>>>(q); else assemble_kernel<128><<<(unsigned)nb, 256, smem, st>>>(q);
+  };
   if (n == 0) { HKM_CUDA_TRY(cudaMemsetAsync(n_out, 0, sizeof(int64_t), st)); return HKM_OK; }
   if (nb > 0x7fffffff) { set_error("hkm_assemble: too many rows for one launch"); return HKM_ERR_UNSUPPORTED; }
   if (!skip_invalid) {
     p.mode = X_out == nullptr ? 2 : 0;   // no matrix asked for: only count the invalid rows
-    assemble_kernel<<<(unsigned)nb, 256, smem, st>>>(p);
+    launch(p);
     HKM_CUDA_TRY(cudaGetLastError());
     store_i64_kernel<<<1, 1, 0, st>>>(n_out, n);   // every row is kept
     HKM_CUDA_TRY(cudaGetLastError());
@@ -242,12 +262,12 @@ int hkm_assemble(const void* const* cols_host, const int32_t* dtypes_host, const
   int64_t* counts = reinterpret_cast<int64_t*>(scratch);
   int64_t* base = counts + nb;
   p.mode = 2; p.block_valid = counts; p.invalid_count = invalid_count;
-  assemble_kernel<<<(unsigned)nb, 256, smem, st>>>(p);
+  launch(p);
   HKM_CUDA_TRY(cudaGetLastError());
   scan_blocks_kernel<<<1, 1024, 0, st>>>(counts, nb, base, n_out);
   HKM_CUDA_TRY(cudaGetLastError());
   p.mode = 1; p.block_valid = nullptr; p.block_base = base; p.invalid_count = nullptr;
-  assemble_kernel<<<(unsigned)nb, 256, smem, st>>>(p);
+  launch(p);
   HKM_CUDA_TRY(cudaGetLastError());
   return HKM_OK;
 }

@@ -68,7 +68,7 @@ def loader(n, d):
     in_bytes = sum(c.element_size() for c in cols) * n
     shift = torch.randn(d, dtype=torch.float64, device="cuda"); scale = torch.rand(d, dtype=torch.float64, device="cuda") + 0.5
     ms = timeit(lambda: N.assemble(cols, valids, n, shift, scale), iters=5, warm=2)
-    report("assemble (+fused standardise)", f"{n} rows, {d} cols (int32/f64 mix)", in_bytes + n * d * 8, ms, "includes torch.empty of the output and two .item() syncs")
+    report("assemble (+fused standardise)", f"{n} rows, {d} cols (int32/f64 mix)", in_bytes + n * d * 8, ms, "includes torch.empty of the output")
     pivot = torch.stack([c[0].double() for c in cols])
     ms = timeit(lambda: N.column_moments(cols, valids, n, pivot), iters=5, warm=2)
     report("column_moments", f"{n} rows, {d} cols", in_bytes, ms)
