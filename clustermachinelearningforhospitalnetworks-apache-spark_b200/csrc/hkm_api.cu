@@ -102,7 +102,7 @@ extern "C" {
 const char* hkm_last_error(void) { return g_err; }
 int hkm_version(void) { return 100; }
 int hkm_max_k(void) { return 64; }
-int hkm_max_d(void) { return 128; }
+int hkm_max_d(void) { return 96; }
 
 size_t hkm_assign_reduce_scratch_bytes(int d, int k) {
   if (d < 1 || k < 1) return 0;

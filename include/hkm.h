@@ -57,7 +57,7 @@ typedef struct hkm_lloyd_state {
 HKM_API const char* hkm_last_error(void);
 HKM_API int hkm_version(void);
 
-/* Largest k and d the fp64 DMMA kernels accept. */
+/* Largest k and d the kernels accept (a (d, k) pair whose tile ring does not fit in shared memory is refused with HKM_ERR_UNSUPPORTED). */
 HKM_API int hkm_max_k(void);
 HKM_API int hkm_max_d(void);
 
