@@ -18,7 +18,7 @@ EXPORTS = (
     "hkm_assign_reduce_scratch_bytes", "hkm_assign_reduce", "hkm_update_centers", "hkm_lloyd_step", "hkm_lloyd_step_peer", "hkm_peer_exchange_bytes",
     "hkm_kmpar_scratch_bytes", "hkm_kmpar_cost_update", "hkm_kmpar_sample", "hkm_kmpar_strip_rows", "hkm_closest_counts",
     "hkm_silhouette_stats", "hkm_silhouette_score",
-    "hkm_assemble_scratch_bytes", "hkm_assemble", "hkm_moments_scratch_bytes", "hkm_moments", "hkm_column_moments", "hkm_scale_rows",
+    "hkm_assemble_scratch_bytes", "hkm_assemble", "hkm_moments_scratch_bytes", "hkm_moments", "hkm_column_moments", "hkm_scale_rows", "hkm_normalize_rows",
 )
 
 _lib = None
@@ -68,6 +68,7 @@ def load() -> ctypes.CDLL:
         L.hkm_moments.argtypes = [vp, i64, i32, vp, vp, vp, sz, vp]
         L.hkm_column_moments.argtypes = [vp, vp, vp, vp, i32, i64, vp, vp, vp, sz, vp]
         L.hkm_scale_rows.argtypes = [vp, vp, i64, i32, vp, vp, vp]
+        L.hkm_normalize_rows.argtypes = [vp, vp, i64, i32, vp, vp]
         L.hkm_silhouette_stats.argtypes = [vp, vp, vp, i64, i32, i32, vp, vp, sz, vp]
         L.hkm_silhouette_score.argtypes = [vp, vp, vp, i64, i32, i32, vp, vp, vp, vp, sz, vp]
         _lib = L
@@ -307,3 +308,14 @@ def scale_rows(X, shift, scale):
         rc = load().hkm_scale_rows(_ptr(X), _ptr(out), X.shape[0], X.shape[1], _ptr(shift), _ptr(scale), _stream())
     _check(rc)
     return out
+
+
+def normalize_rows(X):
+    """hkm_normalize_rows -> (X_hat, number of zero-length rows)."""
+    require_cuda(X, "X", torch.float64)
+    out = torch.empty_like(X)
+    zero = torch.zeros(1, dtype=torch.int64, device=X.device)
+    with torch.cuda.device(X.device):
+        rc = load().hkm_normalize_rows(_ptr(X), _ptr(out), X.shape[0], X.shape[1], _ptr(zero), _stream())
+    _check(rc)
+    return out, int(zero.item())

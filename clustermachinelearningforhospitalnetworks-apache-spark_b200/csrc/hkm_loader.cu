@@ -200,6 +200,25 @@ __global__ void __launch_bounds__(256) scale_rows_kernel(const double* __restric
   }
 }
 
+// x_hat = x * (1 / |x|_2) per row (cosine distance measure: Spark normalises every vector before use).
+// One warp per row; rows of zero length are counted (Spark: "Cosine distance is not defined for zero-length vectors").
+__global__ void __launch_bounds__(256) normalize_rows_kernel(const double* __restrict__ in, double* __restrict__ out, int64_t n, int d,
+                                                            unsigned long long* __restrict__ zero_rows) {
+  const int lane = threadIdx.x & 31;
+  for (int64_t r = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5); r < n; r += (int64_t)gridDim.x * 8) {
+    double v[3], s = 0;
+#pragma unroll
+    for (int e = 0; e < 3; ++e) { const int f = lane + 32 * e; v[e] = f < d ? in[r * d + f] : 0.0; s = fma(v[e], v[e], s); }
+#pragma unroll
+    for (int m = 16; m >= 1; m >>= 1) s += shfl_xor_d(s, m);
+    const double nrm = sqrt(s);
+    if (nrm == 0.0 && lane == 0) atomicAdd(zero_rows, 1ull);
+    const double inv = nrm > 0.0 ? 1.0 / nrm : 0.0;
+#pragma unroll
+    for (int e = 0; e < 3; ++e) { const int f = lane + 32 * e; if (f < d) out[r * d + f] = v[e] * inv; }
+  }
+}
+
 static int fill_params(AssembleParams& p, const void* const* cols_host, const int32_t* dtypes_host, const void* const* valid_host,
                        const int32_t* vkind_host, int d, int64_t n, const char* who) {
   if (d < 1 || d > kMaxCols || n < 0 || cols_host == nullptr || dtypes_host == nullptr) { set_error("%s: bad d/n/columns (d <= %d)", who, kMaxCols); return HKM_ERR_INVALID; }
@@ -300,6 +319,16 @@ int hkm_column_moments(const void* const* cols_host, const int32_t* dtypes_host,
   moments_cols_kernel<<<dim3(gx, d), 256, 0, st>>>(p, pivot, reinterpret_cast<double*>(scratch));
   HKM_CUDA_TRY(cudaGetLastError());
   moments_fold_kernel<<<1, 256, 0, st>>>(reinterpret_cast<double*>(scratch), gx, d, out2d);
+  HKM_CUDA_TRY(cudaGetLastError());
+  return HKM_OK;
+}
+
+int hkm_normalize_rows(const double* X_in, double* X_out, int64_t n, int d, unsigned long long* zero_rows, void* stream) {
+  if (d < 1 || d > 96 || n < 0 || zero_rows == nullptr || (n > 0 && (X_in == nullptr || X_out == nullptr))) { set_error("hkm_normalize_rows: bad arguments (d <= 96)"); return HKM_ERR_INVALID; }
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  HKM_CUDA_TRY(cudaMemsetAsync(zero_rows, 0, sizeof(unsigned long long), st));
+  if (n == 0) return HKM_OK;
+  normalize_rows_kernel<<<sm_count() * 8, 256, 0, st>>>(X_in, X_out, n, d, zero_rows);
   HKM_CUDA_TRY(cudaGetLastError());
   return HKM_OK;
 }

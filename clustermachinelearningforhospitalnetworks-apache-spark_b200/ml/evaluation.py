@@ -41,8 +41,6 @@ class ClusteringEvaluator(Params):
     def evaluate(self, dataset, params=None) -> float:
         if params:
             return self.copy(params).evaluate(dataset)
-        if self.getDistanceMeasure() != "squaredEuclidean":
-            raise IllegalArgumentException("distanceMeasure='cosine' is not built yet on the CUDA path (SURVEY 8f-4)")
         t = Table.wrap(dataset)
         dev = RT.device()
         X = features_to_device(t[self.getFeaturesCol()], dev).X
@@ -56,15 +54,25 @@ class ClusteringEvaluator(Params):
             wc = t[self.getWeightCol()]
             wv = wc.values if isinstance(wc.values, torch.Tensor) else torch.as_tensor(wc.values)
             w = wv.to(device=dev, dtype=torch.float64).contiguous()
-        return silhouette(X, lab, w)
+        return silhouette(X, lab, w, cosine=self.getDistanceMeasure() == "cosine")
 
 
 add_accessors(ClusteringEvaluator, ["predictionCol", "featuresCol", "metricName", "distanceMeasure", "weightCol"])
 
 
-def silhouette(X: torch.Tensor, labels: torch.Tensor, w=None) -> float:
-    """Squared-Euclidean silhouette of device-resident rows/labels (global over torch.distributed ranks)."""
+def silhouette(X: torch.Tensor, labels: torch.Tensor, w=None, cosine: bool = False) -> float:
+    """Silhouette of device-resident rows/labels (global over torch.distributed ranks).
+
+    squared Euclidean: Spark's closed form D(x,G) = |x|^2 + Psi_G/N_G - 2 x.Y_G/N_G.
+    cosine (CosineSilhouette): D(x,G) = 1 - x_hat . Omega_G / N_G on normalised rows x_hat -- the same two passes run on
+    x_hat with Y := Omega/2 and Psi := 0, since |x_hat|^2 - 2 x_hat.(Omega/2N) = 1 - x_hat.Omega/N."""
     n, d = X.shape
+    if cosine:
+        X, zero_rows = N.normalize_rows(X)
+        tot = torch.tensor([zero_rows], dtype=torch.int64, device=X.device)
+        RT.all_reduce_sum(tot)
+        if int(tot.item()):
+            raise IllegalArgumentException("requirement failed: Cosine distance is not defined for zero-length vectors.")
     kmax = torch.zeros(1, dtype=torch.int64, device=X.device)
     if n:
         if int(labels.min()) < 0:
@@ -84,6 +92,9 @@ def silhouette(X: torch.Tensor, labels: torch.Tensor, w=None) -> float:
     present = int((stats[k * d:k * d + k] > 0).sum().item())
     if present < 2:
         raise AssertionError("requirement failed: Number of clusters must be greater than one.")
+    if cosine:
+        stats[:k * d] *= 0.5
+        stats[k * d + k + 1:] = 0.0
     work = torch.empty(k * d + 2 * k, dtype=torch.float64, device=X.device)
     out2 = torch.zeros(2, dtype=torch.float64, device=X.device)
     N.silhouette_score(X, labels, k, stats, work, out2, scratch, weights=w)

@@ -257,6 +257,10 @@ HKM_API int hkm_column_moments(const void* const* cols_host, const int32_t* dtyp
                                const int32_t* vkind_host, int d, int64_t n, const double* pivot, double* out2d,
                                void* scratch, size_t scratch_bytes, void* stream);
 
+/* Cosine distance measure (ClusteringEvaluator distanceMeasure="cosine"): out = x / |x|_2 per row (multiply by the
+ * reciprocal norm); *zero_rows = rows of zero length, for which Spark refuses the cosine distance.  In place allowed. */
+HKM_API int hkm_normalize_rows(const double* X_in, double* X_out, int64_t n, int d, unsigned long long* zero_rows, void* stream);
+
 /* StandardScalerModel.transform on an existing matrix: out = (in - shift) * scale (in place allowed). */
 HKM_API int hkm_scale_rows(const double* X_in, double* X_out, int64_t n, int d, const double* shift, const double* scale,
                            void* stream);

@@ -79,3 +79,22 @@ def test_full_size_invariants(hkm):
     assert -1.0 <= s <= 1.0 and s > 0.3
     assert silhouette(X, perm[lab.long()]) == pytest.approx(s, abs=1e-12)
     assert silhouette(X, lab) == s                                   # bit-stable
+
+
+def test_cosine_silhouette_iris_constant_and_oracle(hkm, oracle):
+    """distanceMeasure='cosine' (SURVEY 8f-4): Spark's ClusteringEvaluatorSuite constant on iris, and the oracle."""
+    from hkm_b200.ml.evaluation import ClusteringEvaluator
+    a = np.loadtxt(os.path.join(GOLD, "iris_uci.csv"), delimiter=",")
+    ev = ClusteringEvaluator(distanceMeasure="cosine")
+    s = ev.evaluate({"features": np.ascontiguousarray(a[:, :4]), "prediction": a[:, 4].astype(np.int32)})
+    assert s == pytest.approx(KAT["iris"]["silhouette_cosine"], rel=KAT["iris"]["rel_tol"])
+    rng = np.random.default_rng(4)
+    X = rng.normal(size=(30_000, 24)) + rng.integers(0, 6, size=(30_000, 1)) * 1.5 + 0.5
+    lab = rng.integers(0, 6, size=30_000).astype(np.int32)
+    w = rng.uniform(0.5, 2.0, size=30_000)
+    assert ev.evaluate({"features": X, "prediction": lab}) == pytest.approx(oracle.silhouette(X, lab, distance="cosine"), abs=1e-10)
+    assert ClusteringEvaluator(distanceMeasure="cosine", weightCol="w").evaluate({"features": X, "prediction": lab, "w": w}) == \
+        pytest.approx(oracle.silhouette(X, lab, w=w, distance="cosine"), abs=1e-10)
+    X[7] = 0.0
+    with pytest.raises(hkm.IllegalArgumentException, match="zero-length"):
+        ev.evaluate({"features": X, "prediction": lab})
