@@ -163,10 +163,24 @@ def run_reference(args):
                          "sample": f"{n} of {n_full} rows x {d}, {args.steps} Lloyd passes; CPU restatement of the MLlib row solver (not Spark: no JVM here)"},
         "e2e": {"value": val, "unit": "rows*iter/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_JSON_FD = None
+
+
+def emit(line):
+    """The ONE JSON line goes to the real stdout; everything else any library prints (NCCL's version banner, warnings)
+    was sent to stderr by main(), so stdout holds exactly one line."""
+    sys.stdout.flush()
+    os.write(_JSON_FD if _JSON_FD is not None else 1, (json.dumps(line) + "\n").encode())
 
 
 def main():
+    global _JSON_FD
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=100)
@@ -342,7 +356,7 @@ def main():
         line["cpu_baseline"] = {"value": ns * reps / dt, "unit": "rows*iter/s", "cores": threads, "kind": "port",
                                 "sample": f"{reps} Lloyd passes over {ns} x {d} rows (k={k}); C/OpenMP restatement of the MLlib row solver "
                                           "(Spark local[N] cannot run here: no JVM/pyspark)"}
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
