@@ -28,17 +28,17 @@ static int launch_regb(const LloydParams& p, const LaunchPlan& pl, int grid, cud
   constexpr int LPR = KS_T <= 2 ? 8 : (KS_T <= 4 ? 16 : 32);
   constexpr int FPL = KS_T <= 8 ? 1 : 2;
   // 16 warps/SM = 4 per scheduler partition (16K registers each) -> 128 regs when two CTAs share an SM
-  constexpr int MAXREG = (KS_T * NT <= 16 && NT <= 2) ? 128 : 255;
+  constexpr int MAXREG = ((KS_T * NT <= 16 && NT <= 2) || (NT >= 3 && NT <= 6)) ? 128 : 255;
   return launch_lloyd<KS_T, NT, LPR, FPL, MAXREG>(p, pl, grid, st);
 }
 template <int NT, int MODE = 0>
 static int launch_smemb(const LloydParams& p, const LaunchPlan& pl, int grid, cudaStream_t st) {
   const int d = p.d;
-  constexpr int MINB = NT <= 2 ? 128 : 255;
+  constexpr int MINB = NT <= 6 ? 128 : 255;   // two CTAs per SM (d <= 32 rings fit twice): 16 warps hide the phase latencies
   if (d <= 8) return launch_lloyd<0, NT, 8, 1, MINB, MODE>(p, pl, grid, st);
   if (d <= 16) return launch_lloyd<0, NT, 16, 1, MINB, MODE>(p, pl, grid, st);
   if (d <= 32) return launch_lloyd<0, NT, 32, 1, MINB, MODE>(p, pl, grid, st);
-  if (d <= 64) return launch_lloyd<0, NT, 32, 2, MINB, MODE>(p, pl, grid, st);
+  if (d <= 64) return launch_lloyd<0, NT, 32, 2, (NT <= 2 ? 128 : 255), MODE>(p, pl, grid, st);
   if (d <= 96) return launch_lloyd<0, NT, 32, 3, 255, MODE>(p, pl, grid, st);
   return launch_lloyd<0, NT, 32, 4, 255, MODE>(p, pl, grid, st);
 }
@@ -94,8 +94,8 @@ int HKM_CAT(dispatch_lloyd_nt, HKM_NT)(const LloydParams& p, const LaunchPlan& p
 #undef HKM_MMA
     }
   }
-  // register-resident B fragments while KS*NT doubles per lane stay affordable
-#define HKM_REGB(KS) if constexpr (KS * NT <= 32) { if (ks == KS) return launch_regb<KS, NT>(p, pl, grid, st); }
+  // register-resident B fragments while KS*NT doubles per lane stay affordable (24 under the 128-register cap of NT 3..6)
+#define HKM_REGB(KS) if constexpr (KS * NT <= ((NT >= 3 && NT <= 6) ? 24 : 32)) { if (ks == KS) return launch_regb<KS, NT>(p, pl, grid, st); }
 #ifndef HKM_DEV_FAST
   HKM_REGB(1) HKM_REGB(2) HKM_REGB(3) HKM_REGB(4) HKM_REGB(5) HKM_REGB(6) HKM_REGB(7)
 #endif
