@@ -15,7 +15,7 @@ SO_PATH = os.path.join(_HERE, "csrc", "libhkm.so")
 
 EXPORTS = (
     "hkm_last_error", "hkm_version", "hkm_max_k", "hkm_max_d",
-    "hkm_assign_reduce_scratch_bytes", "hkm_assign_reduce", "hkm_update_centers", "hkm_lloyd_step", "hkm_lloyd_step_peer", "hkm_peer_exchange_bytes",
+    "hkm_assign_reduce_scratch_bytes", "hkm_assign_reduce", "hkm_update_centers", "hkm_update_centers_cosine", "hkm_lloyd_step", "hkm_lloyd_step_peer", "hkm_peer_exchange_bytes",
     "hkm_kmpar_scratch_bytes", "hkm_kmpar_cost_update", "hkm_kmpar_sample", "hkm_kmpar_strip_rows", "hkm_closest_counts",
     "hkm_silhouette_stats", "hkm_silhouette_score",
     "hkm_assemble_scratch_bytes", "hkm_assemble", "hkm_moments_scratch_bytes", "hkm_moments", "hkm_column_moments", "hkm_scale_rows", "hkm_normalize_rows",
@@ -50,6 +50,7 @@ def load() -> ctypes.CDLL:
         L.hkm_assign_reduce_scratch_bytes.argtypes = [i32, i32]
         L.hkm_assign_reduce.argtypes = [vp, i64, i32, vp, i32, vp, vp, vp, vp, vp, i32, vp, i32, vp, sz, vp]
         L.hkm_update_centers.argtypes = [vp, i32, i32, vp, ctypes.c_double, vp, vp]
+        L.hkm_update_centers_cosine.argtypes = [vp, i32, i32, vp, ctypes.c_double, vp, vp]
         L.hkm_lloyd_step.argtypes = [vp, i64, i32, vp, i32, vp, vp, vp, i32, ctypes.c_double, vp, vp, sz, vp]
         L.hkm_peer_exchange_bytes.restype = sz
         L.hkm_peer_exchange_bytes.argtypes = [i32]
@@ -156,10 +157,11 @@ def lloyd_step_peer(X, C, partial, tol: float, state, scratch, xchg, weights=Non
     _check(rc)
 
 
-def update_centers(partial, C, tol: float, state):
+def update_centers(partial, C, tol: float, state, cosine: bool = False):
     k, d = C.shape
+    fn = load().hkm_update_centers_cosine if cosine else load().hkm_update_centers
     with torch.cuda.device(C.device):
-        rc = load().hkm_update_centers(_ptr(partial), k, d, _ptr(C), float(tol), _ptr(state), _stream())
+        rc = fn(_ptr(partial), k, d, _ptr(C), float(tol), _ptr(state), _stream())
     _check(rc)
 
 

@@ -59,6 +59,44 @@ __global__ void update_centers_kernel(const double* __restrict__ partial, int k,
   update_centers_body(partial, k, d, C, tol2, state, s_shift, threadIdx.x);
 }
 
+
+// CosineDistanceMeasure.centroid / isCenterConverged on partial sums of UNIT rows: new_j = normalise(sums_j * (1/w_j)),
+// converged iff every updated centre has 1 - old.new / |old| <= tol (not squared).  The pass ran the Euclidean
+// machinery on unit vectors, where |x - c|^2 = 2 (1 - x.c): cost = partial cost / 2.
+__global__ void update_centers_cosine_kernel(const double* __restrict__ partial, int k, int d, double* __restrict__ C, double tol,
+                                             hkm_lloyd_state* __restrict__ state) {
+  if (state->converged != 0) return;
+  __shared__ double s_shift[64];
+  const int tid = threadIdx.x;
+  double shift = -1.0;
+  if (tid < k) {
+    const double wsum = partial[(size_t)k * d + tid];
+    if (wsum > 0) {
+      const double inv = 1.0 / wsum;
+      double nn = 0, oo = 0;
+      for (int f = 0; f < d; ++f) { const double v = partial[(size_t)tid * d + f] * inv; nn = fma(v, v, nn); const double o = C[(size_t)tid * d + f]; oo = fma(o, o, oo); }
+      const double inv2 = 1.0 / sqrt(nn), on = sqrt(oo);
+      double dot = 0;
+      for (int f = 0; f < d; ++f) {
+        const double nc = partial[(size_t)tid * d + f] * inv * inv2;
+        dot = fma(C[(size_t)tid * d + f], nc, dot);
+        C[(size_t)tid * d + f] = nc;
+      }
+      shift = fmax(1.0 - dot / on, 0.0);
+    }
+  }
+  if (tid < 64) s_shift[tid] = shift;
+  __syncthreads();
+  if (tid == 0) {
+    double mx = -1.0;
+    for (int i = 0; i < k; ++i) mx = fmax(mx, s_shift[i]);
+    state->cost = 0.5 * partial[(size_t)k * d + k];
+    state->iter += 1;
+    state->max_shift2 = mx < 0 ? 0.0 : mx;
+    state->converged = (mx <= tol) ? 1 : 0;
+  }
+}
+
 }  // namespace hkm
 
 namespace hkm {
@@ -153,6 +191,13 @@ int hkm_lloyd_step_peer(const double* X, int64_t n, int d, double* C_inout, int 
 int hkm_update_centers(const double* partial, int k, int d, double* C_inout, double tol, hkm_lloyd_state* state, void* stream) {
   if (partial == nullptr || C_inout == nullptr || state == nullptr || k < 1 || k > hkm_max_k() || d < 1) { set_error("hkm_update_centers: bad arguments"); return HKM_ERR_INVALID; }
   update_centers_kernel<<<1, 64, 0, reinterpret_cast<cudaStream_t>(stream)>>>(partial, k, d, C_inout, tol < 0 ? -1.0 : tol * tol, state);
+  HKM_CUDA_TRY(cudaGetLastError());
+  return HKM_OK;
+}
+
+int hkm_update_centers_cosine(const double* partial, int k, int d, double* C_inout, double tol, hkm_lloyd_state* state, void* stream) {
+  if (partial == nullptr || C_inout == nullptr || state == nullptr || k < 1 || k > hkm_max_k() || d < 1) { set_error("hkm_update_centers_cosine: bad arguments"); return HKM_ERR_INVALID; }
+  update_centers_cosine_kernel<<<1, 64, 0, reinterpret_cast<cudaStream_t>(stream)>>>(partial, k, d, C_inout, tol < 0 ? -1.0 : tol, state);
   HKM_CUDA_TRY(cudaGetLastError());
   return HKM_OK;
 }

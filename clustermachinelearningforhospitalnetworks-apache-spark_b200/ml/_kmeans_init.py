@@ -83,9 +83,18 @@ def init_random(X: torch.Tensor, layout: PartitionLayout, k: int, seed: int) -> 
     return SR.distinct_rows(_gather_global_rows(X, layout, idx))
 
 
+def _unit(C: np.ndarray) -> np.ndarray:
+    return C * (1.0 / np.sqrt((C * C).sum(axis=1)))[:, None]
+
+
 def init_kmeans_parallel(X: torch.Tensor, layout: PartitionLayout, k: int, init_steps: int, seed: int,
-                         first_idx: int = -1, debug: dict | None = None) -> np.ndarray:
+                         first_idx: int = -1, debug: dict | None = None, X_unit: torch.Tensor | None = None) -> np.ndarray:
+    """X_unit (cosine measure): the distance passes run on the unit rows against unit candidates -- there
+    |x - c|^2 = 2 * cosine distance, and the sampling rule 2*k*cost/sum(cost) does not see the factor; the candidates
+    themselves stay RAW rows and LocalKMeans stays Euclidean, as in Spark."""
     dev = X.device
+    Xd = X if X_unit is None else X_unit
+    prep = (lambda c: c) if X_unit is None else _unit
     n, d = X.shape
     seed2 = SR.XORShiftRandom(seed).next_int()
     if first_idx < 0:
@@ -112,7 +121,7 @@ def init_kmeans_parallel(X: torch.Tensor, layout: PartitionLayout, k: int, init_
 
     for step in range(init_steps):
         if len(new):
-            N.kmpar_cost_update(X, torch.from_numpy(np.ascontiguousarray(new)).to(dev), costs, sum_costs, scratch)
+            N.kmpar_cost_update(Xd, torch.from_numpy(np.ascontiguousarray(prep(new))).to(dev), costs, sum_costs, scratch)
             RT.all_reduce_sum(sum_costs)
         # else: no new centres -> costs and their sum are unchanged (pointCost over nothing is +inf)
         while True:
@@ -137,7 +146,7 @@ def init_kmeans_parallel(X: torch.Tensor, layout: PartitionLayout, k: int, init_
     labels_work = torch.empty(n, dtype=torch.int32, device=dev)
     mind2_work = torch.empty(n, dtype=torch.float64, device=dev)
     counts = torch.zeros(m, dtype=torch.int64, device=dev)
-    N.closest_counts(X, torch.from_numpy(np.ascontiguousarray(cand)).to(dev), labels_work, mind2_work, counts)
+    N.closest_counts(Xd, torch.from_numpy(np.ascontiguousarray(prep(cand))).to(dev), labels_work, mind2_work, counts)
     RT.all_reduce_sum(counts)
     weights = counts.cpu().numpy().astype(np.float64)
     if debug is not None:

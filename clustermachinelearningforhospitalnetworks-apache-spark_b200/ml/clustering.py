@@ -141,10 +141,18 @@ class KMeansModel(_KMeansParams):
             self._dev_centers = torch.from_numpy(self._centers).to(dev)
         return self._dev_centers
 
+    def _pass_centers(self, dev) -> torch.Tensor:
+        """Centres as the data passes take them: unit length under the cosine measure."""
+        if self.getDistanceMeasure() != "cosine":
+            return self._centers_on(dev)
+        return torch.from_numpy(_unit_centers(self._centers)).to(dev)
+
     def _predict_matrix(self, X: torch.Tensor) -> torch.Tensor:
         labels = torch.empty(X.shape[0], dtype=torch.int32, device=X.device)
         if X.shape[0]:
-            N.assign_reduce(X, self._centers_on(X.device), labels=labels, do_reduce=False)
+            if self.getDistanceMeasure() == "cosine":
+                X = _unit_rows(X)
+            N.assign_reduce(X, self._pass_centers(X.device), labels=labels, do_reduce=False)
         return labels
 
     def transform(self, dataset, params=None) -> Table:
@@ -237,8 +245,7 @@ class KMeans(_KMeansParams):
 
     def _fit(self, table: Table) -> KMeansModel:
         from . import _kmeans_init as KI
-        if self.getDistanceMeasure() != "euclidean":
-            raise IllegalArgumentException("distanceMeasure='cosine' is not built yet on the CUDA path (SURVEY 8f-4)")
+        cosine = self.getDistanceMeasure() == "cosine"
         dev = RT.device()
         fm = features_to_device(table[self.getFeaturesCol()], dev)
         X = fm.X
@@ -254,18 +261,23 @@ class KMeans(_KMeansParams):
             raise N.HkmError(f"d={d}, k={k} is outside the built CUDA kernels (d<={N.load().hkm_max_d()}, k<={N.load().hkm_max_k()})")
 
         layout = KI.PartitionLayout.build(sizes, rank, self.numPartitions)
+        # cosine: every data pass runs on the unit rows (one extra resident copy); the initialisers still pick RAW rows
+        Xp = _unit_rows(X) if cosine else X
         if self.initialCenters is not None:
             C0 = SR.distinct_rows(self.initialCenters)
         elif self.getInitMode() == "random":
             C0 = KI.init_random(X, layout, k, self.getSeed())
         else:
-            C0 = KI.init_kmeans_parallel(X, layout, k, self.getInitSteps(), self.getSeed())
-        centers, num_iter, cost = lloyd(X, C0, w, self.getMaxIter(), self.getTol())
+            C0 = KI.init_kmeans_parallel(X, layout, k, self.getInitSteps(), self.getSeed(), X_unit=Xp if cosine else None)
+        centers, num_iter, cost = lloyd(Xp, _unit_centers(C0) if cosine else C0, w, self.getMaxIter(), self.getTol(), cosine=cosine)
+        if num_iter == 0:
+            centers = C0          # maxIter = 0: Spark hands back the initial centres as drawn (raw rows)
 
         model = KMeansModel(centers)
         self._copyValues(model)
         # summary: one more pass, as ml.clustering.KMeans.fit does with model.transform(dataset)
-        pred, sizes_k = _predict_and_count(X, model._centers_on(dev))
+        pred, sizes_k = _predict_and_count(Xp, model._pass_centers(dev))
+        del Xp
         pred_table = table.withColumn(self.getFeaturesCol(), fm).withColumn(self.getPredictionCol(), Column(pred))
         model._summary = KMeansSummary(pred_table, self.getPredictionCol(), self.getFeaturesCol(), self.getK(), num_iter, cost, sizes_k)
         return model
@@ -275,7 +287,25 @@ add_accessors(KMeans, ["featuresCol", "predictionCol", "k", "initMode", "initSte
                        "distanceMeasure", "weightCol", "solver", "maxBlockSizeInMB"])
 
 
-def lloyd(X: torch.Tensor, C0: np.ndarray, w: Optional[torch.Tensor], max_iter: int, tol: float, check_every: int = 4):
+def _unit_rows(X: torch.Tensor) -> torch.Tensor:
+    """x / |x|_2 per row; Spark's CosineDistanceMeasure refuses zero-length vectors (global over ranks)."""
+    Xu, zero_rows = N.normalize_rows(X)
+    tot = torch.tensor([zero_rows], dtype=torch.int64, device=X.device)
+    RT.all_reduce_sum(tot)
+    if int(tot.item()):
+        raise IllegalArgumentException("requirement failed: Cosine distance is not defined for zero-length vectors.")
+    return Xu
+
+
+def _unit_centers(C: np.ndarray) -> np.ndarray:
+    nrm = np.sqrt((C * C).sum(axis=1))
+    if (nrm == 0).any():
+        raise IllegalArgumentException("requirement failed: Cosine distance is not defined for zero-length vectors.")
+    return C * (1.0 / nrm)[:, None]
+
+
+def lloyd(X: torch.Tensor, C0: np.ndarray, w: Optional[torch.Tensor], max_iter: int, tol: float, check_every: int = 4,
+          cosine: bool = False):
     """KMeans.runAlgorithmWithWeight loop on the current device / process group.
 
     Every iteration is hkm_assign_reduce -> (all-reduce of k*(d+1)+1 doubles) -> hkm_update_centers,
@@ -295,9 +325,15 @@ def lloyd(X: torch.Tensor, C0: np.ndarray, w: Optional[torch.Tensor], max_iter: 
     xsum = torch.zeros(1, dtype=torch.float64, device=dev)
     world = RT.dist_info()[1]
 
-    xchg = RT.PeerExchange.get(dev) if world > 1 else None
+    xchg = RT.PeerExchange.get(dev) if world > 1 and not cosine else None
 
     def one_iter(mode):
+        if cosine:       # X holds unit rows, C unit centres: same pass, CosineDistanceMeasure.centroid as the driver step
+            N.assign_reduce(X, C, partial, weights=w, state=state, scratch=scratch, xnorm2_sum=xsum, xnorm2_mode=mode)
+            if world > 1:
+                RT.all_reduce_sum(partial)
+            N.update_centers(partial, C, tol, state, cosine=True)
+            return
         if world == 1:   # one launch: the last CTA of the pass also updates the centres
             N.lloyd_step(X, C, partial, tol, state, scratch, weights=w, xnorm2_sum=xsum, xnorm2_mode=mode)
             return

@@ -154,6 +154,15 @@ HKM_API int hkm_assign_reduce_noalloc(const double* X, int64_t n, int d, const d
 HKM_API int hkm_update_centers(const double* partial, int k, int d, double* C_inout, double tol,
                        hkm_lloyd_state* state, void* stream);
 
+/* distanceMeasure="cosine" (CosineDistanceMeasure, mllib/clustering/DistanceMeasure.scala): the rows are normalised once
+ * (hkm_normalize_rows), the centres are kept at unit length, and the passes above run unchanged on the unit rows --
+ * argmin of 1 - x.c equals argmin of |x - c|^2 there, the sums are the sums of unit rows (updateClusterSum) and the
+ * cost is half the Euclidean one.  This is the driver step for that mode: centre = normalise(sum / w) (centroid),
+ * converged iff every updated centre has cosine distance <= tol to its predecessor (isCenterConverged; tol is NOT
+ * squared here), state->cost = partial cost / 2.  tol < 0 never converges. */
+HKM_API int hkm_update_centers_cosine(const double* partial, int k, int d, double* C_inout, double tol,
+                                      hkm_lloyd_state* state, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * k-means|| seeding (mllib KMeans.initKMeansParallel)
  * ------------------------------------------------------------------------------------------- */

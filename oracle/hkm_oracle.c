@@ -126,7 +126,11 @@ static double sqdist(const double* a, const double* b, int d) {
   double s = 0; for (int i = 0; i < d; ++i) { double t = a[i] - b[i]; s += t * t; } return s;
 }
 static const double EPSILON_ML = 2.220446049250313e-16; /* MLUtils.EPSILON: smallest eps with 1+eps != 1 */
+/* form 2 = CosineDistanceMeasure.distance(v1, v2) = 1 - dot(v1, v2) / v1.norm / v2.norm (DistanceMeasure.scala);
+ * callers pass (centre, point) in that order, as DistanceMeasure.findClosest does. */
+#define HKMO_FORM_COSINE 2
 static double fast_sqdist(const double* a, double na, const double* b, double nb, int d, int form) {
+  if (form == HKMO_FORM_COSINE) { double dot = 0; for (int i = 0; i < d; ++i) dot += a[i] * b[i]; return 1 - dot / na / nb; }
   if (form == 0) return sqdist(a, b, d);
   double ssn = na * na + nb * nb, nd = na - nb;
   double bound = 2.0 * EPSILON_ML * ssn / (nd * nd + EPSILON_ML);
@@ -159,6 +163,7 @@ static int find_closest(const double* C, const double* cn, int k, int d, const d
   double best = INFINITY; int bi = 0;
   for (int i = 0; i < k; ++i) {
     double lb = cn[i] - xn; lb *= lb;
+    if (form == HKMO_FORM_COSINE) lb = -1;                /* base DistanceMeasure.findClosest: no norm bound */
     if (lb < best) {
       double dist = fast_sqdist(C + (size_t)i * d, cn[i], x, xn, d, form);
       if (dist < best) { best = dist; bi = i; }
@@ -205,13 +210,13 @@ static inline int64_t part_lo(int64_t n, int P, int i) { return (int64_t)(((__in
  * (OpenMP) when threads>1 -- each partition is sequential, merge is in index order, so the
  * result does not depend on the thread count.
  * ---------------------------------------------------------------------------------------- */
-HKMO_API void hkmo_lloyd_pass(const double* X, const double* w, int64_t n, int d, const double* C, int k,
-                              int P, int use_stats, int form, int threads,
-                              double* sums, double* wsum, double* cost_out, int32_t* labels) {
+static void lloyd_pass_impl(const double* X, const double* w, int64_t n, int d, const double* C, const double* cn_in, int k,
+                            int P, int use_stats, int form, int threads,
+                            double* sums, double* wsum, double* cost_out, int32_t* labels) {
   double* cn = (double*)malloc(sizeof(double) * k);
-  for (int i = 0; i < k; ++i) cn[i] = vnorm2(C + (size_t)i * d, d);
+  for (int i = 0; i < k; ++i) cn[i] = cn_in ? cn_in[i] : vnorm2(C + (size_t)i * d, d);
   double* st = NULL;
-  if (use_stats && k > 1) { st = (double*)malloc(sizeof(double) * (k * (k + 1) / 2)); hkmo_compute_statistics(C, k, d, form, st); }
+  if (use_stats && k > 1 && form != HKMO_FORM_COSINE) { st = (double*)malloc(sizeof(double) * (k * (k + 1) / 2)); hkmo_compute_statistics(C, k, d, form, st); }
   size_t per = (size_t)k * d + k + 1;
   double* part = (double*)calloc((size_t)P * per, sizeof(double));
 #ifdef _OPENMP
@@ -228,6 +233,10 @@ HKMO_API void hkmo_lloyd_pass(const double* X, const double* w, int64_t n, int d
       double wt = w ? w[r] : 1.0;
       *pc += dist * wt;                                   /* costAccum.add(cost * point.weight) */
       double* s = ps + (size_t)b * d;
+      if (form == HKMO_FORM_COSINE) {                     /* CosineDistanceMeasure.updateClusterSum: axpy(weight / norm, v, sum) */
+        double a = wt / xn;                               /* xn == 0: Spark asserts; here the sums turn NaN/inf and the test sees it */
+        for (int j = 0; j < d; ++j) s[j] += a * x[j];
+      } else
       for (int j = 0; j < d; ++j) s[j] += wt * x[j];      /* axpy(point.weight, point.vector, sum) */
       pw[b] += wt;
       if (labels) labels[r] = b;
@@ -247,6 +256,30 @@ HKMO_API void hkmo_lloyd_pass(const double* X, const double* w, int64_t n, int d
   }
   *cost_out = cost;
   free(part); free(cn); free(st);
+}
+
+HKMO_API void hkmo_lloyd_pass(const double* X, const double* w, int64_t n, int d, const double* C, int k,
+                              int P, int use_stats, int form, int threads,
+                              double* sums, double* wsum, double* cost_out, int32_t* labels) {
+  lloyd_pass_impl(X, w, n, d, C, NULL, k, P, use_stats, form, threads, sums, wsum, cost_out, labels);
+}
+
+/* Cosine driver side: CosineDistanceMeasure.centroid = scal(1/w, sum); scal(1/norm(sum), sum); VectorWithNorm(sum, 1)
+ * -- the stored norm is exactly 1.0 from then on (cn[j]); isCenterConverged = distance(old, new) <= epsilon (NOT squared). */
+HKMO_API int hkmo_update_centers_cosine(const double* sums, const double* wsum, int k, int d, double tol, double* C, double* cn) {
+  int converged = 1;
+  double* nc = (double*)malloc(sizeof(double) * d);
+  for (int j = 0; j < k; ++j) {
+    if (!(wsum[j] > 0)) continue;
+    double inv = 1.0 / wsum[j];
+    for (int f = 0; f < d; ++f) nc[f] = sums[(size_t)j * d + f] * inv;
+    double inv2 = 1.0 / vnorm2(nc, d);
+    for (int f = 0; f < d; ++f) nc[f] *= inv2;
+    double* c = C + (size_t)j * d;
+    if (converged && !(fast_sqdist(c, cn[j], nc, 1.0, d, HKMO_FORM_COSINE) <= tol)) converged = 0;
+    memcpy(c, nc, sizeof(double) * d); cn[j] = 1.0;
+  }
+  free(nc); return converged;
 }
 
 /* Driver side of the iteration: centroid = scal(1/w, sum); converged iff every updated centre
@@ -272,11 +305,19 @@ HKMO_API void hkmo_lloyd(const double* X, const double* w, int64_t n, int d, dou
   double* sums = (double*)malloc(sizeof(double) * (size_t)k * d);
   double* wsum = (double*)malloc(sizeof(double) * k);
   int it = 0, converged = 0; double cost = 0.0;
+  double* cn = (double*)malloc(sizeof(double) * k);
+  for (int j = 0; j < k; ++j) cn[j] = vnorm2(C + (size_t)j * d, d);   /* new VectorWithNorm(initial centre) */
   while (it < max_iter && !converged) {
-    hkmo_lloyd_pass(X, w, n, d, C, k, P, use_stats, form, threads, sums, wsum, &cost, NULL);
-    converged = hkmo_update_centers(sums, wsum, k, d, tol, form, C);
+    if (form == HKMO_FORM_COSINE) {
+      lloyd_pass_impl(X, w, n, d, C, cn, k, P, 0, form, threads, sums, wsum, &cost, NULL);
+      converged = hkmo_update_centers_cosine(sums, wsum, k, d, tol, C, cn);
+    } else {
+      hkmo_lloyd_pass(X, w, n, d, C, k, P, use_stats, form, threads, sums, wsum, &cost, NULL);
+      converged = hkmo_update_centers(sums, wsum, k, d, tol, form, C);
+    }
     ++it;
   }
+  free(cn);
   *num_iter = it; *cost_out = cost; free(sums); free(wsum);
 }
 
@@ -286,7 +327,7 @@ HKMO_API void hkmo_predict(const double* X, int64_t n, int d, const double* C, i
   double* cn = (double*)malloc(sizeof(double) * k);
   for (int i = 0; i < k; ++i) cn[i] = vnorm2(C + (size_t)i * d, d);
   double* st = NULL;
-  if (use_stats && k > 1) { st = (double*)malloc(sizeof(double) * (k * (k + 1) / 2)); hkmo_compute_statistics(C, k, d, form, st); }
+  if (use_stats && k > 1 && form != HKMO_FORM_COSINE) { st = (double*)malloc(sizeof(double) * (k * (k + 1) / 2)); hkmo_compute_statistics(C, k, d, form, st); }
 #ifdef _OPENMP
   if (threads <= 0) threads = omp_get_max_threads();
 #pragma omp parallel for schedule(static) num_threads(threads)
@@ -521,7 +562,8 @@ HKMO_API int hkmo_init_kmeans_parallel(const double* X, int64_t n, int d, int k,
     hkmo_predict(X, n, d, cand, m, 0, form, threads, lab, NULL);          /* findClosest(candidates, x)._1, countByValue */
     double* wts = (double*)calloc(m, sizeof(double));
     for (int64_t i = 0; i < n; ++i) wts[lab[i]] += 1.0;
-    hkmo_local_kmeanspp(0, cand, wts, m, d, k, 30, form, C_out);
+    /* LocalKMeans works with EuclideanDistanceMeasure.fastSquaredDistance whatever the distance measure of the run */
+    hkmo_local_kmeanspp(0, cand, wts, m, d, k, 30, form == HKMO_FORM_COSINE ? 0 : form, C_out);
     free(lab); free(wts); kout = k;
   }
   free(cand);

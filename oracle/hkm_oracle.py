@@ -247,12 +247,17 @@ def num_threads() -> int:
     return lib().hkmo_num_threads()
 
 
+FORM_COSINE = 2   # distanceMeasure="cosine" (CosineDistanceMeasure); 0 / 1 are the two Euclidean code paths
+
+
 def kmeans_fit(X, k, seed, max_iter=20, tol=1e-4, init_mode="k-means||", init_steps=2, P=8, w=None,
-               init_centers=None, first_idx=-1, use_stats=False, form=0, threads=0):
+               init_centers=None, first_idx=-1, use_stats=False, form=0, threads=0, distance="euclidean"):
     """ml.clustering.KMeans.fit restated end to end: init, Lloyd, summary pass.
 
     Returns dict(centers, num_iter, training_cost, labels, cluster_sizes)."""
     X = _c64(X)
+    if distance == "cosine":
+        form, use_stats = FORM_COSINE, False
     if init_centers is not None:
         C0 = np.array(init_centers, dtype=np.float64)
     elif init_mode == "random":

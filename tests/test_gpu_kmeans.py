@@ -151,3 +151,37 @@ def test_cfg2_fit_end_to_end(hkm):
     for lo in range(0, 10_000_000, 1_000_000):
         direct += float(((X[lo:lo + 1_000_000] - C[lab[lo:lo + 1_000_000]]) ** 2).sum())
     assert direct <= m2.summary.trainingCost * (1 + 1e-6)
+
+
+@pytest.mark.parametrize("init_mode", ["random", "k-means||"])
+def test_cosine_distance_measure(hkm, oracle, init_mode):
+    """distanceMeasure='cosine' (SURVEY 8f-4): unit rows + unit centres through the same kernels == CosineDistanceMeasure."""
+    from hkm_b200.ml.clustering import KMeans
+    rng = np.random.default_rng(5)
+    n, d, k, P = 40_000, 12, 6, 8
+    dirs = rng.normal(size=(k, d))
+    X = dirs[rng.integers(0, k, size=n)] * rng.uniform(0.5, 20.0, size=(n, 1)) + 0.3 * rng.normal(size=(n, d))
+    w = rng.uniform(0.5, 2.0, size=n) if init_mode == "random" else None
+    km = KMeans(k=k, seed=11, initMode=init_mode, distanceMeasure="cosine", maxIter=20, tol=1e-5).setNumPartitions(P)
+    t = {"features": X}
+    if w is not None:
+        km.setWeightCol("w")
+        t["w"] = w
+    model = km.fit(t)
+    ref = oracle.kmeans_fit(X, k, 11, tol=1e-5, init_mode=init_mode, P=P, w=w, distance="cosine")
+    C = np.array(model.clusterCenters())
+    assert model.summary.numIter == ref["num_iter"]
+    assert np.abs(C - ref["centers"]).max() < 1e-9 and np.allclose(np.linalg.norm(C, axis=1), 1.0, atol=1e-14)
+    assert model.summary.trainingCost == pytest.approx(ref["training_cost"], rel=1e-8)
+    pred = model.transform({"features": X}).to_numpy("prediction")
+    assert (pred == ref["labels"]).mean() >= 0.9999
+    assert model.summary.clusterSizes == np.bincount(pred, minlength=k).tolist()
+    assert model.predict(X[3]) == ref["labels"][3]
+    # ml KMeansSuite "KMeans with cosine distance"
+    S = np.array([[1.0, 1.0], [10.0, 10.0], [1.0, 0.5], [10.0, 4.4], [-1.0, 1.0], [-100.0, 90.0]])
+    m2 = KMeans(k=3, seed=42, initMode="random", tol=1e-6, distanceMeasure="cosine").setNumPartitions(2).fit({"features": S})
+    p2 = m2.transform({"features": S}).to_numpy("prediction")
+    assert len(set(p2.tolist())) == 3 and p2[0] == p2[1] and p2[2] == p2[3] and p2[4] == p2[5]
+    S[2] = 0.0
+    with pytest.raises(hkm.IllegalArgumentException, match="zero-length"):
+        KMeans(k=2, distanceMeasure="cosine").fit({"features": S})

@@ -166,3 +166,34 @@ def test_kmeans_parallel_structure(oracle):
     Xd = np.repeat(np.array([[0.0, 0], [1, 1], [2, 2]]), 50, axis=0)
     r = oracle.kmeans_fit(Xd, 5, seed=3, P=2)
     assert r["centers"].shape[0] <= 3 and r["training_cost"] == pytest.approx(0.0, abs=1e-20)
+
+
+def test_cosine_kmeans_spark_suite_case_and_numpy_twin(oracle):
+    """ml KMeansSuite "KMeans with cosine distance": 6 points in 3 directions, 2 partitions, k=3, random init, seed 42,
+    tol 1e-6 -> three clusters, same-direction points together, unit-length centres.  Plus an independent NumPy Lloyd."""
+    X = np.array([[1.0, 1.0], [10.0, 10.0], [1.0, 0.5], [10.0, 4.4], [-1.0, 1.0], [-100.0, 90.0]])
+    r = oracle.kmeans_fit(X, 3, 42, tol=1e-6, init_mode="random", P=2, distance="cosine")
+    lab = r["labels"]
+    assert len(set(lab.tolist())) == 3 and lab[0] == lab[1] and lab[2] == lab[3] and lab[4] == lab[5]
+    assert np.allclose(np.linalg.norm(r["centers"], axis=1), 1.0, atol=1e-15)
+
+    rng = np.random.default_rng(0)
+    Xr = rng.normal(size=(5000, 6)) + rng.integers(0, 4, size=(5000, 1)) * np.array([1, -1, 2, 0, 1, 3.0])
+    C = Xr[:5].copy()
+    Co, it_o, cost_o = oracle.lloyd(Xr, C, max_iter=20, tol=1e-4, P=4, form=oracle.FORM_COSINE)
+    cn, xn = np.linalg.norm(C, axis=1), np.linalg.norm(Xr, axis=1)
+    for it in range(20):
+        D = 1 - (Xr @ C.T) / cn[None, :] / xn[:, None]
+        lab = D.argmin(1)
+        cost = D[np.arange(len(Xr)), lab].sum()
+        conv = True
+        for j in range(len(C)):
+            m = lab == j
+            if m.any():
+                s = (Xr[m] / xn[m, None]).sum(0) / m.sum()
+                s /= np.linalg.norm(s)
+                conv &= bool(1 - C[j] @ s / cn[j] <= 1e-4)
+                C[j], cn[j] = s, 1.0
+        if conv:
+            break
+    assert it_o == it + 1 and cost_o == pytest.approx(cost, rel=1e-12) and np.abs(Co - C).max() < 1e-12
