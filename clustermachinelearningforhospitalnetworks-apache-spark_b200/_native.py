@@ -18,7 +18,7 @@ EXPORTS = (
     "hkm_assign_reduce_scratch_bytes", "hkm_assign_reduce", "hkm_update_centers", "hkm_update_centers_cosine", "hkm_lloyd_step", "hkm_lloyd_step_peer", "hkm_peer_exchange_bytes",
     "hkm_kmpar_scratch_bytes", "hkm_kmpar_cost_update", "hkm_kmpar_sample", "hkm_kmpar_strip_rows", "hkm_closest_counts",
     "hkm_silhouette_stats", "hkm_silhouette_score",
-    "hkm_assemble_scratch_bytes", "hkm_assemble", "hkm_moments_scratch_bytes", "hkm_moments", "hkm_column_moments", "hkm_scale_rows", "hkm_normalize_rows",
+    "hkm_assemble_scratch_bytes", "hkm_assemble", "hkm_moments_scratch_bytes", "hkm_moments", "hkm_column_moments", "hkm_scale_rows", "hkm_normalize_rows", "hkm_local_kmeanspp",
 )
 
 _lib = None
@@ -70,6 +70,7 @@ def load() -> ctypes.CDLL:
         L.hkm_column_moments.argtypes = [vp, vp, vp, vp, i32, i64, vp, vp, vp, sz, vp]
         L.hkm_scale_rows.argtypes = [vp, vp, i64, i32, vp, vp, vp]
         L.hkm_normalize_rows.argtypes = [vp, vp, i64, i32, vp, vp]
+        L.hkm_local_kmeanspp.argtypes = [ctypes.c_int32, vp, vp, i32, i32, i32, i32, vp]
         L.hkm_silhouette_stats.argtypes = [vp, vp, vp, i64, i32, i32, vp, vp, sz, vp]
         L.hkm_silhouette_score.argtypes = [vp, vp, vp, i64, i32, i32, vp, vp, vp, vp, sz, vp]
         _lib = L
@@ -321,3 +322,14 @@ def normalize_rows(X):
         rc = load().hkm_normalize_rows(_ptr(X), _ptr(out), X.shape[0], X.shape[1], _ptr(zero), _stream())
     _check(rc)
     return out, int(zero.item())
+
+
+def local_kmeanspp(seed: int, points, weights, k: int, max_iter: int = 30):
+    """hkm_local_kmeanspp (host arrays in, host array out): LocalKMeans.kMeansPlusPlus on the k-means|| candidates."""
+    import numpy as np
+    pts = np.ascontiguousarray(points, dtype=np.float64)
+    wts = np.ascontiguousarray(weights, dtype=np.float64)
+    m, d = pts.shape
+    out = np.empty((k, d), dtype=np.float64)
+    _check(load().hkm_local_kmeanspp(int(seed), pts.ctypes.data, wts.ctypes.data, m, d, int(k), int(max_iter), out.ctypes.data))
+    return out

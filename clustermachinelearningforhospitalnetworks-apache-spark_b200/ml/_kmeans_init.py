@@ -151,4 +151,4 @@ def init_kmeans_parallel(X: torch.Tensor, layout: PartitionLayout, k: int, init_
     weights = counts.cpu().numpy().astype(np.float64)
     if debug is not None:
         debug.update(weights=weights.copy())
-    return SR.local_kmeans_pp(0, cand, weights, k, 30)
+    return N.local_kmeanspp(0, cand, weights, k, 30)

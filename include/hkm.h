@@ -266,6 +266,13 @@ HKM_API int hkm_column_moments(const void* const* cols_host, const int32_t* dtyp
                                const int32_t* vkind_host, int d, int64_t n, const double* pivot, double* out2d,
                                void* scratch, size_t scratch_bytes, void* stream);
 
+/* Driver side of k-means|| (KMeans.initKMeansParallel's last step): LocalKMeans.kMeansPlusPlus(seed, points, weights,
+ * k, maxIterations) -- weighted k-means++ with java.util.Random(seed), then Lloyd on the m candidates until no
+ * assignment moves or max_iter (Spark passes seed 0, 30).  HOST pointers (m is a few hundred rows: Spark runs this on
+ * the driver JVM as well); points [m, d], weights [m], centers_out [k, d].  Always Euclidean, whatever the measure. */
+HKM_API int hkm_local_kmeanspp(int32_t seed, const double* points, const double* weights, int m, int d, int k, int max_iter,
+                               double* centers_out);
+
 /* Cosine distance measure (ClusteringEvaluator distanceMeasure="cosine"): out = x / |x|_2 per row (multiply by the
  * reciprocal norm); *zero_rows = rows of zero length, for which Spark refuses the cosine distance.  In place allowed. */
 HKM_API int hkm_normalize_rows(const double* X_in, double* X_out, int64_t n, int d, unsigned long long* zero_rows, void* stream);

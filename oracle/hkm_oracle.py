@@ -21,8 +21,9 @@ def build(force: bool = False) -> str:
     src = os.path.join(_HERE, "hkm_oracle.c")
     if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
         os.makedirs(os.path.dirname(_SO), exist_ok=True)
-        # -march=native code must be rebuilt on the box that runs it; fall back if unsupported
-        cmd = ["gcc", "-O3", "-march=native", "-fopenmp", "-fPIC", "-fvisibility=hidden", "-shared",
+        # -march=native code must be rebuilt on the box that runs it; fall back if unsupported.
+        # -ffp-contract=off: the JVM never fuses a*b+c into an FMA, so the restatement must not either.
+        cmd = ["gcc", "-O3", "-march=native", "-ffp-contract=off", "-fopenmp", "-fPIC", "-fvisibility=hidden", "-shared",
                "-o", _SO, src, "-lm"]
         subprocess.run(cmd, check=True, capture_output=True)
     return _SO

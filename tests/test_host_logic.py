@@ -93,6 +93,8 @@ def test_local_kmeanspp_matches_oracle(hkm, oracle):
         w = rng.integers(0, 10, size=m).astype(float)
         w[0] = max(w[0], 1.0)
         assert np.allclose(hkm._sparkrand.local_kmeans_pp(0, pts, w, k), oracle.local_kmeanspp(0, pts, w, k), atol=1e-12)
+        # the product's driver step (host C++ inside libhkm; runs without a GPU) -- same summation order as Vectors.sqdist
+        assert np.array_equal(hkm._native.local_kmeanspp(0, pts, w, k), oracle.local_kmeanspp(0, pts, w, k))
 
 
 def test_xorshift_jump_table(hkm):
