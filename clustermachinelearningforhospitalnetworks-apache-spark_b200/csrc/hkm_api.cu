@@ -19,7 +19,7 @@ int lloyd_variant_override() {
   static int v = -1;
   if (v < 0) {
     const char* e = getenv("HKM_LLOYD_VARIANT");
-    v = e == nullptr ? 0 : (strcmp(e, "gather") == 0 ? 1 : (strcmp(e, "mma") == 0 ? 2 : 0));
+    v = e == nullptr ? 0 : (strcmp(e, "gather") == 0 ? 1 : (strcmp(e, "mma") == 0 ? 2 : (strcmp(e, "ws") == 0 ? 3 : 0)));
   }
   return v;
 }

@@ -1,4 +1,5 @@
 // Instantiations of lloyd_pass_kernel for one NT = ceil(k/8) (compile with -DHKM_NT=<1..8>).
+#include <cstdlib>
 #include "../../include/hkm.h"
 #include "hkm_lloyd_launch.cuh"
 
@@ -60,6 +61,31 @@ static int launch_mma(LloydParams p, int grid, cudaStream_t st) {
   return HKM_OK;
 }
 
+// mid-k variant: score warps + reduce warps, one CTA of 16 warps per SM (hkm_lloyd_ws.cuh)
+template <int KS_T, int NT, int SW, int NSET>
+static int launch_ws_n(LloydParams p, int grid, cudaStream_t st) {
+  p.stages = ws_stages(p.d, NT * 8, kWsWarps - SW, NSET);
+  if (p.stages < 2) { set_error("lloyd_ws: %d stages", p.stages); return HKM_ERR_UNSUPPORTED; }
+  const int smem = ws_smem_layout(p.d, NT * 8, p.stages, kWsWarps - SW, NSET).total;
+  auto kern = lloyd_ws_kernel<KS_T, NT, SW, NSET, 128>;
+  static int attr_smem[64];
+  int dev = 0; HKM_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev >= 64 || attr_smem[dev] < smem) {
+    HKM_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    if (dev < 64) attr_smem[dev] = smem;
+  }
+  kern<<<grid, kWsThreads, smem, st>>>(p);
+  HKM_CUDA_TRY(cudaGetLastError());
+  return HKM_OK;
+}
+template <int KS_T, int NT>
+static int launch_ws(const LloydParams& p, int grid, cudaStream_t st) {
+  constexpr int SW = NT >= 7 ? 12 : 8;
+  static_assert(SW == 12 || SW == 8, "");
+  if (ws_nset(p.d, NT * 8, kWsWarps - SW) == 2) return launch_ws_n<KS_T, NT, SW, 2>(p, grid, st);
+  return launch_ws_n<KS_T, NT, SW, 1>(p, grid, st);
+}
+
 #define HKM_CAT2(a, b) a##b
 #define HKM_CAT(a, b) HKM_CAT2(a, b)
 
@@ -81,6 +107,24 @@ int HKM_CAT(dispatch_lloyd_nt, HKM_NT)(const LloydParams& p, const LaunchPlan& p
   if (mode == 1) return launch_smemb<NT, 1>(p, pl, grid, st);
   if (mode == 2) return launch_smemb<NT, 2>(p, pl, grid, st);
   if (mode == 3) return launch_smemb<NT, 3>(p, pl, grid, st);   // weighted Lloyd pass (weightCol)
+  if constexpr (NT >= 3) {
+    // 16 < k, d <= 32: warp-specialised variant (score warps on the fp64 tensor pipe, reduce warps with shared-memory
+    // accumulators) whenever at least three stages fit next to the accumulators; k <= 24 with d <= 16 stays on the
+    // gather variant (measured)
+    const int variant = lloyd_variant_override();
+    const bool fits = p.d <= 32 && ws_stages(p.d, NT * 8, kWsWarps - ws_score_warps(NT), 1) >= 3;
+    const bool wanted = variant == 3 || (variant == 0 && !(NT == 3 && p.d <= 16));
+    if (mode == 0 && p.do_reduce == 1 && p.out_mode == 0 && fits && wanted) {
+      const int grid1 = grid / (pl.ctas_per_sm > 0 ? pl.ctas_per_sm : 1);
+#define HKM_WS(KS) if constexpr (KS * NT <= 24) { if (ks == KS) return launch_ws<KS, NT>(p, grid1, st); }
+#ifndef HKM_DEV_FAST
+      HKM_WS(1) HKM_WS(2) HKM_WS(3) HKM_WS(5) HKM_WS(7)
+#endif
+      HKM_WS(4) HKM_WS(6) HKM_WS(8)
+#undef HKM_WS
+      return launch_ws<0, NT>(p, grid1, st);
+    }
+  }
   if constexpr (NT <= 2) {
     // k <= 16: reduce on the tensor pipe as well (see hkm_lloyd_mma.cuh) when the pass is a plain Lloyd step
     const int variant = lloyd_variant_override();

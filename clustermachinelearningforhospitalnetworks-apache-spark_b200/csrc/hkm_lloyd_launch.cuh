@@ -5,6 +5,7 @@
 #include "../../include/hkm.h"
 #include "hkm_lloyd.cuh"
 #include "hkm_lloyd_mma.cuh"
+#include "hkm_lloyd_ws.cuh"
 
 namespace hkm {
 
@@ -39,7 +40,8 @@ inline LaunchPlan plan_lloyd_mma(int d, int k_pad) {
 // tcgen05 screening variant (hkm_lloyd_tc.cuh): 16 < k <= 64, even 32 < d <= 64, plain Lloyd / predict passes
 bool lloyd_tc_eligible(const LloydParams& p, int mode);
 int launch_lloyd_tc(const LloydParams& p, cudaStream_t st);
-// 0: pick per shape (default); 1: always the gather variant; 2: the tensor-pipe variant wherever it is built.
+// 0: pick per shape (default); 1: always the gather variant; 2: the tensor-pipe variant wherever it is built;
+// 3: the warp-specialised variant wherever it is built (HKM_LLOYD_VARIANT=gather|mma|ws).
 int lloyd_variant_override();
 
 // Validated, dispatched Lloyd data pass shared by the C entry points (hkm_api.cu).

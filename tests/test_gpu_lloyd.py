@@ -39,7 +39,10 @@ def _check(g, o_sums, o_wsum, o_cost, o_lab, o_dist, scale):
 
 SHAPES = [(1000, 8, 5), (128, 32, 8), (127, 32, 8), (129, 32, 8), (4096, 32, 8), (100003, 32, 8), (50000, 16, 16), (30000, 24, 7),
           (30000, 24, 32), (20000, 5, 3), (20000, 7, 2), (20000, 64, 16), (20000, 33, 9), (77, 3, 2), (1, 4, 2), (20000, 64, 64),
-          (5000, 1, 3), (5000, 2, 8), (9000, 12, 20), (6000, 48, 24), (3000, 63, 33), (3000, 96, 5), (5000, 80, 40), (4000, 66, 64)]
+          (5000, 1, 3), (5000, 2, 8), (9000, 12, 20), (6000, 48, 24), (3000, 63, 33), (3000, 96, 5), (5000, 80, 40), (4000, 66, 64),
+          # 16 < k, d <= 32: the warp-specialised variant (score warps + reduce warps), all NT, ragged tails, one tile, < one tile
+          (40000, 32, 64), (45001, 20, 50), (70003, 7, 33), (33333, 32, 17), (50000, 29, 41), (128, 24, 32), (100, 24, 24), (60000, 3, 64),
+          (200000, 24, 32)]
 
 
 @pytest.mark.parametrize("n,d,k", SHAPES)
