@@ -17,7 +17,7 @@ from hkm_b200.ml.evaluation import ClusteringEvaluator
 from hkm_b200.ml.feature import StandardScaler
 
 ok = True
-for n, d, k, seed in [(80_000, 8, 5, 42), (160_000, 24, 16, 7)]:
+for n, d, k, seed in [(80_000, 8, 5, 42), (160_000, 24, 16, 7), (240_000, 20, 24, 3)]:
     P = 8
     raw = datagen.hospital_matrix(n, d=d, profiles=k, seed=20250331, standardize=False)
     lo, hi = rank * n // world, (rank + 1) * n // world                   # n divisible by P: shards line up with Spark's slices
