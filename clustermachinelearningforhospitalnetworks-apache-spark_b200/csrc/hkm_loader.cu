@@ -143,10 +143,19 @@ __global__ void __launch_bounds__(256) moments_rows_kernel(const double* __restr
   for (int f0 = f; f0 < d; f0 += dp) {   // d > 256 is not a case here, loop kept for generality
     const double K = pivot[f0];
     double a1 = 0, a2 = 0;
-    for (int64_t r = (int64_t)blockIdx.x * rows_par + rl; r < n; r += (int64_t)gridDim.x * rows_par) {
-      const double v = X[r * d + f0] - K;
-      a1 += v; a2 = fma(v, v, a2);
+    // eight independent loads in flight per thread, four accumulator pairs (fixed order -> deterministic)
+    double b1[4] = {0, 0, 0, 0}, b2[4] = {0, 0, 0, 0};
+    const int64_t step = (int64_t)gridDim.x * rows_par;
+    int64_t r = (int64_t)blockIdx.x * rows_par + rl;
+    for (; r + 7 * step < n; r += 8 * step) {
+      double v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = __ldcs(X + (r + u * step) * d + f0) - K;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) { b1[u & 3] += v[u]; b2[u & 3] = fma(v[u], v[u], b2[u & 3]); }
     }
+    for (; r < n; r += step) { const double v = X[r * d + f0] - K; b1[0] += v; b2[0] = fma(v, v, b2[0]); }
+    a1 = (b1[0] + b1[1]) + (b1[2] + b1[3]); a2 = (b2[0] + b2[1]) + (b2[2] + b2[3]);
     if (f0 == f) { s1 = a1; s2 = a2; }
   }
   if (f < d) { sm[(rl * d + f) * 2] = s1; sm[(rl * d + f) * 2 + 1] = s2; }
@@ -158,15 +167,43 @@ __global__ void __launch_bounds__(256) moments_rows_kernel(const double* __restr
   }
 }
 
+// one typed column: eight independent loads in flight per thread, four accumulator pairs (fixed order -> deterministic)
+template <typename T>
+__device__ __forceinline__ void col_moments(const T* __restrict__ x, int64_t n, int64_t r, int64_t step, double K, double& a1, double& a2) {
+  double b1[4] = {0, 0, 0, 0}, b2[4] = {0, 0, 0, 0};
+  for (; r + 7 * step < n; r += 8 * step) {
+    T raw[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) raw[u] = __ldcs(x + r + u * step);
+#pragma unroll
+    for (int u = 0; u < 8; ++u) { const double v = (double)raw[u] - K; b1[u & 3] += v; b2[u & 3] = fma(v, v, b2[u & 3]); }
+  }
+  for (; r < n; r += step) { const double v = (double)x[r] - K; b1[0] += v; b2[0] = fma(v, v, b2[0]); }
+  a1 = (b1[0] + b1[1]) + (b1[2] + b1[3]); a2 = (b2[0] + b2[1]) + (b2[2] + b2[3]);
+}
+
 // Columnar input: blockIdx.y = column, blocks stride over rows.
 __global__ void __launch_bounds__(256) moments_cols_kernel(const AssembleParams p, const double* __restrict__ pivot, double* __restrict__ part /* [gridDim.x][2*d] */) {
   __shared__ double s_a[8], s_b[8];
   const int c = blockIdx.y;
   const double K = pivot[c];
   double a1 = 0, a2 = 0;
-  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < p.n; r += (int64_t)gridDim.x * blockDim.x) {
-    bool ok; const double v = load_col(p.cols[c], r, ok) - K;
-    a1 += v; a2 = fma(v, v, a2);
+  {
+    const ColDesc& col = p.cols[c];
+    const int64_t step = (int64_t)gridDim.x * blockDim.x, r0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (col.vkind != 0) {           // columns with a validity mask: element-wise path (nulls turn the moments NaN, as Summarizer does)
+      for (int64_t r = r0; r < p.n; r += step) { bool ok; const double v = load_col(col, r, ok) - K; a1 += v; a2 = fma(v, v, a2); }
+    } else {
+      switch (col.dtype) {           // the type switch sits outside the streaming loop
+        case HKM_DTYPE_F64: col_moments(reinterpret_cast<const double*>(col.data), p.n, r0, step, K, a1, a2); break;
+        case HKM_DTYPE_F32: col_moments(reinterpret_cast<const float*>(col.data), p.n, r0, step, K, a1, a2); break;
+        case HKM_DTYPE_I32: col_moments(reinterpret_cast<const int32_t*>(col.data), p.n, r0, step, K, a1, a2); break;
+        case HKM_DTYPE_I64: col_moments(reinterpret_cast<const int64_t*>(col.data), p.n, r0, step, K, a1, a2); break;
+        case HKM_DTYPE_I16: col_moments(reinterpret_cast<const int16_t*>(col.data), p.n, r0, step, K, a1, a2); break;
+        case HKM_DTYPE_I8: col_moments(reinterpret_cast<const int8_t*>(col.data), p.n, r0, step, K, a1, a2); break;
+        default: col_moments(reinterpret_cast<const uint8_t*>(col.data), p.n, r0, step, K, a1, a2); break;
+      }
+    }
   }
 #pragma unroll
   for (int m = 16; m >= 1; m >>= 1) { a1 += shfl_xor_d(a1, m); a2 += shfl_xor_d(a2, m); }

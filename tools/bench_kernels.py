@@ -97,6 +97,8 @@ def kmpar(n, d, k):
 
 
 if __name__ == "__main__":
+    if "loader" in sys.argv:
+        loader(10_000_000, 32); loader(10_000_000, 24); sys.exit(0)
     lloyd(10_000_000, 32, 8, "cfg2")
     lloyd(20_000_000, 16, 16, "cfg4 shard shape")
     lloyd(5_000_000, 24, 16, "cfg5 mid sweep")
