@@ -210,3 +210,29 @@ def test_tensor_core_variant_exact_ties(hkm, oracle):
     sums, wsum, cost, lab = oracle.lloyd_pass(X, C, P=1, want_labels=True)
     assert np.array_equal(g["labels"], lab) and wsum[7] == 0 and wsum[40] == 0 and wsum[20] == 0
     assert np.array_equal(g["sums"], sums) and np.array_equal(g["wsum"], wsum) and g["cost"] == cost
+
+
+@pytest.mark.parametrize("n,d,k", [(400_000, 24, 32), (300_001, 16, 48), (250_000, 32, 64), (300_000, 32, 8), (300_000, 16, 16)])
+def test_passes_are_bit_stable(hkm, n, d, k):
+    """Fixed summation order in every variant (no atomics on the data path): repeated passes over the same input give
+    bit-identical sums, counts, cost and labels -- which is also what a shared-memory race would break."""
+    N = hkm._native
+    g = torch.Generator(device="cuda"); g.manual_seed(n + d + k)
+    prof = torch.randn(k, d, dtype=torch.float64, device="cuda", generator=g) * 2
+    X = prof[torch.randint(0, k, (n,), device="cuda", generator=g)] + torch.randn(n, d, dtype=torch.float64, device="cuda", generator=g)
+    C = prof + 0.05
+    scratch = N.new_scratch(d, k, "cuda")
+    xs = torch.zeros(1, dtype=torch.float64, device="cuda")
+    ref = None
+    for rep in range(6):
+        partial = torch.empty(k * d + k + 1, dtype=torch.float64, device="cuda")
+        labels = torch.empty(n, dtype=torch.int32, device="cuda")
+        N.assign_reduce(X, C, partial, labels, scratch=scratch, xnorm2_sum=xs, xnorm2_mode=1 if rep == 0 else 2)
+        if rep == 0:
+            continue                       # STORE pass: its cost is formed per row, the REUSE passes below from the sums
+        cur = (partial.clone(), labels.clone())
+        if ref is None:
+            ref = cur
+        else:
+            assert torch.equal(ref[0], cur[0]) and torch.equal(ref[1], cur[1])
+    assert int(ref[0][k * d:k * d + k].sum().item()) == n
