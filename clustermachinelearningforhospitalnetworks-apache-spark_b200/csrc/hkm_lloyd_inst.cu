@@ -107,13 +107,14 @@ int HKM_CAT(dispatch_lloyd_nt, HKM_NT)(const LloydParams& p, const LaunchPlan& p
   if (mode == 1) return launch_smemb<NT, 1>(p, pl, grid, st);
   if (mode == 2) return launch_smemb<NT, 2>(p, pl, grid, st);
   if (mode == 3) return launch_smemb<NT, 3>(p, pl, grid, st);   // weighted Lloyd pass (weightCol)
-  if constexpr (NT >= 3) {
-    // 16 < k, d <= 32: warp-specialised variant (score warps on the fp64 tensor pipe, reduce warps with shared-memory
-    // accumulators) whenever at least three stages fit next to the accumulators; k <= 24 with d <= 16 stays on the
-    // gather variant (measured)
+  if constexpr (NT >= 2) {
+    // 8 < k, d <= 32: warp-specialised variant (score warps on the fp64 tensor pipe, reduce warps with shared-memory
+    // accumulators) whenever at least three stages fit next to the accumulators
     const int variant = lloyd_variant_override();
     const bool fits = p.d <= 32 && ws_stages(p.d, NT * 8, kWsWarps - ws_score_warps(NT), 1) >= 3;
-    const bool wanted = variant == 3 || (variant == 0 && !(NT == 3 && p.d <= 16));
+    // measured: k <= 16 only wins here at d = 29..32 (the tensor-pipe variant runs out of registers there); k <= 24 with
+    // d <= 16 stays on the gather variant
+    const bool wanted = variant == 3 || (variant == 0 && (NT >= 3 ? !(NT == 3 && p.d <= 16) : ks == 8));
     if (mode == 0 && p.do_reduce == 1 && p.out_mode == 0 && fits && wanted) {
       const int grid1 = grid / (pl.ctas_per_sm > 0 ? pl.ctas_per_sm : 1);
 #define HKM_WS(KS) if constexpr (KS * NT <= 24) { if (ks == KS) return launch_ws<KS, NT>(p, grid1, st); }

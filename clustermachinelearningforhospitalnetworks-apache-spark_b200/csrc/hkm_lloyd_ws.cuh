@@ -17,7 +17,7 @@
 //     warp to finish a tile (an acq_rel counter per stage) issues the bulk copies of the tile that reuses the stage.
 // No CTA barrier in the steady state; summation order is fixed (row order within a reduce warp, warp order in the
 // combine), so results are bit-stable.  Same tile geometry, TMA ring and last-CTA fold as hkm_lloyd.cuh.
-// Plain Lloyd passes only (unit weights, out_mode 0).
+// Plain Lloyd passes only (unit weights, do_reduce 1, out_mode 0); the dispatcher sends everything else elsewhere.
 #pragma once
 #include "hkm_lloyd.cuh"
 
@@ -300,7 +300,7 @@ __global__ void __launch_bounds__(kWsThreads) __maxnreg__(MAXREG) lloyd_ws_kerne
     int s = 0; uint32_t ph = 0;
     for (int i = 0; i < my_tiles; ++i) {
       mbar_wait_a(a_scored + 8u * (uint32_t)s, ph);
-      if (p.do_reduce == 1) reduce_rows(a_x + (uint32_t)s * sbytes, a_lab + (uint32_t)s * (kTileRows * 4));
+      reduce_rows(a_x + (uint32_t)s * sbytes, a_lab + (uint32_t)s * (kTileRows * 4));
       __syncwarp();
       if (lane == 0) {
         // stage hand-back: the last reduce warp to get here refills the stage with tile i + stages
@@ -324,10 +324,9 @@ __global__ void __launch_bounds__(kWsThreads) __maxnreg__(MAXREG) lloyd_ws_kerne
       }
       named_bar_sync(1, kWsThreads);
       named_bar_sync(1, kWsThreads);       // score warps have written the tail tile's labels
-      if (p.do_reduce == 1) reduce_rows(a_x, a_lab);
+      reduce_rows(a_x, a_lab);
     }
   }
-  if (!p.do_reduce) return;
 
   // ===================================================================== CTA-level combine
   const int P = k * d + k + 1;
@@ -345,7 +344,7 @@ __global__ void __launch_bounds__(kWsThreads) __maxnreg__(MAXREG) lloyd_ws_kerne
   {
     const double* acc0 = reinterpret_cast<const double*>(smem + L.acc_off);
     const int kd = k * d, ald = ws_acc_ld(d), wstride = k_pad * ald;
-    if (p.do_reduce == 1) {
+    {
       for (int i = tid; i < kd; i += kWsThreads) {
         const int j = i / d, f = i - j * d;
         double s = 0;
@@ -382,12 +381,11 @@ __global__ void __launch_bounds__(kWsThreads) __maxnreg__(MAXREG) lloyd_ws_kerne
   __syncthreads();
   if (s_ticket == gridDim.x - 1) {
     __threadfence();
-    const int i_lo = p.do_reduce == 1 ? 0 : P - 1;
-    for (int i = i_lo + tid; i < P + 1; i += kWsThreads) {
+    for (int i = tid; i < P + 1; i += kWsThreads) {
       double s = 0;
       for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(p.cta_partials + (size_t)b * S + i);
       if (i == P - 1 && xx_mode == 2) s = fmax(fma(-2.0, s, *p.xnorm2_sum), 0.0);  // cost = sum |x|^2 - 2 sum score
-      if (i < P) p.partial_out[p.do_reduce == 1 ? i : 0] = s;
+      if (i < P) p.partial_out[i] = s;
       else if (xx_mode == 1) *p.xnorm2_sum = s;
     }
     if (tid == 0) *p.counter = 0u;
