@@ -81,7 +81,15 @@ static int launch_ws_n(LloydParams p, int grid, cudaStream_t st) {
 template <int KS_T, int NT>
 static int launch_ws(const LloydParams& p, int grid, cudaStream_t st) {
   constexpr int SW = NT >= 7 ? 12 : 8;
-  static_assert(SW == 12 || SW == 8, "");
+#ifdef HKM_DEV_FAST
+  if (const char* e = getenv("HKM_WS_SW")) {     // developer sweep of the score/reduce split
+    const int sw = atoi(e), ns = getenv("HKM_WS_NSET") ? atoi(getenv("HKM_WS_NSET")) : 2;
+#define HKM_WS_TRY(S, N2) if (sw == S && ns == N2) return launch_ws_n<KS_T, NT, S, N2>(p, grid, st);
+    HKM_WS_TRY(8, 1) HKM_WS_TRY(8, 2) HKM_WS_TRY(9, 1) HKM_WS_TRY(9, 2) HKM_WS_TRY(10, 1) HKM_WS_TRY(10, 2) HKM_WS_TRY(11, 1) HKM_WS_TRY(11, 2)
+    HKM_WS_TRY(12, 1) HKM_WS_TRY(12, 2)
+#undef HKM_WS_TRY
+  }
+#endif
   if (ws_nset(p.d, NT * 8, kWsWarps - SW) == 2) return launch_ws_n<KS_T, NT, SW, 2>(p, grid, st);
   return launch_ws_n<KS_T, NT, SW, 1>(p, grid, st);
 }
@@ -112,9 +120,11 @@ int HKM_CAT(dispatch_lloyd_nt, HKM_NT)(const LloydParams& p, const LaunchPlan& p
     // accumulators) whenever at least three stages fit next to the accumulators
     const int variant = lloyd_variant_override();
     const bool fits = p.d <= 32 && ws_stages(p.d, NT * 8, kWsWarps - ws_score_warps(NT), 1) >= 3;
-    // measured: k <= 16 only wins here at d = 29..32 (the tensor-pipe variant runs out of registers there); k <= 24 with
-    // d <= 16 stays on the gather variant
-    const bool wanted = variant == 3 || (variant == 0 && (NT >= 3 ? !(NT == 3 && p.d <= 16) : ks == 8));
+    // measured on the same box against the gather / tensor-pipe variants (tools/ws_check.py): k <= 24 wins here only
+    // at d = 29..32, k = 25..32 from d = 17 up except d = 25..28 (centre fragments no longer fit in registers there),
+    // k > 32 everywhere
+    const bool wins = NT >= 5 ? true : (NT == 4 ? (p.d > 16 && ks != 7) : ks == 8);
+    const bool wanted = variant == 3 || (variant == 0 && wins);
     if (mode == 0 && p.do_reduce == 1 && p.out_mode == 0 && fits && wanted) {
       const int grid1 = grid / (pl.ctas_per_sm > 0 ? pl.ctas_per_sm : 1);
 #define HKM_WS(KS) if constexpr (KS * NT <= 24) { if (ks == KS) return launch_ws<KS, NT>(p, grid1, st); }

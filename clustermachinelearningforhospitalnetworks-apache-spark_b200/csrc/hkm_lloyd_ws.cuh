@@ -5,16 +5,17 @@
 // hkm_lloyd.cuh / hkm_lloyd_mma.cuh leave that pipe half idle -- every warp alternates between a DMMA phase and a
 // DMMA-free phase (argmax, label exchange, gather), and DSETP/DADD share the fp64 pipe with DMMA.  Here the roles are
 // split.  One CTA of 16 warps per SM (4 per scheduler partition, 128 registers):
-//   * SW score warps (8, or 12 for k > 48) take (tile, 16-row sub-tile pair) items round robin: wait for the tile's
+//   * SW score warps take (tile, 16-row sub-tile pair) items round robin: wait for the tile's
 //     "full" mbarrier, run the score DMMAs + the shuffle argmax, add the cost, store the 16 labels into the stage's
 //     label slots, arrive on the stage's "scored" mbarrier (8 arrivals per tile).
-//   * RW = 16 - SW reduce warps each own 128/RW rows of EVERY tile and NSET private [k_pad, row] fp64 accumulator blocks
-//     in shared memory: wait for "scored", then four rows at a time (lane = feature): one LDS per row, and one
+//   * RW = 16 - SW reduce warps take (tile, 16-row chunk) items round robin as well and own NSET private [k_pad, row]
+//     fp64 accumulator blocks in shared memory: wait for "scored", then four rows at a time (lane = feature): one LDS per row, and one
 //     LDS / DADD / STS on the accumulator row of its label in block (row % NSET).  The four read-modify-writes are
 //     issued together unless two rows of the group share a block AND a label (one ballot per tile finds those groups;
 //     they take the row-by-row path).  For d < 32 lane d adds 1.0, so the rows per cluster are column d of the
-//     accumulators; for d = 32 they are counted in registers (lane c counts clusters c and c + 32).  The last reduce
-//     warp to finish a tile (an acq_rel counter per stage) issues the bulk copies of the tile that reuses the stage.
+//     accumulators; for d = 32 they are counted in registers (lane c counts clusters c and c + 32).  The reduce warp
+//     that finishes the last chunk of a tile (an acq_rel counter per stage) issues the bulk copies of the tile that
+//     reuses the stage.
 // No CTA barrier in the steady state; summation order is fixed (row order within a reduce warp, warp order in the
 // combine), so results are bit-stable.  Same tile geometry, TMA ring and last-CTA fold as hkm_lloyd.cuh.
 // Plain Lloyd passes only (unit weights, do_reduce 1, out_mode 0); the dispatcher sends everything else elsewhere.
@@ -61,9 +62,9 @@ __global__ void __launch_bounds__(kWsThreads) __maxnreg__(MAXREG) lloyd_ws_kerne
   if (p.skip != nullptr && *p.skip != 0) return;
   constexpr int k_pad = NT * 8;
   constexpr int RW = kWsWarps - SW;
-  constexpr int RROWS = kTileRows / RW;     // rows of every tile owned by one reduce warp (32 or 16)
+  constexpr int RROWS = 16;                 // reduce item: one 16-row chunk ("slice") of a tile, 8 per tile
   constexpr bool CNTLANE = KS_T >= 1 && KS_T <= 7;   // d <= 28: lane d adds 1.0 per row, the count is column d of the accumulators
-  static_assert(SW == 12 || SW == 8, "score warps: 12 or 8");
+  static_assert(SW >= 8 && SW <= 12, "score warps: 8..12");
 
   extern __shared__ __align__(128) unsigned char smem[];
   const int d = p.d, k = p.k;
@@ -254,12 +255,11 @@ __global__ void __launch_bounds__(kWsThreads) __maxnreg__(MAXREG) lloyd_ws_kerne
     const bool fl_ok = lane < ws_acc_ld(d);                                    // lane = feature (or the count column)
     const uint32_t set_bytes = (uint32_t)k_pad * acc_row;
     const uint32_t a_acc = sb + L.acc_off + (uint32_t)(rw * NSET) * set_bytes + (uint32_t)lane * 8u;
-    // first owned row of a tile: tile row rw*RROWS (a multiple of 16 -> chunk aligned)
-    const uint32_t x_first = (uint32_t)((rw * RROWS) >> 4) * cstride + (uint32_t)lane * 8u;
     const int q4 = lane & 3;
 
-    auto reduce_rows = [&](const uint32_t xs, const uint32_t lab_b) {
-      const int lab = (int)lds_u32(lab_b + 4u * (uint32_t)(rw * RROWS + (lane & (RROWS - 1))));   // lane r holds the label of owned row r
+    // one item: the 16 rows of chunk `slice` of the tile in stage memory xs
+    auto reduce_rows = [&](const uint32_t xs, const uint32_t lab_b, const int slice) {
+      const int lab = (int)lds_u32(lab_b + 4u * (uint32_t)(slice * RROWS + (lane & (RROWS - 1))));   // lane r holds the label of row r of the slice
       // groups of four rows whose read-modify-writes may not be issued together: two rows in the same block with the
       // same label, or an invalid row (tail tile)
       bool clash = lab < 0;
@@ -269,7 +269,7 @@ __global__ void __launch_bounds__(kWsThreads) __maxnreg__(MAXREG) lloyd_ws_kerne
         clash |= (q4 >= 1 && o1 == lab) || (q4 == 3 && o3 == lab);
       }
       const unsigned cm = __ballot_sync(0xffffffffu, clash);
-      uint32_t xr = xs + x_first;
+      uint32_t xr = xs + (uint32_t)slice * cstride + (uint32_t)lane * 8u;
 #pragma unroll
       for (int r = 0; r < RROWS; r += 4) {
         int lb[4]; double v[4], a[4]; uint32_t aa[4];
@@ -277,7 +277,7 @@ __global__ void __launch_bounds__(kWsThreads) __maxnreg__(MAXREG) lloyd_ws_kerne
         for (int u = 0; u < 4; ++u) {
           lb[u] = __shfl_sync(0xffffffffu, lab, r + u);
           v[u] = lds_f64(xr);                              // lanes >= d read past the row: replaced or never stored
-          xr += row_bytes + (((r + u + 1) & 15) == 0 ? (uint32_t)kChunkPad : 0u);
+          xr += row_bytes;
           if (CNTLANE) v[u] = one_lane ? 1.0 : v[u];
           else { cnt0 += (lb[u] == lane ? 1u : 0u); if (NT > 4) cnt1 += (lb[u] == lane + 32 ? 1u : 0u); }
           aa[u] = a_acc + (uint32_t)(u % NSET) * set_bytes + (uint32_t)lb[u] * acc_row;
@@ -297,21 +297,27 @@ __global__ void __launch_bounds__(kWsThreads) __maxnreg__(MAXREG) lloyd_ws_kerne
       }
     };
 
-    int s = 0; uint32_t ph = 0;
-    for (int i = 0; i < my_tiles; ++i) {
-      mbar_wait_a(a_scored + 8u * (uint32_t)s, ph);
-      reduce_rows(a_x + (uint32_t)s * sbytes, a_lab + (uint32_t)s * (kTileRows * 4));
+    // items u = tile * 8 + slice, taken round robin by the RW reduce warps
+    int tile = rw >> 3, slice = rw & 7;
+    int s = tile, wraps = 0;
+    constexpr int DT = RW / kWsPairs, DP = RW % kWsPairs;
+    while (tile < my_tiles) {
+      mbar_wait_a(a_scored + 8u * (uint32_t)s, (uint32_t)(wraps & 1));
+      reduce_rows(a_x + (uint32_t)s * sbytes, a_lab + (uint32_t)s * (kTileRows * 4), slice);
       __syncwarp();
       if (lane == 0) {
-        // stage hand-back: the last reduce warp to get here refills the stage with tile i + stages
+        // stage hand-back: whoever finishes the last of the tile's 8 slices refills the stage with tile + stages
         unsigned old;
         asm volatile("atom.acq_rel.cta.shared.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(a_done + 8u * (uint32_t)s) : "memory");
-        if (old == RW - 1) {
+        if (old == kWsPairs - 1) {
           sts_u32(a_done + 8u * (uint32_t)s, 0u);
-          if (i + stages < my_tiles) issue_tile(i + stages, s);
+          if (tile + stages < my_tiles) issue_tile(tile + stages, s);
         }
       }
-      if (++s == stages) { s = 0; ph ^= 1u; }
+      int dt = DT; slice += DP;
+      if (slice >= kWsPairs) { slice -= kWsPairs; ++dt; }
+      tile += dt; s += dt;
+      while (s >= stages) { s -= stages; ++wraps; }
     }
     if (tail_mine) {
       named_bar_sync(1, kWsThreads);
@@ -324,7 +330,7 @@ __global__ void __launch_bounds__(kWsThreads) __maxnreg__(MAXREG) lloyd_ws_kerne
       }
       named_bar_sync(1, kWsThreads);
       named_bar_sync(1, kWsThreads);       // score warps have written the tail tile's labels
-      reduce_rows(a_x, a_lab);
+      for (int sl = rw; sl < kWsPairs; sl += RW) reduce_rows(a_x, a_lab, sl);
     }
   }
 
