@@ -131,6 +131,15 @@ def ncu_traffic(workload: str):
     return None
 
 
+def host_threads() -> int:
+    """Cores this process may use.  torchrun exports OMP_NUM_THREADS=1 to its workers, which would silently make the
+    CPU arm single-threaded; the oracle takes an explicit thread count instead."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
 def run_reference(args):
     """CPU arm: the oracle's Lloyd pass (C, OpenMP over Spark-style partitions) on all host threads."""
     rank = int(os.environ.get("RANK", "0"))
@@ -144,7 +153,7 @@ def run_reference(args):
     prof = rng.normal(size=(k, d)) * 2.0
     X = prof[rng.integers(0, k, size=n)] + rng.normal(size=(n, d)) * 0.7
     C = X[:k].copy()
-    threads = O.num_threads()
+    threads = host_threads()
     P = max(8, 4 * threads)
     for _ in range(max(args.warmup, 1)):
         O.lloyd_pass(X, C, P=P, threads=threads)
@@ -346,7 +355,7 @@ def main():
         prof = rng.normal(size=(k, d)) * 2.0
         Xh = prof[rng.integers(0, k, size=ns)] + rng.normal(size=(ns, d)) * 0.7
         Ch = Xh[:k].copy()
-        threads = O.num_threads()
+        threads = host_threads()
         O.lloyd_pass(Xh, Ch, P=4 * threads, threads=threads)
         reps, t0 = 0, time.perf_counter()
         while reps < 3 or (time.perf_counter() - t0 < 10 and reps < 200):
