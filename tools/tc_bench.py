@@ -1,5 +1,5 @@
 import sys, os
-sys.path.insert(0, "/root/repo")
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import importlib, json, torch, numpy as np
 N = importlib.import_module("clustermachinelearningforhospitalnetworks-apache-spark_b200._native")
 def bench(n, d, k, iters=10, spread=2.0):
