@@ -362,7 +362,7 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
         oth0 = fmax(oth0, shfl_xor_d(oth0, msk)); oth1 = fmax(oth1, shfl_xor_d(oth1, msk));
         xx0 += shfl_xor_d(xx0, msk); xx1 += shfl_xor_d(xx1, msk);
       }
-      if (q == 0) {
+      if (q < 2) {   // lane q = 0 finishes row t0, lane q = 1 row t1: one pass through the fp64 divisions instead of two
         auto point = [&](bool valid, int a, double xx, double own, double oth, int64_t row) {
           if (!valid || a < 0) return;
           const double wv = has_w ? p.w[row] : 1.0;
@@ -376,8 +376,7 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
           }
           cost = fma(sil, wv, cost); xxs += wv;
         };
-        point(v0, a0l, xx0, own0, oth0, row0 + t0);
-        point(v1, a1l, xx1, own1, oth1, row0 + t1);
+        point(q ? v1 : v0, q ? a1l : a0l, q ? xx1 : xx0, q ? own1 : own0, q ? oth1 : oth0, row0 + (q ? t1 : t0));
       }
     } else {
       // argmax over this lane's columns (ascending index), then across the 4 lanes of the row

@@ -136,6 +136,15 @@ __global__ void __launch_bounds__(kMmaThreads) __maxnreg__(MAXREG) lloyd_mma_ker
 
     auto process_tile = [&](auto need_xx_tag, const uint32_t xs, const int rows_valid, const int64_t row0) {
       constexpr bool NEED_XX = decltype(need_xx_tag)::value;
+      // silhouette passes: the given labels / weights of this lane's two rows are fetched first, so their global-memory
+      // latency runs under the score tiles
+      int lin0 = -1, lin1 = -1; double win0 = 1.0, win1 = 1.0;
+      if constexpr (MODE == 1 || MODE == 2) {
+        if (t0 < rows_valid) { lin0 = __ldg(p.labels_in + row0 + t0); if (has_w) win0 = __ldg(p.w + row0 + t0); }
+        if (t1 < rows_valid) { lin1 = __ldg(p.labels_in + row0 + t1); if (has_w) win1 = __ldg(p.w + row0 + t1); }
+        if (lin0 >= k) lin0 = -1;
+        if (lin1 >= k) lin1 = -1;
+      }
       // ---------------- score tiles
       const uint32_t xa0 = xs + a_frag + (uint32_t)i0 * row_bytes, xa1 = xs + a_frag + (uint32_t)i1 * row_bytes;
       double s0[NT][2], s1[NT][2];
@@ -153,9 +162,7 @@ __global__ void __launch_bounds__(kMmaThreads) __maxnreg__(MAXREG) lloyd_mma_ker
       if constexpr (MODE == 2) {
         // ---------------- silhouette score (ClusteringMetrics.pointSilhouetteCoefficient), one value per row
         const bool v0 = t0 < rows_valid, v1 = t1 < rows_valid;
-        int a0l = v0 ? p.labels_in[row0 + t0] : -1, a1l = v1 ? p.labels_in[row0 + t1] : -1;
-        if (a0l >= k) a0l = -1;
-        if (a1l >= k) a1l = -1;
+        const int a0l = lin0, a1l = lin1;
         const double ninf = -__longlong_as_double(0x7ff0000000000000LL);
         double own0 = ninf, own1 = ninf, oth0 = ninf, oth1 = ninf;
 #pragma unroll
@@ -172,10 +179,9 @@ __global__ void __launch_bounds__(kMmaThreads) __maxnreg__(MAXREG) lloyd_mma_ker
           oth0 = fmax(oth0, shfl_xor_d(oth0, msk)); oth1 = fmax(oth1, shfl_xor_d(oth1, msk));
           xx0 += shfl_xor_d(xx0, msk); xx1 += shfl_xor_d(xx1, msk);
         }
-        if (t == 0) {
-          auto point = [&](bool valid, int a, double xx, double own, double oth, int64_t row) {
+        if (t < 2) {   // lane t = 0 finishes row t0, lane t = 1 row t1: one pass through the fp64 divisions instead of two
+          auto point = [&](bool valid, int a, double xx, double own, double oth, double wv) {
             if (!valid || a < 0) return;
-            const double wv = has_w ? p.w[row] : 1.0;
             const double nrm = sqrt(xx), sn = nrm * nrm;
             const double NA = cn_s[k_pad + a];
             double sil = 0.0;
@@ -186,8 +192,7 @@ __global__ void __launch_bounds__(kMmaThreads) __maxnreg__(MAXREG) lloyd_mma_ker
             }
             cost = fma(sil, wv, cost); xxs += wv;
           };
-          point(v0, a0l, xx0, own0, oth0, row0 + t0);
-          point(v1, a1l, xx1, own1, oth1, row0 + t1);
+          point(t ? v1 : v0, t ? a1l : a0l, t ? xx1 : xx0, t ? own1 : own0, t ? oth1 : oth0, t ? win1 : win0);
         }
         return;
       }
@@ -195,11 +200,8 @@ __global__ void __launch_bounds__(kMmaThreads) __maxnreg__(MAXREG) lloyd_mma_ker
         // ---------------- silhouette statistics: labels and weights are given, phase 1 only supplied |x|^2
 #pragma unroll
         for (int msk = 1; msk <= 2; msk <<= 1) { xx0 += shfl_xor_d(xx0, msk); xx1 += shfl_xor_d(xx1, msk); }
-        const bool v0 = t0 < rows_valid, v1 = t1 < rows_valid;
-        int l0 = v0 ? p.labels_in[row0 + t0] : -1, l1 = v1 ? p.labels_in[row0 + t1] : -1;
-        if (l0 >= k) l0 = -1;
-        if (l1 >= k) l1 = -1;
-        const double w0 = (v0 && has_w) ? p.w[row0 + t0] : 1.0, w1 = (v1 && has_w) ? p.w[row0 + t1] : 1.0;
+        const int l0 = lin0, l1 = lin1;
+        const double w0 = win0, w1 = win1;
         const double n0 = sqrt(xx0), n1 = sqrt(xx1);           // squaredNorm = math.pow(Vectors.norm(features, 2.0), 2.0)
         xx0 = n0 * n0; xx1 = n1 * n1;
 #pragma unroll

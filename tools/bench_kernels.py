@@ -97,6 +97,8 @@ def kmpar(n, d, k):
 
 
 if __name__ == "__main__":
+    if "sil" in sys.argv:
+        silhouette(5_000_000, 24, 8); silhouette(10_000_000, 32, 8); silhouette(5_000_000, 24, 16); silhouette(5_000_000, 24, 32); sys.exit(0)
     if "loader" in sys.argv:
         loader(10_000_000, 32); loader(10_000_000, 24); sys.exit(0)
     lloyd(10_000_000, 32, 8, "cfg2")
