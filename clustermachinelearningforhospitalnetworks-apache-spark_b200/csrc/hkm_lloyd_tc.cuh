@@ -147,7 +147,6 @@ __global__ void __launch_bounds__(kTcThreads, 1) lloyd_tc_kernel(const LloydPara
     // gather: warp w owns clusters w, w+8, ... (slot m = label >> 3); lane = feature (and feature + 32)
     double cost = 0, xxs = 0;
     const uint32_t a_acc = a_cs + fl8;                       // per-cluster sums in shared memory: row j at j*512, this lane's feature
-    const uint32_t a_cnt = sb + L.zero_off;
     const int xx_mode = p.xx_mode;
     // per-row distances wanted (first Lloyd pass, mind2_out): every row is re-scored exactly; label-only passes
     // (predict) and steady-state Lloyd passes only re-score the ambiguous rows
@@ -169,16 +168,18 @@ __global__ void __launch_bounds__(kTcThreads, 1) lloyd_tc_kernel(const LloydPara
       for (int gg = 0; gg < 2; ++gg) {
         const int g = warp + 8 * gg;
         float part[8];
+        double2 vin[8];
+        // rows 8g .. 8g+7 sit in one 16-row chunk, row_bytes apart: all eight loads go out before the first use
+        const uint32_t ra0 = xs + (uint32_t)((8 * g) >> 4) * cstride + (uint32_t)((8 * g) & 15) * row_bytes + 16u * lane;
 #pragma unroll
         for (int rr = 0; rr < 8; ++rr) {
-          const int t = 8 * g + rr;
-          const uint32_t ra = xs + (uint32_t)(t >> 4) * cstride + (uint32_t)(t & 15) * row_bytes + 16u * lane;
+          vin[rr] = make_double2(mu0, mu1);
+          if (conv_ok) asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(vin[rr].x), "=d"(vin[rr].y) : "r"(ra0 + (uint32_t)rr * row_bytes));
+        }
+#pragma unroll
+        for (int rr = 0; rr < 8; ++rr) {
           float2 o = make_float2(0.f, 0.f);
-          if (conv_ok) {
-            double2 v;
-            asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(ra));
-            o.x = (float)(v.x - mu0); o.y = (float)(v.y - mu1);
-          }
+          if (conv_ok) { o.x = (float)(vin[rr].x - mu0); o.y = (float)(vin[rr].y - mu1); }
           part[rr] = fmaf(o.x, o.x, o.y * o.y);
           if (2 * lane < kchunks * 4)
             asm volatile("st.shared.v2.f32 [%0], {%1,%2};" ::"r"(a_conv + (uint32_t)g * 128u + (uint32_t)rr * 16u), "f"(o.x), "f"(o.y) : "memory");
@@ -205,6 +206,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) lloyd_tc_kernel(const LloydPara
     // per-cluster sums: one ballot per 32 rows finds this warp's rows (label & 7 == warp, so no two warps ever touch
     // the same cluster); each row is added to its cluster's shared-memory accumulator row, one feature (pair) per lane.
     // Two rows are in flight per step; equal labels are merged first so the read-modify-write stays race free.
+    unsigned gcnt0 = 0, gcnt1 = 0;
     auto gather_tile = [&](const uint32_t xs, const uint32_t lab_b) {
 #pragma unroll 1
       for (int g = 0; g < kTileRows / 32; ++g) {
@@ -233,10 +235,9 @@ __global__ void __launch_bounds__(kTcThreads, 1) lloyd_tc_kernel(const LloydPara
           for (int e = 0; e < FPL; ++e) { s0[e] = lds_f64(aa0 + 256u * e); if (two) s1[e] = lds_f64(aa1 + 256u * e); }
 #pragma unroll
           for (int e = 0; e < FPL; ++e) { sts_f64(aa0 + 256u * e, s0[e] + v0[e]); if (two) sts_f64(aa1 + 256u * e, s1[e] + v1[e]); }
-          if (lane == 0) {
-            sts_u32(a_cnt + 4u * (uint32_t)l0, lds_u32(a_cnt + 4u * (uint32_t)l0) + n0);
-            if (two) sts_u32(a_cnt + 4u * (uint32_t)l1, lds_u32(a_cnt + 4u * (uint32_t)l1) + 1u);
-          }
+          // rows per cluster, in registers: lane c counts clusters c and c + 32 (this warp only ever sees its own clusters)
+          gcnt0 += (l0 == lane ? n0 : 0u) + ((two && l1 == lane) ? 1u : 0u);
+          gcnt1 += (l0 == lane + 32 ? n0 : 0u) + ((two && l1 == lane + 32) ? 1u : 0u);
         }
       }
     };
@@ -404,6 +405,10 @@ __global__ void __launch_bounds__(kTcThreads, 1) lloyd_tc_kernel(const LloydPara
       const int P = k * d + k + 1;
       const int S = P + 1 + k;
       double* out = p.cta_partials + (size_t)blockIdx.x * S;
+      if ((lane & 7) == warp) {                               // this warp's clusters: w, w+8, ... (counts kept in registers by the gather)
+        unsigned int* cnt_s = reinterpret_cast<unsigned int*>(smem + L.zero_off);
+        cnt_s[lane] = gcnt0; cnt_s[lane + 32] = gcnt1;
+      }
       named_bar_sync(1, kComputeThreads);                     // every warp's gather has landed in shared memory
       if (!refine_all) {
         // steady state: the sum of the exact winner scores needs no per-row work at all:
