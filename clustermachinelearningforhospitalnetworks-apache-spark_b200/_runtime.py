@@ -73,6 +73,12 @@ class PeerExchange:
                 cls._cached = False
                 import warnings
                 warnings.warn(f"NVLink peer exchange unavailable ({type(e).__name__}: {e}); using NCCL all-reduce")
+            # every rank must take the same path: one rank on NCCL while the others spin on peer flags would hang
+            import torch.distributed as dist
+            ok = torch.tensor([1 if cls._cached else 0], dtype=torch.int32, device=dev)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if int(ok.item()) == 0:
+                cls._cached = False
         return cls._cached or None
 
     def check(self):
