@@ -1,4 +1,4 @@
-// Lloyd data pass, large-k variant (16 < k <= 64, even d <= 64): tcgen05 tensor-core screening + fp64 refinement.
+// Lloyd data pass, large-k variant (24 < k <= 64, even 32 < d <= 64): tcgen05 tensor-core screening + fp64 refinement.
 //
 // For k*d this large the fp64 pipe cannot keep up with HBM (k = 64, d = 64 needs 4096 fp64 FMA per 512-byte row), and
 // tcgen05 has no fp64 kind.  So the k distances of a row are first computed APPROXIMATELY on the 5th-gen tensor cores
