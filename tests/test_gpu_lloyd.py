@@ -236,3 +236,33 @@ def test_passes_are_bit_stable(hkm, n, d, k):
         else:
             assert torch.equal(ref[0], cur[0]) and torch.equal(ref[1], cur[1])
     assert int(ref[0][k * d:k * d + k].sum().item()) == n
+
+
+@pytest.mark.parametrize("n,d,k", [(36_000_000, 64, 64), (70_000_000, 32, 8), (90_000_000, 24, 32)])
+def test_more_than_2_31_elements(hkm, n, d, k):
+    """n * d > 2^31 (cfg3 / cfg4 sized shards): 64-bit row addressing in every variant.  Properties that need no oracle:
+    counts add up and equal the histogram of the labels, per-cluster sums add up to the column totals, and the labels
+    of the LAST rows (beyond element 2^31) are the fp64 argmin computed by torch."""
+    assert n * d > 2 ** 31
+    N = hkm._native
+    g = torch.Generator(device="cuda"); g.manual_seed(n % 1000 + d)
+    prof = torch.randn(k, d, dtype=torch.float64, device="cuda", generator=g) * 2
+    X = torch.empty(n, d, dtype=torch.float64, device="cuda")
+    step = 4_000_000
+    for lo in range(0, n, step):                     # generated in slabs: no second full-size temporary
+        hi = min(n, lo + step)
+        X[lo:hi] = prof[torch.randint(0, k, (hi - lo,), device="cuda", generator=g)] + torch.randn(hi - lo, d, dtype=torch.float64, device="cuda", generator=g)
+    C = prof + 0.05
+    partial = torch.empty(k * d + k + 1, dtype=torch.float64, device="cuda")
+    labels = torch.empty(n, dtype=torch.int32, device="cuda")
+    N.assign_reduce(X, C, partial, labels, scratch=N.new_scratch(d, k, "cuda"))
+    counts = partial[k * d:k * d + k]
+    assert counts.sum().item() == n
+    assert torch.equal(counts, torch.bincount(labels, minlength=k).double())
+    col = torch.zeros(d, dtype=torch.float64, device="cuda")
+    for lo in range(0, n, step):
+        col += X[lo:lo + step].sum(0)
+    assert torch.allclose(partial[:k * d].view(k, d).sum(0), col, rtol=1e-9, atol=1e-5)
+    tail = X[n - 200_000:]
+    d2 = (tail * tail).sum(1, keepdim=True) - 2.0 * tail @ C.T + (C * C).sum(1)[None, :]
+    assert (d2.argmin(1).int() == labels[n - 200_000:]).float().mean().item() >= 0.99999
