@@ -238,7 +238,7 @@ def test_passes_are_bit_stable(hkm, n, d, k):
     assert int(ref[0][k * d:k * d + k].sum().item()) == n
 
 
-@pytest.mark.parametrize("n,d,k", [(36_000_000, 64, 64), (70_000_000, 32, 8), (90_000_000, 24, 32)])
+@pytest.mark.parametrize("n,d,k", [(36_000_000, 64, 64), (70_000_000, 32, 8), (90_000_000, 24, 32), (46_000_000, 48, 24)])
 def test_more_than_2_31_elements(hkm, n, d, k):
     """n * d > 2^31 (cfg3 / cfg4 sized shards): 64-bit row addressing in every variant.  Properties that need no oracle:
     counts add up and equal the histogram of the labels, per-cluster sums add up to the column totals, and the labels
