@@ -187,3 +187,23 @@ def test_cosine_distance_measure(hkm, oracle, init_mode):
     S[2] = 0.0
     with pytest.raises(hkm.IllegalArgumentException, match="zero-length"):
         KMeans(k=2, distanceMeasure="cosine").fit({"features": S})
+
+
+def test_fit_and_evaluate_beyond_2_31_elements(hkm):
+    """One whole fit (k-means||, 3 Lloyd steps, summary pass) + silhouette on a 70 M x 32 device-resident table
+    (2.24e9 elements, 17.9 GB): every kernel on the path addresses rows in 64 bits."""
+    from hkm_b200 import datagen
+    from hkm_b200.table import Table, DeviceMatrix
+    from hkm_b200.ml.clustering import KMeans
+    from hkm_b200.ml.evaluation import ClusteringEvaluator
+    n, d, k = 70_000_000, 32, 6
+    X = datagen.hospital_matrix_device(n, d, k, 20250331, torch.device("cuda"))
+    t = Table({"features": DeviceMatrix(X)})
+    model = KMeans(k=k, seed=3, maxIter=3).fit(t)
+    s = model.summary
+    assert sum(s.clusterSizes) == n and s.numIter >= 1 and s.trainingCost > 0
+    pred = s.predictions["prediction"].values
+    assert int(pred.min().item()) >= 0 and int(pred.max().item()) < k
+    assert torch.equal(torch.bincount(pred, minlength=k).cpu(), torch.tensor(s.clusterSizes))
+    sil = ClusteringEvaluator().evaluate(s.predictions)
+    assert -1.0 <= sil <= 1.0
