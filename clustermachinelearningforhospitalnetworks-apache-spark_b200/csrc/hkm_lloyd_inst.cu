@@ -49,7 +49,8 @@ template <int KS_T, int NT, int MODE = 0>
 static int launch_mma(LloydParams p, int grid, cudaStream_t st) {
   const LaunchPlan pl = plan_lloyd_mma(p.d, NT * 8);
   p.stages = pl.stages;
-  auto kern = lloyd_mma_kernel<KS_T, NT, 96, MODE>;
+  constexpr int MAXREG = (KS_T <= 2 && NT == 1 && MODE == 0) ? 64 : 96;   // thin rows: three CTAs per SM
+  auto kern = lloyd_mma_kernel<KS_T, NT, MAXREG, MODE>;
   static int attr_smem[64];
   int dev = 0; HKM_CUDA_TRY(cudaGetDevice(&dev));
   if (dev >= 64 || attr_smem[dev] < pl.smem) {
@@ -102,7 +103,7 @@ int HKM_CAT(dispatch_lloyd_nt, HKM_NT)(const LloydParams& p, const LaunchPlan& p
   const int ks = p.ks;
   // silhouette passes: k <= 16 on the barrier-free tensor-pipe kernel, larger k on the gather kernel
   if constexpr (NT <= 2) {
-    if ((mode == 1 || mode == 2) && ks <= 16 && ks * NT <= 32 && pl.ctas_per_sm == 2 && plan_lloyd_mma(p.d, NT * 8).stages >= 3 &&
+    if ((mode == 1 || mode == 2) && ks <= 16 && ks * NT <= 32 && pl.ctas_per_sm >= 2 && plan_lloyd_mma(p.d, NT * 8).stages >= 3 &&
         lloyd_variant_override() != 1 && (mode == 2 || NT * ((ks + 1) / 2 + 1) <= 14)) {
 #define HKM_SIL(KS) if (ks == KS) return mode == 1 ? launch_mma<KS, NT, 1>(p, grid, st) : launch_mma<KS, NT, 2>(p, grid, st);
 #ifndef HKM_DEV_FAST
@@ -140,7 +141,7 @@ int HKM_CAT(dispatch_lloyd_nt, HKM_NT)(const LloydParams& p, const LaunchPlan& p
     // k <= 16: reduce on the tensor pipe as well (see hkm_lloyd_mma.cuh) when the pass is a plain Lloyd step
     const int variant = lloyd_variant_override();
     const bool eligible = p.do_reduce == 1 && p.out_mode == 0 && ks <= 16 && ks * NT <= 32 && plan_lloyd_mma(p.d, NT * 8).stages >= 3;
-    if (eligible && variant != 1 && pl.ctas_per_sm == 2) {
+    if (eligible && variant != 1 && pl.ctas_per_sm >= 2) {
 #define HKM_MMA(KS) if (ks == KS) return launch_mma<KS, NT>(p, grid, st);
 #ifndef HKM_DEV_FAST
       HKM_MMA(1) HKM_MMA(2) HKM_MMA(3) HKM_MMA(5) HKM_MMA(7) HKM_MMA(10) HKM_MMA(12) HKM_MMA(16)

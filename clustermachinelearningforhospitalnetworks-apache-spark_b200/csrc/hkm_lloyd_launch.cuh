@@ -11,11 +11,21 @@ namespace hkm {
 
 struct LaunchPlan { int stages; int ctas_per_sm; int smem; };
 
+// thin rows (d <= 8, k <= 8: the hospital table's own shape): the pass is bound by per-row latency, not by bytes or
+// the tensor pipe, so three CTAs share an SM (64 registers)
+inline bool plan_thin(int d, int k_pad) { return d <= 8 && k_pad <= 8; }
+
 inline LaunchPlan plan_lloyd(int d, int k_pad) {
   // two CTAs per SM when at least 3 stages fit in ~112 KB each, else one CTA with a deep ring
   LaunchPlan pl{};
   const int budget2 = 112 * 1024, budget1 = 224 * 1024;
   const int fixed = smem_layout(d, k_pad, 0).total;
+  if (plan_thin(d, k_pad)) {
+    const int st = (74 * 1024 - fixed) / stage_bytes(d);
+    pl.stages = st > kMaxStages ? kMaxStages : st; pl.ctas_per_sm = 3;
+    pl.smem = smem_layout(d, k_pad, pl.stages).total;
+    return pl;
+  }
   int st2 = (budget2 - fixed) / stage_bytes(d);
   if (st2 >= 3) { pl.stages = st2 > kMaxStages ? kMaxStages : st2; pl.ctas_per_sm = 2; }
   else {
@@ -26,14 +36,14 @@ inline LaunchPlan plan_lloyd(int d, int k_pad) {
   return pl;
 }
 
-// Plan for the small-k tensor-pipe variant (hkm_lloyd_mma.cuh): always two CTAs of 9 warps per SM.
+// Plan for the small-k tensor-pipe variant (hkm_lloyd_mma.cuh): two CTAs of 9 warps per SM (three for thin rows).
 inline LaunchPlan plan_lloyd_mma(int d, int k_pad) {
   LaunchPlan pl{};
-  const int budget2 = 112 * 1024;
+  const int budget2 = plan_thin(d, k_pad) ? 74 * 1024 : 112 * 1024;
   const int fixed = mma_smem_layout(d, k_pad, 0).total;
   int st = (budget2 - fixed) / stage_bytes(d);
   pl.stages = st > kMaxStages ? kMaxStages : st;
-  pl.ctas_per_sm = 2;
+  pl.ctas_per_sm = plan_thin(d, k_pad) ? 3 : 2;
   pl.smem = mma_smem_layout(d, k_pad, pl.stages > 0 ? pl.stages : 0).total;
   return pl;
 }
