@@ -27,12 +27,14 @@ def _units(dev_fast: bool):
     units = [("hkm_api", "hkm_api.cu", [])]
     for extra in sorted(glob.glob(os.path.join(CSRC, "hkm_*.cu"))):
         base = os.path.basename(extra)
-        if base in ("hkm_api.cu", "hkm_lloyd_inst.cu"):
+        if base in ("hkm_api.cu", "hkm_lloyd_inst.cu", "hkm_lloyd_tp_inst.cu"):
             continue
         units.append((base[:-3], base, []))
     for nt in range(1, 9):
         flags = [f"-DHKM_NT={nt}"] + (["-DHKM_DEV_FAST"] if dev_fast else [])
         units.append((f"hkm_lloyd_nt{nt}" + ("_dev" if dev_fast else ""), "hkm_lloyd_inst.cu", flags))
+    for kp in (16, 32, 48, 64):
+        units.append((f"hkm_lloyd_tp{kp}", "hkm_lloyd_tp_inst.cu", [f"-DHKM_TP_KP={kp}"]))
     return units
 
 

@@ -14,7 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(_HERE, "csrc", "libhkm.so")
 
 EXPORTS = (
-    "hkm_last_error", "hkm_version", "hkm_max_k", "hkm_max_d",
+    "hkm_last_error", "hkm_version", "hkm_max_k", "hkm_max_d", "hkm_set_lloyd_variant",
     "hkm_assign_reduce_scratch_bytes", "hkm_assign_reduce", "hkm_update_centers", "hkm_update_centers_cosine", "hkm_lloyd_step", "hkm_lloyd_step_peer", "hkm_peer_exchange_bytes",
     "hkm_kmpar_scratch_bytes", "hkm_kmpar_cost_update", "hkm_kmpar_sample", "hkm_kmpar_strip_rows", "hkm_closest_counts",
     "hkm_silhouette_stats", "hkm_silhouette_score",
@@ -97,6 +97,11 @@ def _ptr(t):
 
 def _stream():
     return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def set_lloyd_variant(variant: int) -> None:
+    """hkm_set_lloyd_variant: pin one kernel family for the Lloyd passes (0 = automatic); tuning and tests only."""
+    _check(load().hkm_set_lloyd_variant(int(variant)))
 
 
 def assign_reduce_scratch_bytes(d: int, k: int) -> int:

@@ -15,14 +15,8 @@ int cuda_fail(cudaError_t e, const char* what) {
   set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
   return HKM_ERR_CUDA;
 }
-int lloyd_variant_override() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("HKM_LLOYD_VARIANT");
-    v = e == nullptr ? 0 : (strcmp(e, "gather") == 0 ? 1 : (strcmp(e, "mma") == 0 ? 2 : (strcmp(e, "ws") == 0 ? 3 : 0)));
-  }
-  return v;
-}
+static int g_lloyd_variant = 0;   // hkm_set_lloyd_variant: 0 pick per shape; 1..5 pin one kernel family (tuning / tests)
+int lloyd_variant_override() { return g_lloyd_variant; }
 int sm_count() {
   static int cached[64]; static bool have[64];
   int dev = 0;
@@ -126,7 +120,9 @@ int assign_pass(const AssignArgs& a, const char* who) {
   p.stages = pl.stages; p.ks = (d + 3) / 4;
   const int grid = sm_count() * pl.ctas_per_sm;
   const int mode = (a.mode == 0 && a.weights != nullptr) ? 3 : a.mode;   // weights are a compile-time property of the Lloyd kernels
-  if (lloyd_tc_eligible(p, mode) && lloyd_variant_override() != 1)       // large k*d: tensor-core screening + fp64 refinement
+  if (lloyd_tp_eligible(p, mode))                                        // k > 8 plain passes: pipelined tcgen05 screening + fp64 refinement
+    return launch_lloyd_tp(p, reinterpret_cast<cudaStream_t>(a.stream));
+  if (lloyd_tc_eligible(p, mode) && lloyd_variant_override() != 1 && lloyd_variant_override() != 4)   // its unpipelined predecessor (weights / distances)
     return launch_lloyd_tc(p, reinterpret_cast<cudaStream_t>(a.stream));
   return dispatch_lloyd(p, pl, grid, mode, reinterpret_cast<cudaStream_t>(a.stream));
 }
@@ -141,6 +137,11 @@ const char* hkm_last_error(void) { return g_err; }
 int hkm_version(void) { return 100; }
 int hkm_max_k(void) { return 64; }
 int hkm_max_d(void) { return 96; }
+int hkm_set_lloyd_variant(int variant) {
+  if (variant < 0 || variant > 5) { set_error("hkm_set_lloyd_variant: 0..5"); return HKM_ERR_INVALID; }
+  g_lloyd_variant = variant;
+  return HKM_OK;
+}
 
 size_t hkm_assign_reduce_scratch_bytes(int d, int k) {
   if (d < 1 || k < 1) return 0;

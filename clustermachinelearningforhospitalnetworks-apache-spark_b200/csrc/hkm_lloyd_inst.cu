@@ -125,7 +125,7 @@ int HKM_CAT(dispatch_lloyd_nt, HKM_NT)(const LloydParams& p, const LaunchPlan& p
     // at d = 29..32, k = 25..32 from d = 17 up except d = 25..28 (centre fragments no longer fit in registers there),
     // k > 32 everywhere
     const bool wins = NT >= 5 ? true : (NT == 4 ? (p.d > 16 && ks != 7) : ks == 8);
-    const bool wanted = variant == 3 || (variant == 0 && wins);
+    const bool wanted = variant == 3 || ((variant == 0 || variant == 5) && wins);
     if (mode == 0 && p.do_reduce == 1 && p.out_mode == 0 && fits && wanted) {
       const int grid1 = grid / (pl.ctas_per_sm > 0 ? pl.ctas_per_sm : 1);
 #define HKM_WS(KS) if constexpr (KS * NT <= 24) { if (ks == KS) return launch_ws<KS, NT>(p, grid1, st); }

@@ -1,0 +1,37 @@
+// Host side of the pipelined tensor-core Lloyd pass (hkm_lloyd_tp.cuh): shape rules and per-k_pad dispatch.
+#include "../../include/hkm.h"
+#include "hkm_lloyd_launch.cuh"
+#include "hkm_lloyd_tp.cuh"
+
+namespace hkm {
+
+int dispatch_lloyd_tp16(const LloydParams&, const TpPlan&, cudaStream_t);
+int dispatch_lloyd_tp32(const LloydParams&, const TpPlan&, cudaStream_t);
+int dispatch_lloyd_tp48(const LloydParams&, const TpPlan&, cudaStream_t);
+int dispatch_lloyd_tp64(const LloydParams&, const TpPlan&, cudaStream_t);
+
+// Plain passes (unit weights, labels and/or sums, no per-row distances) with 8 < k <= 64 and d <= 64 (odd d only up to 32).
+bool lloyd_tp_eligible(const LloydParams& p, int mode) {
+  const int variant = lloyd_variant_override();
+  if (variant != 0 && variant != 4) return false;
+  if (mode != 0 || p.w != nullptr || p.out_mode != 0 || p.mind2_out != nullptr || p.do_reduce > 1) return false;
+  if (p.k > 64 || p.d > 64 || ((p.d & 1) && p.d > 32)) return false;
+  if (p.k <= 8 && variant != 4) return false;               // k <= 8 stays on the fp64 tensor-pipe kernel (HBM-bound already)
+  const int kp = ((p.k + 15) / 16) * 16;
+  return tp_choose(p.d, kp).stages >= 2;
+}
+
+int launch_lloyd_tp(const LloydParams& p, cudaStream_t st) {
+  const int kp = ((p.k + 15) / 16) * 16;
+  const TpPlan L = tp_choose(p.d, kp);
+  switch (kp) {
+    case 16: return dispatch_lloyd_tp16(p, L, st);
+    case 32: return dispatch_lloyd_tp32(p, L, st);
+    case 48: return dispatch_lloyd_tp48(p, L, st);
+    case 64: return dispatch_lloyd_tp64(p, L, st);
+  }
+  set_error("lloyd_tp: k=%d outside 1..64", p.k);
+  return HKM_ERR_UNSUPPORTED;
+}
+
+}  // namespace hkm

@@ -1,0 +1,653 @@
+// Lloyd data pass, pipelined tensor-core variant (8 < k <= 64, d <= 64): tcgen05 screening + fp64 refinement with the
+// roles of one CTA per SM split over specialised warps, so conversion, MMA, screening and the per-cluster reduction of
+// consecutive 128-row tiles overlap.
+//
+// Why: for k > 8 the fp64 tensor pipe cannot score AND reduce at the HBM rate (k = 16, d = 16 needs 8 fp64 FMA per
+// byte streamed).  tcgen05 has no fp64 kind, so the k scores of a row are first computed approximately in tf32
+// (operands centred by mu = mean of the centres, rounded to nearest tf32 by the CUDA cores, accumulator in TMEM) with a
+// rigorous error bound
+//     |approx_j - exact_j| <= eps = kappa |x - mu| max_j |c_j - mu| + eta max_j |c_j - mu|^2,   kappa = 1.04 * 2^-10
+// (two operands rounded to 11 bits each, fp32 accumulation over K <= 72 terms, 6 index bits packed into the score).
+// A row whose best approximate score beats the second best by more than 2 eps is decided; any other row goes to a
+// list and is re-scored exactly in fp64 against every centre within 2 eps of the best, with the same score, tie rule
+// (lowest index) and arithmetic as the fp64 kernels.  The tensor cores only prune; labels are the fp64 argmax.
+//
+// Warp roles (18 warps, 576 threads, one CTA per SM):
+//   screen   4 or 8 warps (one or two groups of four; group g takes tiles i = g mod groups): thread = tile row; reads
+//            the row's tf32 operand back for |x - mu|, sweeps the TMEM accumulator once (top-2 with the centre index
+//            packed into the low mantissa bits), decides or lists the row, then the group re-scores its listed rows
+//            cooperatively (lane = feature pair) and publishes the tile's labels.
+//   reduce   8 or 4 warps: per-cluster fp64 sums in shared memory.  Small k*d: every warp owns private accumulator sets
+//            and a fixed share of the tile's rows (several rows per instruction, each in its own set; no ballots, no
+//            imbalance).  Large k*d: one shared set, warp r owns the clusters j = r mod R.
+//   convert  4 warps: fp64 stage -> (x - mu) rounded to tf32 -> canonical K-major UMMA operand.
+//   producer 1 warp: 1-D bulk-async copies into the ring;   mma 1 warp: one thread issues tcgen05.mma + commit.
+// Everything meets through mbarriers (full/empty per ring stage, per operand buffer, per TMEM buffer, labels-ready
+// per stage); the only CTA barrier is at the end.  Constant -0.5|c - mu|^2 rides inside the MMA as three extra K
+// columns (a tf32 hi/mid/lo split against a column of ones), so the sweep is 4 instructions per centre.
+// Rows per cluster are counted with shared-memory integer atomics; the cost needs no per-row work:
+//     sum_rows (x.c_label - 0.5|c_label|^2) = sum_j S_j.c_j - 0.5 sum_j n_j |c_j|^2.
+// Summation order is fixed (row order within a reduce warp, set order in the combine, CTA order in the fold), so
+// results are bit-stable.  Plain passes only (unit weights, no per-row distances); the dispatcher sends the rest elsewhere.
+#pragma once
+#include "hkm_lloyd.cuh"
+
+namespace hkm {
+
+constexpr int kTpWarps = 18;
+constexpr int kTpThreads = kTpWarps * 32;
+constexpr int kTpConvWarps = 4;
+constexpr int kTpConvWarp0 = 12, kTpProdWarp = 16, kTpMmaWarp = 17;
+__host__ __device__ constexpr int tp_reduce_warps(int sg) { return 12 - 4 * sg; }   // screen groups of four warps + reduce warps = 12
+__host__ __device__ constexpr int tp_tmem_stride(int kp) { return kp <= 32 ? 32 : (kp <= 64 ? 64 : (kp <= 128 ? 128 : 256)); }
+
+__host__ __device__ inline int tp_pow2ceil(int v) { int p = 1; while (p < v) p <<= 1; return p; }
+
+// reduce modes: 0 private sets, lane = feature (d <= 32); 1 private sets, lane = feature pair (even d <= 64);
+//               2 one shared set, clusters owned per warp, lane = feature pair (even d <= 64)
+struct TpPlan {
+  int stages, rmode, na, sg;   // ring depth, reduce mode, tf32 operand buffers (1 or 2), screen groups (1 or 2)
+  int c_lpr, c_g;            // converter: lanes per row, rows per instruction
+  int r_lpr, r_g, ald, nsets;  // reducer: lanes per row, rows per instruction, accumulator row (doubles), sets
+  int kchunks, lbo_a, lbo_b, a_bytes;
+  int x_off, a_off, b_off, acc_off, cn_off, mu_off, cnt_off, lab_off, list_off, lcnt_off, red_off, bar_off, tmem_off, total;
+};
+
+__host__ __device__ inline TpPlan tp_plan(int d, int kp, int stages, int rmode, int na, int sg) {
+  TpPlan L{};
+  L.stages = stages; L.rmode = rmode; L.na = na; L.sg = sg;
+  const int cvec = (d & 1) ? 1 : 2;
+  int cl = tp_pow2ceil((d + cvec - 1) / cvec); if (cl < 4) cl = 4; if (cl > 32) cl = 32;
+  L.c_lpr = cl; L.c_g = 32 / cl;
+  const int R = tp_reduce_warps(sg);
+  if (rmode == 2) { L.r_lpr = 32; L.r_g = 1; L.ald = 64; L.nsets = 1; }
+  else {
+    const int rvec = rmode == 0 ? 1 : 2;
+    int rl = tp_pow2ceil((d + rvec - 1) / rvec); if (rl < 4) rl = 4; if (rl > 32) rl = 32;
+    L.r_lpr = rl; L.r_g = 32 / rl; L.ald = rl * rvec; L.nsets = R * L.r_g;
+  }
+  const int d8 = (d + 7) & ~7;
+  L.kchunks = (d8 + 8) / 4;
+  const int pad_a = 8 * L.c_g > 16 ? 8 * L.c_g : 16;
+  L.lbo_a = (kTileRows / 8) * 128 + pad_a;
+  L.lbo_b = (kp / 8) * 128 + 16;
+  L.a_bytes = (L.kchunks * L.lbo_a + 127) & ~127;
+  int o = 0;
+  L.x_off = o; o += stages * stage_bytes(d); o = (o + 127) & ~127;
+  L.a_off = o; o += na * L.a_bytes;
+  L.b_off = o; o += (L.kchunks * L.lbo_b + 127) & ~127;
+  L.acc_off = o; o += L.nsets * kp * L.ald * 8;
+  L.cn_off = o; o += kp * 8;
+  L.mu_off = o; o += (d8 + 8) * 8;
+  L.cnt_off = o; o += kp * 4;
+  L.lab_off = o; o += (stages > 0 ? stages : 2) * kTileRows * 4;
+  L.list_off = o; o += sg * 2 * kTileRows * 16;       // [group][parity][row] entries {row, mask_lo, mask_hi, -}
+  L.lcnt_off = o; o += 2 * 4 * 4;                     // [group][3] entry counters
+  L.red_off = o; o += (2 * kTpWarps + 64) * 8;
+  L.bar_off = o; o += (3 * kMaxStages + 8) * 8;
+  L.tmem_off = o; o += 16;
+  L.total = o;
+  return L;
+}
+
+// Picks reduce mode, operand buffering, screen groups and ring depth for a shape; stages < 2 => the shape does not fit.
+// Preference: two screen groups for k > 32, private accumulator sets, two operand buffers -- whatever of that still
+// leaves three ring stages; failing that, the combination with the deepest ring.
+__host__ inline TpPlan tp_choose(int d, int kp) {
+  const int budget = 227 * 1024 - 1024;
+  TpPlan best{}; best.stages = 0;
+  const int sg_pref = kp >= 48 ? 2 : 1;
+  for (int si = 0; si < 2; ++si) {
+    const int sg = si == 0 ? sg_pref : 3 - sg_pref;
+    if (sg == 2 && kp < 48) continue;
+    for (int mi = 0; mi < 2; ++mi) {
+      const int rm = mi == 0 ? (d <= 32 ? 0 : 1) : 2;
+      if (rm == 2 && (d & 1)) continue;
+      if (rm == 1 && (d & 1)) continue;
+      for (int na = 2; na >= 1; --na) {
+        const int fixed = tp_plan(d, kp, 2, rm, na, sg).total - 2 * stage_bytes(d) - 2 * kTileRows * 4;
+        int st = (budget - fixed) / (stage_bytes(d) + kTileRows * 4);
+        if (st > kMaxStages) st = kMaxStages;
+        if (st < 2) continue;
+        if (st >= 3) return tp_plan(d, kp, st, rm, na, sg);
+        if (st > best.stages) best = tp_plan(d, kp, st, rm, na, sg);
+      }
+    }
+  }
+  return best;
+}
+
+__device__ __forceinline__ uint32_t f32_to_tf32_rn(float v) { uint32_t r; asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v)); return r; }
+__device__ __forceinline__ uint64_t tp_desc_kmajor(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  // K-major, no swizzle: element (row r, 16-byte chunk c) sits at (r % 8) * 16 + (r / 8) * SBO + c * LBO
+  return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16) | ((uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32) |
+         ((uint64_t)1 << 46);
+}
+__device__ __forceinline__ void tp_tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+                 "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+               : "r"(taddr));
+}
+// mbarrier wait with a watchdog: a protocol bug must end the kernel with a message, not hang the GPU
+static __device__ __noinline__ void tp_wait_timeout(uint32_t bar, uint32_t parity, int tag) {
+  const long long t0 = clock64();
+  while (!mbar_test_a(bar, parity)) {
+    if (clock64() - t0 > 6000000000LL) {   // ~3 s
+      printf("lloyd_tp: block %d warp %d stuck on barrier tag %d (smem 0x%x, parity %u)\n", (int)blockIdx.x, (int)(threadIdx.x >> 5), tag, bar, parity);
+      __trap();
+    }
+  }
+}
+__device__ __forceinline__ void tp_wait(uint32_t bar, uint32_t parity, int tag) {
+  if (mbar_test_a(bar, parity)) return;
+  if (mbar_test_a(bar, parity)) return;
+  tp_wait_timeout(bar, parity, tag);
+}
+__device__ __forceinline__ void tp_tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ void mbar_arrive_a(uint32_t bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
+__device__ __forceinline__ void lds_v2f64(uint32_t a, double& x, double& y) { asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(x), "=d"(y) : "r"(a)); }
+__device__ __forceinline__ void sts_v2f64(uint32_t a, double x, double y) { asm volatile("st.shared.v2.f64 [%0], {%1,%2};" ::"r"(a), "d"(x), "d"(y) : "memory"); }
+
+// KP = padded cluster count (16, 32, 48, 64); CVEC = 2 (even d) or 1; RMODE as in TpPlan; SG = screen groups.
+template <int KP, int CVEC, int RMODE, int SG>
+__global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydParams p, const TpPlan L) {
+  if (p.skip != nullptr && *p.skip != 0) return;
+  constexpr int R = tp_reduce_warps(SG);
+  constexpr int NW = (KP + 31) / 32;              // candidate mask words
+  constexpr int TSTRIDE = tp_tmem_stride(KP);
+  constexpr int TCOLS = 2 * TSTRIDE;
+  constexpr int IDXBITS = 6;
+  constexpr uint32_t IDXMASK = (1u << IDXBITS) - 1u;
+  static_assert(KP % 16 == 0 && KP >= 16 && KP <= 64, "k_pad: 16..64 in steps of 16");
+
+  extern __shared__ __align__(1024) unsigned char smem[];
+  const int d = p.d, k = p.k;
+  const int S = L.stages;
+  const uint32_t sb = smem_u32(smem);
+  const uint32_t a_x = sb + L.x_off, a_A = sb + L.a_off, a_B = sb + L.b_off, a_acc = sb + L.acc_off;
+  const uint32_t a_lab = sb + L.lab_off, a_list = sb + L.list_off, a_lcnt = sb + L.lcnt_off, a_cnt = sb + L.cnt_off;
+  const uint32_t a_bar = sb + L.bar_off;
+  const uint32_t b_full = a_bar, b_sempty = a_bar + 8u * kMaxStages, b_lfull = a_bar + 16u * kMaxStages;
+  const uint32_t b_afull = a_bar + 24u * kMaxStages, b_aempty = b_afull + 16u, b_tfull = b_afull + 32u, b_tempty = b_afull + 48u;
+  double* cn_s = reinterpret_cast<double*>(smem + L.cn_off);
+  double* mu_s = reinterpret_cast<double*>(smem + L.mu_off);
+  double* red_s = reinterpret_cast<double*>(smem + L.red_off);
+  unsigned int* cnt_s = reinterpret_cast<unsigned int*>(smem + L.cnt_off);
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t cstride = (uint32_t)chunk_stride_bytes(d);
+  const uint32_t sbytes = (uint32_t)stage_bytes(d);
+  const uint32_t row_bytes = (uint32_t)d * 8u;
+  const int d8 = (d + 7) & ~7;
+  const uint32_t LBO_A = (uint32_t)L.lbo_a, LBO_B = (uint32_t)L.lbo_b;
+  const int64_t full_tiles = p.n / kTileRows;
+  const int tail_rows = (int)(p.n - full_tiles * kTileRows);
+  const int my_tiles = full_tiles > (int64_t)blockIdx.x ? (int)((full_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
+  const bool tail_mine = tail_rows > 0 && (int)(full_tiles % gridDim.x) == (int)blockIdx.x;
+  const int T = my_tiles + (tail_mine ? 1 : 0);    // the ragged tail is this CTA's last tile
+  const bool do_reduce = p.do_reduce == 1;
+  const int xx_mode = p.xx_mode;
+  const bool na2 = L.na == 2;
+
+  // ------------------------------------------------------------------ one-time set-up
+  if (tid == 0) {
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bar_off);
+    for (int s = 0; s < S; ++s) {
+      mbar_init(bars + s, 1);
+      mbar_init(bars + kMaxStages + s, do_reduce ? R : 4);
+      mbar_init(bars + 2 * kMaxStages + s, 4);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(bars + 3 * kMaxStages + b, kTpConvWarps);      // afull
+      mbar_init(bars + 3 * kMaxStages + 2 + b, 4);             // aempty
+      mbar_init(bars + 3 * kMaxStages + 4 + b, 1);             // tfull
+      mbar_init(bars + 3 * kMaxStages + 6 + b, 4);             // tempty
+    }
+    mbar_fence_init();
+  }
+  if (warp == kTpProdWarp) {   // the producer warp owns the TMEM allocation
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(sb + L.tmem_off), "n"(TCOLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  // zero: both A operands, B, the accumulators, counters
+  for (int i = tid; i < (L.acc_off - L.a_off) / 16; i += kTpThreads) reinterpret_cast<uint4*>(smem + L.a_off)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = tid; i < (L.nsets * KP * L.ald) / 2; i += kTpThreads) reinterpret_cast<uint4*>(smem + L.acc_off)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = tid; i < KP; i += kTpThreads) cnt_s[i] = 0u;
+  if (tid < 8) reinterpret_cast<unsigned int*>(smem + L.lcnt_off)[tid] = 0u;
+  if (tid < d8 + 8) { double s = 0; if (tid < d) for (int j = 0; j < k; ++j) s += p.C[(size_t)j * d + tid]; mu_s[tid] = tid < d ? s / k : 0.0; }   // mu = mean of the centres
+  __syncthreads();
+  double* h_s = red_s + 2 * kTpWarps;   // [KP] |c - mu|^2, later the centre-update scratch
+  if (tid < KP) {
+    double s = 0, sc = 0;
+    if (tid < k) for (int f = 0; f < d; ++f) { const double c = p.C[(size_t)tid * d + f], cc = c - mu_s[f]; s = fma(c, c, s); sc = fma(cc, cc, sc); }
+    cn_s[tid] = tid < k ? -0.5 * s : -__longlong_as_double(0x7ff0000000000000LL);
+    h_s[tid] = tid < k ? sc : 0.0;
+  }
+  // B operand: tf32(c - mu) in the canonical K-major layout, then the constant -0.5|c - mu|^2 as a hi/mid/lo tf32 split in
+  // K columns d8, d8+1, d8+2 (padding centres get -1e30 there: never the best, never a candidate)
+  for (int i = tid; i < KP * (d8 / 4); i += kTpThreads) {
+    const int j = i % KP, c = i / KP;
+    uint32_t vv[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) { const int f = 4 * c + e; vv[e] = (j < k && f < d) ? f32_to_tf32_rn((float)(p.C[(size_t)j * d + f] - mu_s[f])) : 0u; }
+    *reinterpret_cast<uint4*>(smem + L.b_off + c * LBO_B + (j >> 3) * 128 + (j & 7) * 16) = make_uint4(vv[0], vv[1], vv[2], vv[3]);
+  }
+  // A operands: the column of ones that multiplies the constant (written once; the converters never touch it)
+  for (int i = tid; i < L.na * kTileRows; i += kTpThreads) {
+    const int b = i / kTileRows, r = i % kTileRows;
+    const uint32_t one = __float_as_uint(1.0f);
+    *reinterpret_cast<uint4*>(smem + L.a_off + b * L.a_bytes + (d8 / 4) * LBO_A + r * 16) = make_uint4(one, one, one, 0u);
+  }
+  __syncthreads();
+  if (tid < KP) {
+    const double h = tid < k ? -0.5 * h_s[tid] : -1e30;
+    const float hi = __uint_as_float(f32_to_tf32_rn((float)h));
+    const double r1 = h - (double)hi;
+    const float mid = __uint_as_float(f32_to_tf32_rn((float)r1));
+    const double r2 = r1 - (double)mid;
+    const float lo = __uint_as_float(f32_to_tf32_rn((float)r2));
+    *reinterpret_cast<uint4*>(smem + L.b_off + (d8 / 4) * LBO_B + (tid >> 3) * 128 + (tid & 7) * 16) =
+        make_uint4(__float_as_uint(hi), __float_as_uint(mid), __float_as_uint(lo), 0u);
+  }
+  float vmax2 = 0.f;
+  for (int j = 0; j < k; ++j) vmax2 = fmaxf(vmax2, (float)h_s[j]);
+  const float vmax = sqrtf(vmax2) * 1.0001f;
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = *reinterpret_cast<const uint32_t*>(smem + L.tmem_off);
+
+  double cost = 0, xxs = 0;
+
+  if (warp == kTpProdWarp) {
+    // ===================================================================== producer
+    const uint32_t cbytes = (uint32_t)kChunkRows * row_bytes;
+    const size_t tile_gbytes = (size_t)kTileRows * row_bytes;
+    const unsigned char* src = reinterpret_cast<const unsigned char*>(p.X) + (size_t)blockIdx.x * tile_gbytes;
+    const size_t src_step = (size_t)gridDim.x * tile_gbytes;
+    int s = 0; uint32_t ph = 0;
+    for (int i = 0; i < T; ++i) {
+      if (lane == 0) tp_wait(b_sempty + 8u * (uint32_t)s, ph ^ 1u, 7);
+      __syncwarp();
+      const uint32_t bar = b_full + 8u * (uint32_t)s, dst = a_x + (uint32_t)s * sbytes;
+      if (i < my_tiles) {
+        if (lane == 0) {
+          mbar_expect_tx_a(bar, cbytes * kChunks);
+#pragma unroll
+          for (int c = 0; c < kChunks; ++c) bulk_g2s_a(dst + c * cstride, src + (size_t)c * cbytes, cbytes, bar);
+        }
+        src += src_step;
+      } else {
+        // ragged tail (< 128 rows): plain loads by the whole warp, zero filled; rows_valid masks the rest downstream
+        const double* tsrc = p.X + (size_t)full_tiles * kTileRows * d;
+        for (int e = lane; e < kTileRows * d; e += 32) {
+          const int tr = e / d, f = e - tr * d;
+          sts_f64(dst + (uint32_t)(tr >> 4) * cstride + (uint32_t)((tr & 15) * d + f) * 8u, tr < tail_rows ? tsrc[(size_t)tr * d + f] : 0.0);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive_a(bar);
+      }
+      if (++s == S) { s = 0; ph ^= 1u; }
+    }
+  } else if (warp == kTpMmaWarp) {
+    // ===================================================================== MMA issuer
+    if (lane == 0) {
+      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(KP >> 3) << 17) | ((uint32_t)(kTileRows >> 4) << 24);
+      const int nmma = L.kchunks / 2;                            // one UMMA consumes K = 8 tf32 = two 16-byte chunks
+      for (int i = 0; i < T; ++i) {
+        const uint32_t b = (uint32_t)(i & 1), ph = (uint32_t)((i >> 1) & 1);          // TMEM buffer / phase
+        const uint32_t ab = na2 ? b : 0u, aph = na2 ? ph : (uint32_t)(i & 1);          // operand buffer / phase
+        tp_wait(b_afull + 8u * ab, aph, 1);
+        tp_wait(b_tempty + 8u * b, ph ^ 1u, 2);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t abase = a_A + ab * (uint32_t)L.a_bytes, dcol = tmem + b * (uint32_t)TSTRIDE;
+        for (int ks = 0; ks < nmma; ++ks) {
+          const uint64_t da = tp_desc_kmajor(abase + (uint32_t)(2 * ks) * LBO_A, LBO_A, 128u);
+          const uint64_t db = tp_desc_kmajor(a_B + (uint32_t)(2 * ks) * LBO_B, LBO_B, 128u);
+          const uint32_t accf = ks > 0 ? 1u : 0u;
+          asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n}\n" ::"r"(dcol),
+                       "l"(da), "l"(db), "r"(idesc), "r"(accf)
+                       : "memory");
+        }
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(b_tfull + 8u * b) : "memory");
+      }
+    }
+  } else if (warp >= kTpConvWarp0) {
+    // ===================================================================== converters
+    const int cw = warp - kTpConvWarp0;
+    const int lpr = L.c_lpr, g = L.c_g;
+    const int subc = lane / lpr, fc = (lane % lpr) * CVEC;
+    const bool act = fc < d;
+    const double mu0 = act ? mu_s[fc] : 0.0, mu1 = (CVEC == 2 && act) ? mu_s[fc + 1] : 0.0;
+    const uint32_t dst_lane = (uint32_t)(fc >> 2) * LBO_A + (uint32_t)(fc & 3) * 4u + (uint32_t)subc * 16u;
+    const uint32_t src_lane = (uint32_t)subc * row_bytes + (uint32_t)fc * 8u;
+    const int nit = kChunkRows / g;
+    const uint32_t src_it = (uint32_t)g * row_bytes, dst_it = (uint32_t)g * 16u;
+    const bool need_xx = do_reduce && xx_mode != 2;
+    int s = 0; uint32_t sph = 0;
+    for (int i = 0; i < T; ++i) {
+      const uint32_t b = na2 ? (uint32_t)(i & 1) : 0u, ph = na2 ? (uint32_t)((i >> 1) & 1) : (uint32_t)(i & 1);
+      tp_wait(b_full + 8u * (uint32_t)s, sph, 3);
+      tp_wait(b_aempty + 8u * b, ph ^ 1u, 4);
+      const uint32_t xs = a_x + (uint32_t)s * sbytes, ab = a_A + b * (uint32_t)L.a_bytes;
+#pragma unroll 1
+      for (int cc = cw; cc < kChunks; cc += kTpConvWarps) {
+        const uint32_t src0 = xs + (uint32_t)cc * cstride + src_lane;
+        const uint32_t dst0 = ab + (uint32_t)cc * 256u + dst_lane;
+        if (act) {
+#pragma unroll 4
+          for (int it = 0; it < nit; ++it) {
+            double v0, v1 = 0.0;
+            if (CVEC == 2) lds_v2f64(src0 + (uint32_t)it * src_it, v0, v1); else v0 = lds_f64(src0 + (uint32_t)it * src_it);
+            if (need_xx) { xxs = fma(v0, v0, xxs); if (CVEC == 2) xxs = fma(v1, v1, xxs); }
+            const uint32_t t0 = f32_to_tf32_rn((float)(v0 - mu0));
+            if (CVEC == 2) {
+              const uint32_t t1 = f32_to_tf32_rn((float)(v1 - mu1));
+              asm volatile("st.shared.v2.u32 [%0], {%1,%2};" ::"r"(dst0 + (uint32_t)it * dst_it), "r"(t0), "r"(t1) : "memory");
+            } else sts_u32(dst0 + (uint32_t)it * dst_it, t0);
+          }
+        }
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");       // conversion stores -> visible to the tensor core
+      __syncwarp();
+      if (lane == 0) mbar_arrive_a(b_afull + 8u * b);
+      if (++s == S) { s = 0; sph ^= 1u; }
+    }
+  } else if (warp < 4 * SG) {
+    // ===================================================================== screen warps
+    const int grp = warp >> 2, wsub = warp & 3;
+    const int row = 32 * wsub + lane;                              // tile row of this thread = TMEM lane
+    const uint32_t tlane = ((uint32_t)(32 * wsub)) << 16;
+    const float kapv = 1.04f * 0.0009765625f * vmax;               // kappa * max|c - mu|
+    const float etab = 0.5f * 1.52587890625e-05f * vmax * vmax;    // eta * max 0.5|c - mu|^2, eta = 2^-16
+    const int dch = d8 / 4;
+    const bool conv2 = (d & 1) == 0;
+    const int rlane = conv2 ? 2 * lane : lane;                     // refine: first feature of this lane
+    const bool ract = rlane < d;
+    for (int i = grp; i < T; i += SG) {
+      const int s = i % S;
+      const uint32_t b = (uint32_t)(i & 1), ph = (uint32_t)((i >> 1) & 1);
+      const int rows_valid = i < my_tiles ? kTileRows : tail_rows;
+      const int64_t r0 = i < my_tiles ? ((int64_t)blockIdx.x + (int64_t)i * gridDim.x) * kTileRows : full_tiles * kTileRows;
+      const int li = i / SG;                                       // this group's tile counter
+      const uint32_t lab_b = a_lab + (uint32_t)s * (kTileRows * 4);
+      const uint32_t list_b = a_list + (uint32_t)((grp * 2 + (li & 1)) * kTileRows) * 16u;
+      const uint32_t lc_cur = a_lcnt + (uint32_t)(grp * 4 + li % 3) * 4u, lc_next = a_lcnt + (uint32_t)(grp * 4 + (li + 1) % 3) * 4u;
+      tp_wait(b_tfull + 8u * b, ph, 5);
+      asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+      // |x - mu|^2 of this row from the tf32 operand the tensor core just consumed
+      const uint32_t abuf = na2 ? b : 0u;
+      const uint32_t arow = a_A + abuf * (uint32_t)L.a_bytes + (uint32_t)row * 16u;
+      float xn2 = 0.f;
+      for (int c = 0; c < dch; ++c) {
+        float4 a;
+        asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "r"(arow + (uint32_t)c * LBO_A));
+        xn2 = fmaf(a.x, a.x, xn2); xn2 = fmaf(a.y, a.y, xn2); xn2 = fmaf(a.z, a.z, xn2); xn2 = fmaf(a.w, a.w, xn2);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive_a(b_aempty + 8u * abuf);        // the operand buffer can take the next conversion
+      // sweep 1: best and second best approximate score, centre index in the low mantissa bits
+      const uint32_t tbase = tmem + tlane + b * (uint32_t)TSTRIDE;
+      const float ninf = -__int_as_float(0x7f800000);
+      float m1 = ninf, m2 = ninf;
+#pragma unroll
+      for (int ch = 0; ch < KP / 16; ++ch) {
+        uint32_t v[16];
+        tp_tmem_ld16(tbase + (uint32_t)(ch * 16), v);
+        tp_tmem_wait_ld();
+#pragma unroll
+        for (int c = 0; c < 16; ++c) {
+          const float pv = __uint_as_float((v[c] & ~IDXMASK) | (uint32_t)(ch * 16 + c));
+          m2 = fmaxf(m2, fminf(m1, pv));
+          m1 = fmaxf(m1, pv);
+        }
+      }
+      const bool valid = row < rows_valid;
+      const float eps = fmaf(kapv, sqrtf(xn2) * 1.001f, etab) + 6e-5f * fabsf(m1);
+      const float thr = m1 - 2.0f * eps;
+      const bool amb = valid && !(m2 < thr);
+      const int j1 = (int)(__float_as_uint(m1) & IDXMASK);
+      if (__any_sync(0xffffffffu, amb)) {
+        // sweep 2 (only when some row of the warp is undecided): every centre within 2 eps of the best is a candidate
+        uint32_t w[NW];
+#pragma unroll
+        for (int q = 0; q < NW; ++q) w[q] = 0u;
+#pragma unroll
+        for (int ch = 0; ch < KP / 16; ++ch) {
+          uint32_t v[16];
+          tp_tmem_ld16(tbase + (uint32_t)(ch * 16), v);
+          tp_tmem_wait_ld();
+#pragma unroll
+          for (int c = 0; c < 16; ++c) w[ch >> 1] |= (__uint_as_float(v[c]) >= thr) ? (1u << ((ch & 1) * 16 + c)) : 0u;
+        }
+        if (amb) {
+          unsigned slot;
+          asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(slot) : "r"(lc_cur) : "memory");
+          asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(list_b + 16u * slot), "r"((uint32_t)row), "r"(w[0]), "r"(NW > 1 ? w[NW - 1] : 0u), "r"(0u) : "memory");
+        }
+      }
+      // the TMEM buffer is free again
+      asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+      __syncwarp();
+      if (lane == 0) mbar_arrive_a(b_tempty + 8u * b);
+      if (!amb) {
+        sts_u32(lab_b + 4u * (uint32_t)row, valid ? (uint32_t)j1 : 0xffffffffu);
+        if (valid) {
+          if (p.labels_out != nullptr) p.labels_out[r0 + row] = j1;
+          if (do_reduce) asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(a_cnt + 4u * (uint32_t)j1) : "memory");
+        }
+      }
+      if (wsub == 0 && lane == 0) sts_u32(lc_next, 0u);              // the counter two tiles back: all its readers passed the previous barrier
+      named_bar_sync(1 + grp, 128);
+      // cooperative exact re-scoring of the listed rows: warp per row, lane = feature (pair), ascending centre index
+      const unsigned namb = lds_u32(lc_cur);
+      const uint32_t xs = a_x + (uint32_t)s * sbytes;
+      for (unsigned e = (unsigned)wsub; e < namb; e += 4u) {
+        const uint4 en = lds_v4(list_b + 16u * e);
+        const int rr = (int)en.x;
+        const uint32_t ra = xs + (uint32_t)(rr >> 4) * cstride + (uint32_t)(rr & 15) * row_bytes + (uint32_t)rlane * 8u;
+        double x0 = 0.0, x1 = 0.0;
+        if (ract) { if (conv2) lds_v2f64(ra, x0, x1); else x0 = lds_f64(ra); }
+        double best = -__longlong_as_double(0x7ff0000000000000LL); int bj = -1;
+#pragma unroll
+        for (int q = 0; q < NW; ++q) {
+          uint32_t msk = q == 0 ? en.y : en.z;
+          while (msk) {
+            const int j = 32 * q + __ffs(msk) - 1; msk &= msk - 1;
+            double c0 = 0.0, c1 = 0.0;
+            if (ract) {
+              if (conv2) { const double2 cc = __ldg(reinterpret_cast<const double2*>(p.C + (size_t)j * d + rlane)); c0 = cc.x; c1 = cc.y; }
+              else c0 = __ldg(p.C + (size_t)j * d + rlane);
+            }
+            double sdot = fma(x0, c0, x1 * c1);
+#pragma unroll
+            for (int mk = 16; mk >= 1; mk >>= 1) sdot += shfl_xor_d(sdot, mk);
+            const double sc = sdot + cn_s[j];
+            if (sc > best) { best = sc; bj = j; }
+          }
+        }
+        if (lane == 0) {
+          sts_u32(lab_b + 4u * (uint32_t)rr, (uint32_t)bj);
+          if (p.labels_out != nullptr) p.labels_out[r0 + rr] = bj;
+          if (do_reduce) asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(a_cnt + 4u * (uint32_t)bj) : "memory");
+        }
+      }
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive_a(b_lfull + 8u * (uint32_t)s);
+        if (!do_reduce) mbar_arrive_a(b_sempty + 8u * (uint32_t)s);
+      }
+    }
+  } else {
+    // ===================================================================== reduce warps
+    const int ridx = warp - 4 * SG;
+    if (do_reduce) {
+      int s = 0; uint32_t sph = 0;
+      if constexpr (RMODE != 2) {
+        // private sets: this warp's rows are the groups gi = ridx, ridx + R, ... of r_g consecutive rows; sub-row `sub` of a
+        // group accumulates into set ridx * r_g + sub, so no two lanes ever meet on an address
+        constexpr int RVEC = RMODE == 0 ? 1 : 2;
+        const int lpr = L.r_lpr, g = L.r_g, ng = kTileRows / g;
+        const int sub = lane / lpr, f = (lane % lpr) * RVEC;
+        const bool act = f < d;
+        const uint32_t acc_row = (uint32_t)L.ald * 8u;
+        const uint32_t my_acc = a_acc + (uint32_t)(ridx * g + sub) * (uint32_t)KP * acc_row + (uint32_t)f * 8u;
+        for (int i = 0; i < T; ++i) {
+          tp_wait(b_lfull + 8u * (uint32_t)s, sph, 6);
+          const uint32_t xs = a_x + (uint32_t)s * sbytes + (uint32_t)f * 8u, lab_b = a_lab + (uint32_t)s * (kTileRows * 4);
+          for (int gi = ridx; gi < ng; gi += 2 * R) {
+            // two groups in flight unless a sub-row would hit the same accumulator row in both
+            const int rA = gi * g + sub, rB = (gi + R) * g + sub;
+            const bool hasB = gi + R < ng;
+            const int labA = (int)lds_u32(lab_b + 4u * (uint32_t)rA);
+            const int labB = hasB ? (int)lds_u32(lab_b + 4u * (uint32_t)rB) : -1;
+            const uint32_t xA = xs + (uint32_t)(rA >> 4) * cstride + (uint32_t)(rA & 15) * row_bytes;
+            const uint32_t xB = xs + (uint32_t)(rB >> 4) * cstride + (uint32_t)(rB & 15) * row_bytes;
+            const bool doA = act && labA >= 0, doB = act && labB >= 0;
+            const uint32_t aA = my_acc + (uint32_t)(doA ? labA : 0) * acc_row, aB = my_acc + (uint32_t)(doB ? labB : 0) * acc_row;
+            const bool clash = __any_sync(0xffffffffu, doA && doB && labA == labB);
+            if constexpr (RVEC == 1) {
+              double vA = 0, vB = 0;
+              if (doA) vA = lds_f64(xA);
+              if (doB) vB = lds_f64(xB);
+              if (!clash) {
+                double sA = 0, sB = 0;
+                if (doA) sA = lds_f64(aA);
+                if (doB) sB = lds_f64(aB);
+                if (doA) sts_f64(aA, sA + vA);
+                if (doB) sts_f64(aB, sB + vB);
+              } else {
+                if (doA) sts_f64(aA, lds_f64(aA) + vA);
+                if (doB) sts_f64(aB, lds_f64(aB) + vB);
+              }
+            } else {
+              double vA0 = 0, vA1 = 0, vB0 = 0, vB1 = 0;
+              if (doA) lds_v2f64(xA, vA0, vA1);
+              if (doB) lds_v2f64(xB, vB0, vB1);
+              if (!clash) {
+                double sA0 = 0, sA1 = 0, sB0 = 0, sB1 = 0;
+                if (doA) lds_v2f64(aA, sA0, sA1);
+                if (doB) lds_v2f64(aB, sB0, sB1);
+                if (doA) sts_v2f64(aA, sA0 + vA0, sA1 + vA1);
+                if (doB) sts_v2f64(aB, sB0 + vB0, sB1 + vB1);
+              } else {
+                if (doA) { double t0, t1; lds_v2f64(aA, t0, t1); sts_v2f64(aA, t0 + vA0, t1 + vA1); }
+                if (doB) { double t0, t1; lds_v2f64(aB, t0, t1); sts_v2f64(aB, t0 + vB0, t1 + vB1); }
+              }
+            }
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive_a(b_sempty + 8u * (uint32_t)s);
+          if (++s == S) { s = 0; sph ^= 1u; }
+        }
+      } else {
+        // one shared set: warp r owns the clusters j = r mod R; lane = feature pair; rows in tile order, two per step
+        const bool act = 2 * lane < d;
+        const uint32_t my_acc = a_acc + (uint32_t)lane * 16u;      // accumulator row j at j * 512 bytes
+        for (int i = 0; i < T; ++i) {
+          tp_wait(b_lfull + 8u * (uint32_t)s, sph, 6);
+          const uint32_t xs = a_x + (uint32_t)s * sbytes + (uint32_t)lane * 16u, lab_b = a_lab + (uint32_t)s * (kTileRows * 4);
+#pragma unroll 1
+          for (int gq = 0; gq < kTileRows / 32; ++gq) {
+            const int lab = (int)lds_u32(lab_b + 4u * (uint32_t)(gq * 32 + lane));
+            unsigned mask = __ballot_sync(0xffffffffu, lab >= 0 && (lab & (R - 1)) == ridx);
+            while (mask) {
+              const int q0 = __ffs(mask) - 1; mask &= mask - 1;
+              bool two = mask != 0;
+              const int q1 = two ? __ffs(mask) - 1 : q0; mask &= mask - 1;
+              const int l0 = __shfl_sync(0xffffffffu, lab, q0), l1 = __shfl_sync(0xffffffffu, lab, q1);
+              const int t0 = gq * 32 + q0, t1 = gq * 32 + q1;
+              double v00 = 0, v01 = 0, v10 = 0, v11 = 0;
+              if (act) {
+                lds_v2f64(xs + (uint32_t)(t0 >> 4) * cstride + (uint32_t)(t0 & 15) * row_bytes, v00, v01);
+                if (two) lds_v2f64(xs + (uint32_t)(t1 >> 4) * cstride + (uint32_t)(t1 & 15) * row_bytes, v10, v11);
+              }
+              if (two && l1 == l0) { v00 += v10; v01 += v11; two = false; }
+              const uint32_t aa0 = my_acc + (uint32_t)l0 * 512u, aa1 = my_acc + (uint32_t)l1 * 512u;
+              if (act) {
+                double s00, s01, s10 = 0, s11 = 0;
+                lds_v2f64(aa0, s00, s01);
+                if (two) lds_v2f64(aa1, s10, s11);
+                sts_v2f64(aa0, s00 + v00, s01 + v01);
+                if (two) sts_v2f64(aa1, s10 + v10, s11 + v11);
+              }
+            }
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive_a(b_sempty + 8u * (uint32_t)s);
+          if (++s == S) { s = 0; sph ^= 1u; }
+        }
+      }
+    }
+  }
+
+  // ===================================================================== CTA-level combine (all warps)
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == kTpProdWarp) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TCOLS) : "memory");
+  if (!p.do_reduce) return;
+
+  const int P = k * d + k + 1;
+  const int SL = P + 1 + k;
+  double* out = p.cta_partials + (size_t)blockIdx.x * SL;
+  const double* acc0 = reinterpret_cast<const double*>(smem + L.acc_off);
+  {
+    const int ald = L.ald, setn = KP * L.ald, nsets = L.nsets;
+    for (int i = tid; i < k * d; i += kTpThreads) {
+      const int j = i / d, f = i - j * d;
+      double sacc = 0;
+      for (int w = 0; w < nsets; ++w) sacc += acc0[w * setn + j * ald + f];
+      out[i] = sacc;
+      cost = fma(sacc, p.C[i], cost);                           // sum_j S_j . c_j
+    }
+    if (tid < k) { const double nj = (double)cnt_s[tid]; out[(size_t)k * d + tid] = nj; cost = fma(nj, cn_s[tid], cost); }
+  }
+#pragma unroll
+  for (int msk = 16; msk >= 1; msk >>= 1) { cost += shfl_xor_d(cost, msk); xxs += shfl_xor_d(xxs, msk); }
+  if (lane == 0) { red_s[warp] = cost; red_s[kTpWarps + warp] = xxs; }
+  __syncthreads();
+  if (tid == 0) {
+    double c = 0, x2 = 0;
+#pragma unroll
+    for (int wv = 0; wv < kTpWarps; ++wv) { c += red_s[wv]; x2 += red_s[kTpWarps + wv]; }
+    out[P - 1] = c; out[P] = x2;                                 // [sum of winner scores][sum |x|^2 of this CTA's rows]
+  }
+  // ===================================================================== last CTA folds all partials
+  __threadfence();
+  __syncthreads();
+  __shared__ unsigned int s_ticket;
+  if (tid == 0) s_ticket = atomicAdd(p.counter, 1u);
+  __syncthreads();
+  if (s_ticket == gridDim.x - 1) {
+    __threadfence();
+    for (int i = tid; i < P + 1; i += kTpThreads) {
+      if (i == P - 1) continue;
+      double sum = 0;
+      for (unsigned bq = 0; bq < gridDim.x; ++bq) sum += __ldcg(p.cta_partials + (size_t)bq * SL + i);
+      if (i < P) p.partial_out[i] = sum; else red_s[0] = sum;    // i == P: sum |x|^2 over the whole pass
+    }
+    __syncthreads();
+    if (tid == 0) {
+      double ssc = 0;
+      for (unsigned bq = 0; bq < gridDim.x; ++bq) ssc += __ldcg(p.cta_partials + (size_t)bq * SL + (P - 1));
+      const double xx = xx_mode == 2 ? *p.xnorm2_sum : red_s[0];
+      if (xx_mode == 1) *p.xnorm2_sum = xx;
+      p.partial_out[P - 1] = fmax(fma(-2.0, ssc, xx), 0.0);      // cost = sum |x|^2 - 2 sum score
+      *p.counter = 0u;
+    }
+    if (p.peer_bufs != nullptr) {                                // ranks > 1: sum the vector over NVLink peer memory right here
+      __threadfence_block();
+      __syncthreads();
+      peer_allreduce(p, p.partial_out, P, tid, kTpThreads, [] { __syncthreads(); });
+    }
+    if (p.C_update != nullptr) {                                 // fused driver step
+      __threadfence_block();
+      __syncthreads();
+      update_centers_body(p.partial_out, k, d, p.C_update, p.tol2, p.state_rw, red_s + 2 * kTpWarps, tid);
+    }
+  }
+}
+
+}  // namespace hkm

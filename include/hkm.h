@@ -61,6 +61,12 @@ HKM_API int hkm_version(void);
 HKM_API int hkm_max_k(void);
 HKM_API int hkm_max_d(void);
 
+/* Tuning / test hook, process wide: pins the kernel family the Lloyd data passes use wherever that family is built for the
+ * shape.  0 = pick per shape (default), 1 = gather, 2 = fp64 tensor pipe, 3 = warp-specialised fp64, 4 = pipelined tcgen05
+ * screening, 5 = the selection without the pipelined tcgen05 variant.  Every family gives the same labels, sums and cost
+ * (tests/test_gpu_lloyd.py compares them), so this never changes results.  No counterpart in Spark. */
+HKM_API int hkm_set_lloyd_variant(int variant);
+
 /* Bytes of scratch hkm_assign_reduce needs for (d, k) on the current device. */
 HKM_API size_t hkm_assign_reduce_scratch_bytes(int d, int k);
 
