@@ -15,7 +15,7 @@ SO_PATH = os.path.join(_HERE, "csrc", "libhkm.so")
 
 EXPORTS = (
     "hkm_last_error", "hkm_version", "hkm_max_k", "hkm_max_d", "hkm_set_lloyd_variant",
-    "hkm_assign_reduce_scratch_bytes", "hkm_assign_reduce", "hkm_update_centers", "hkm_update_centers_cosine", "hkm_lloyd_step", "hkm_lloyd_step_peer", "hkm_peer_exchange_bytes",
+    "hkm_assign_reduce_scratch_bytes", "hkm_assign_reduce", "hkm_update_centers", "hkm_update_centers_cosine", "hkm_lloyd_step", "hkm_lloyd_step_peer", "hkm_peer_exchange_bytes", "hkm_peer_exchange_slot_doubles",
     "hkm_kmpar_scratch_bytes", "hkm_kmpar_cost_update", "hkm_kmpar_sample", "hkm_kmpar_strip_rows", "hkm_closest_counts",
     "hkm_silhouette_stats", "hkm_silhouette_score",
     "hkm_assemble_scratch_bytes", "hkm_assemble", "hkm_moments_scratch_bytes", "hkm_moments", "hkm_column_moments", "hkm_scale_rows", "hkm_normalize_rows", "hkm_local_kmeanspp",

@@ -81,6 +81,17 @@ class PeerExchange:
                 cls._cached = False
         return cls._cached or None
 
+    def fits(self, k: int, d: int) -> bool:
+        """Whether the k*d + k + 1 partial sums fit one exchange slot (else the NCCL all-reduce path is used)."""
+        from . import _native as N
+        return k * d + k + 1 <= int(N.load().hkm_peer_exchange_slot_doubles())
+
     def check(self):
-        if int(self.err.item()) != 0:
+        """Raises on EVERY rank if any rank timed out in an exchange (the flag is summed over the ranks first, so no rank
+        goes on into a later collective alone), and clears the flag so the next fit starts clean."""
+        import torch.distributed as dist
+        flag = self.err.clone()
+        dist.all_reduce(flag, op=dist.ReduceOp.MAX)
+        if int(flag.item()) != 0:
+            self.err.zero_()
             raise HkmError("hkm_lloyd_step_peer: a peer rank never arrived at the exchange (time-out)")

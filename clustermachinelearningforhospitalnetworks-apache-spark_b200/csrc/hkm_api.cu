@@ -173,6 +173,7 @@ int hkm_lloyd_step(const double* X, int64_t n, int d, double* C_inout, int k, co
 }
 
 size_t hkm_peer_exchange_bytes(int world) { return world < 1 ? 0 : xchg_buffer_bytes(world); }
+int hkm_peer_exchange_slot_doubles(void) { return kXchgSlot; }
 
 int hkm_lloyd_step_peer(const double* X, int64_t n, int d, double* C_inout, int k, const double* weights, double* partial_out,
                         double* xnorm2_sum, int xnorm2_mode, double tol, hkm_lloyd_state* state, void* scratch, size_t scratch_bytes,

@@ -7,6 +7,7 @@
 #include "../../include/hkm.h"
 #include "hkm_lloyd_launch.cuh"
 #include <cmath>
+#include <mutex>
 
 namespace hkm {
 
@@ -38,12 +39,16 @@ __global__ void jump_table_init_kernel() {
   }
 }
 
+// Built once per device.  The first caller waits for the build, so a table marked ready is ready for every stream.
 static int ensure_jump_table(cudaStream_t st) {
   static bool ready[64];
+  static std::mutex mu;
   int dev = 0; HKM_CUDA_TRY(cudaGetDevice(&dev));
+  std::lock_guard<std::mutex> lock(mu);
   if (dev < 64 && ready[dev]) return HKM_OK;
   jump_table_init_kernel<<<1, 64, 0, st>>>();
   HKM_CUDA_TRY(cudaGetLastError());
+  HKM_CUDA_TRY(cudaStreamSynchronize(st));
   if (dev < 64) ready[dev] = true;
   return HKM_OK;
 }
@@ -124,12 +129,18 @@ using namespace hkm;
 
 extern "C" {
 
-size_t hkm_kmpar_scratch_bytes(int d) { return hkm_assign_reduce_scratch_bytes(d, hkm_max_k()); }
+// A k-means|| step scores the rows against chunks of 1..64 new centres; the pass's grid (CTAs per SM) depends on the
+// chunk's k, so the scratch must cover the largest requirement over all chunk sizes, not only k = 64.
+size_t hkm_kmpar_scratch_bytes(int d) {
+  size_t mx = 0;
+  for (int k = 1; k <= 64; ++k) { const size_t b = hkm_assign_reduce_scratch_bytes(d, k); if (b > mx) mx = b; }
+  return mx;
+}
 
 int hkm_kmpar_cost_update(const double* X, int64_t n, int d, const double* newC, int m, double* costs_inout, double* sum_out,
                           void* scratch, size_t scratch_bytes, void* stream) {
   if (m < 1 || costs_inout == nullptr || sum_out == nullptr) { set_error("hkm_kmpar_cost_update: bad arguments"); return HKM_ERR_INVALID; }
-  const int chunk = hkm_max_k();
+  const int chunk = 64;
   for (int c0 = 0; c0 < m; c0 += chunk) {
     AssignArgs a{};
     a.X = X; a.n = n; a.d = d; a.C = newC + (size_t)c0 * d; a.k = (m - c0 < chunk) ? (m - c0) : chunk;
@@ -170,7 +181,7 @@ int hkm_closest_counts(const double* X, int64_t n, int d, const double* cand, in
     fill_double_kernel<<<sm_count() * 4, 256, 0, st>>>(mind2_work, n, HUGE_VAL);
     HKM_CUDA_TRY(cudaGetLastError());
   }
-  const int chunk = hkm_max_k();
+  const int chunk = 64;
   for (int c0 = 0; c0 < m; c0 += chunk) {
     AssignArgs a{};
     a.X = X; a.n = n; a.d = d; a.C = cand + (size_t)c0 * d; a.k = (m - c0 < chunk) ? (m - c0) : chunk;

@@ -105,8 +105,11 @@ constexpr int kXchgSlot = 4352;   // doubles per slot: >= 64*65 + 64 + 2
 __host__ __device__ inline size_t xchg_flags_offset(int world) { return (size_t)2 * world * kXchgSlot * sizeof(double); }
 __host__ __device__ inline size_t xchg_buffer_bytes(int world) { return xchg_flags_offset(world) + (size_t)2 * world * sizeof(unsigned long long) + 64; }
 
+// Returns false (on every thread) if a peer never showed up: the caller must then leave the centres alone.
 template <class Sync>
-__device__ __forceinline__ void peer_allreduce(const LloydParams& p, double* vec, int len, int tid, int nthreads, Sync sync) {
+__device__ __forceinline__ bool peer_allreduce(const LloydParams& p, double* vec, int len, int tid, int nthreads, Sync sync) {
+  __shared__ int s_peer_ok;
+  if (tid == 0) s_peer_ok = 1;
   const int world = p.xworld, rank = p.xrank, set = (int)(p.xepoch & 1ull);
   const size_t slot_off = ((size_t)set * world + rank) * kXchgSlot;
   for (int q = 0; q < world; ++q) {
@@ -123,16 +126,23 @@ __device__ __forceinline__ void peer_allreduce(const LloydParams& p, double* vec
     const long long t0 = clock64();
     do {
       asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(mine) : "memory");
-      if (v != p.xepoch && clock64() - t0 > 8000000000LL) { if (p.xerr != nullptr) *p.xerr = 1; break; }   // ~4 s: a peer is missing, do not hang the GPU
+      if (v != p.xepoch && clock64() - t0 > 8000000000LL) { if (p.xerr != nullptr) *p.xerr = 1; s_peer_ok = 0; break; }   // ~4 s: a peer is missing, do not hang the GPU
     } while (v != p.xepoch);
   }
   sync();
+  if (!s_peer_ok) {
+    // incomplete exchange: stop this rank's loop (later passes become no-ops) instead of updating from partial sums;
+    // the host sees err_flag and raises on every rank
+    if (tid == 0 && p.state_rw != nullptr) p.state_rw->converged = 1;
+    return false;
+  }
   const double* base = reinterpret_cast<const double*>(p.peer_bufs[rank]) + (size_t)set * world * kXchgSlot;
   for (int i = tid; i < len; i += nthreads) {
     double s = 0;
     for (int q = 0; q < world; ++q) s += __ldcv(base + (size_t)q * kXchgSlot + i);
     vec[i] = s;
   }
+  return true;
 }
 
 __host__ __device__ inline int chunk_stride_bytes(int d) { return kChunkRows * d * 8 + kChunkPad; }
@@ -209,7 +219,7 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
   // stage centres: Cs[j][f] (zero padded), cn_s[j] = -0.5|c_j|^2 (-inf for padding)
   for (int i = tid; i < k_pad * csld; i += kThreads) {
     int j = i / csld, f = i - j * csld;
-    Cs[i] = (j < k && f < d) ? p.C[(size_t)j * d + f] : 0.0;
+    Cs[i] = (MODE != 1 && j < k && f < d) ? p.C[(size_t)j * d + f] : 0.0;   // the statistics pass has no centres
   }
   for (int i = tid; i < ((d + 3) & ~3); i += kThreads) reinterpret_cast<double*>(smem + L.zero_off)[i] = 0.0;
   __syncthreads();
@@ -619,12 +629,13 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
       else p.partial_out[i - 1] = s;                           // MODE 1: psi follows [sums][N][cost]
     }
     if (tid == 0) *p.counter = 0u;
+    bool peer_ok = true;
     if (p.peer_bufs != nullptr) {                              // ranks > 1: sum the vector over NVLink peer memory right here
       __threadfence_block();
       __syncthreads();
-      peer_allreduce(p, p.partial_out, P, tid, kComputeThreads, [] { __syncthreads(); });
+      peer_ok = peer_allreduce(p, p.partial_out, P, tid, kComputeThreads, [] { __syncthreads(); });
     }
-    if (p.C_update != nullptr) {                               // fused driver step: uniform branch
+    if (p.C_update != nullptr && peer_ok) {                               // fused driver step: uniform branch
       __threadfence_block();
       __syncthreads();
       update_centers_body(p.partial_out, k, d, p.C_update, p.tol2, p.state_rw, red_s, tid);

@@ -69,7 +69,7 @@ __global__ void __launch_bounds__(kMmaThreads) __maxnreg__(MAXREG) lloyd_mma_ker
   }
   for (int i = tid; i < k_pad * csld; i += kMmaThreads) {
     int j = i / csld, f = i - j * csld;
-    Cs[i] = (j < k && f < d) ? p.C[(size_t)j * d + f] : 0.0;
+    Cs[i] = (MODE != 1 && j < k && f < d) ? p.C[(size_t)j * d + f] : 0.0;   // the statistics pass has no centres
   }
   __syncthreads();
   for (int j = tid; j < k_pad; j += kMmaThreads) {
@@ -367,12 +367,13 @@ __global__ void __launch_bounds__(kMmaThreads) __maxnreg__(MAXREG) lloyd_mma_ker
         else p.partial_out[i - 1] = s;                           // MODE 1: psi follows [sums][N][cost]
       }
       if (tid == 0) *p.counter = 0u;
+      bool peer_ok = true;
       if (p.peer_bufs != nullptr) {                            // ranks > 1: sum the vector over NVLink peer memory right here
         __threadfence_block();
         named_bar_sync(1, kComputeThreads);
-        peer_allreduce(p, p.partial_out, P, tid, kComputeThreads, [] { named_bar_sync(1, kComputeThreads); });
+        peer_ok = peer_allreduce(p, p.partial_out, P, tid, kComputeThreads, [] { named_bar_sync(1, kComputeThreads); });
       }
-      if (p.C_update != nullptr) {                             // fused driver step: compute warps only
+      if (p.C_update != nullptr && peer_ok) {                             // fused driver step: compute warps only
         __threadfence_block();
         named_bar_sync(1, kComputeThreads);
         double shift = -1.0;

@@ -448,12 +448,13 @@ __global__ void __launch_bounds__(kTcThreads, 1) lloyd_tc_kernel(const LloydPara
           else if (xx_mode == 1) *p.xnorm2_sum = sum;
         }
         if (tid == 0) *p.counter = 0u;
+        bool peer_ok = true;
         if (p.peer_bufs != nullptr && p.do_reduce == 1) {
           __threadfence_block();
           named_bar_sync(1, kComputeThreads);
-          peer_allreduce(p, p.partial_out, P, tid, kComputeThreads, [] { named_bar_sync(1, kComputeThreads); });
+          peer_ok = peer_allreduce(p, p.partial_out, P, tid, kComputeThreads, [] { named_bar_sync(1, kComputeThreads); });
         }
-        if (p.C_update != nullptr) {
+        if (p.C_update != nullptr && peer_ok) {
           __threadfence_block();
           named_bar_sync(1, kComputeThreads);
           double shift = -1.0;

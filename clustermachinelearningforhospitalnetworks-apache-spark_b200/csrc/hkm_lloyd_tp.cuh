@@ -637,12 +637,13 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
       p.partial_out[P - 1] = fmax(fma(-2.0, ssc, xx), 0.0);      // cost = sum |x|^2 - 2 sum score
       *p.counter = 0u;
     }
+    bool peer_ok = true;
     if (p.peer_bufs != nullptr) {                                // ranks > 1: sum the vector over NVLink peer memory right here
       __threadfence_block();
       __syncthreads();
-      peer_allreduce(p, p.partial_out, P, tid, kTpThreads, [] { __syncthreads(); });
+      peer_ok = peer_allreduce(p, p.partial_out, P, tid, kTpThreads, [] { __syncthreads(); });
     }
-    if (p.C_update != nullptr) {                                 // fused driver step
+    if (p.C_update != nullptr && peer_ok) {                                 // fused driver step
       __threadfence_block();
       __syncthreads();
       update_centers_body(p.partial_out, k, d, p.C_update, p.tol2, p.state_rw, red_s + 2 * kTpWarps, tid);

@@ -395,12 +395,13 @@ __global__ void __launch_bounds__(kWsThreads) __maxnreg__(MAXREG) lloyd_ws_kerne
       else if (xx_mode == 1) *p.xnorm2_sum = s;
     }
     if (tid == 0) *p.counter = 0u;
+    bool peer_ok = true;
     if (p.peer_bufs != nullptr) {                            // ranks > 1: sum the vector over NVLink peer memory right here
       __threadfence_block();
       __syncthreads();
-      peer_allreduce(p, p.partial_out, P, tid, kWsThreads, [] { __syncthreads(); });
+      peer_ok = peer_allreduce(p, p.partial_out, P, tid, kWsThreads, [] { __syncthreads(); });
     }
-    if (p.C_update != nullptr) {                             // fused driver step
+    if (p.C_update != nullptr && peer_ok) {                             // fused driver step
       __threadfence_block();
       __syncthreads();
       update_centers_body(p.partial_out, k, d, p.C_update, p.tol2, p.state_rw, reinterpret_cast<double*>(smem + L.x_off), tid);

@@ -326,6 +326,8 @@ def lloyd(X: torch.Tensor, C0: np.ndarray, w: Optional[torch.Tensor], max_iter: 
     world = RT.dist_info()[1]
 
     xchg = RT.PeerExchange.get(dev) if world > 1 and not cosine else None
+    if xchg is not None and not xchg.fits(k, d):
+        xchg = None          # partial sums larger than an exchange slot: NCCL all-reduce + hkm_update_centers instead
 
     def one_iter(mode):
         if cosine:       # X holds unit rows, C unit centres: same pass, CosineDistanceMeasure.centroid as the driver step
@@ -345,6 +347,8 @@ def lloyd(X: torch.Tensor, C0: np.ndarray, w: Optional[torch.Tensor], max_iter: 
         N.update_centers(partial, C, tol, state)
 
     one_iter(1)  # HKM_XNORM_STORE: exact per-row cost, and sum w|x|^2 for the later passes
+    if xchg is not None:
+        xchg.check()
     st = N.read_state(state)
     # REUSE needs cost / sum|x|^2 well above fp64 rounding; fall back to per-row norms otherwise
     xs_total = xsum.clone()
@@ -357,10 +361,10 @@ def lloyd(X: torch.Tensor, C0: np.ndarray, w: Optional[torch.Tensor], max_iter: 
         burst = min(check_every, max_iter - it)
         for _ in range(burst):
             one_iter(mode)
+        if xchg is not None:
+            xchg.check()     # a timed-out exchange stops here, on every rank, before more iterations run on partial sums
         st = N.read_state(state)
         it = st.iter
-    if xchg is not None:
-        xchg.check()
     return C.cpu().numpy(), int(st.iter), float(st.cost)
 
 

@@ -116,6 +116,9 @@ HKM_API int hkm_lloyd_step(const double* X, int64_t n, int d, double* C_inout, i
  * that never arrives makes the others give up after a few seconds and set *err_flag = 1).
  */
 HKM_API size_t hkm_peer_exchange_bytes(int world);
+/* Largest vector (doubles) one exchange slot holds: hkm_lloyd_step_peer needs k*d + k + 1 <= this, larger shapes use
+ * hkm_assign_reduce + an all-reduce + hkm_update_centers. */
+HKM_API int hkm_peer_exchange_slot_doubles(void);
 HKM_API int hkm_lloyd_step_peer(const double* X, int64_t n, int d, double* C_inout, int k, const double* weights,
                                 double* partial_out, double* xnorm2_sum, int xnorm2_mode, double tol,
                                 hkm_lloyd_state* state, void* scratch, size_t scratch_bytes,

@@ -49,7 +49,10 @@ def test_cfg1_hospital_table(hkm, oracle, init_mode):
 
 @pytest.mark.parametrize("n,d,k,P,seed", [(20000, 4, 6, 8, 42), (50000, 16, 16, 8, 7), (30011, 24, 3, 5, 1), (8000, 32, 8, 1, 123), (40000, 8, 2, 16, -9),
                                           # k > 16: the warp-specialised, gather and tcgen05 variants behind the fused driver step
-                                          (60000, 24, 32, 8, 5), (50000, 32, 20, 4, 11), (40000, 64, 40, 8, 3), (30000, 16, 48, 8, 2)])
+                                          (60000, 24, 32, 8, 5), (50000, 32, 20, 4, 11), (40000, 64, 40, 8, 3), (30000, 16, 48, 8, 2),
+                                          # d = 28..30 with k near 20: each k-means|| step scores chunks of ~2k new centres, whose pass runs
+                                          # more CTAs per SM than a k = 64 chunk -- the k-means|| scratch must cover that
+                                          (30000, 28, 20, 8, 4), (20000, 30, 16, 4, 9), (20000, 29, 18, 8, 6)])
 def test_fit_matches_oracle(hkm, oracle, n, d, k, P, seed):
     rng = np.random.default_rng(abs(seed) + n)
     X = rng.normal(size=(n, d)) + rng.integers(0, k, size=(n, 1)) * 3.0
