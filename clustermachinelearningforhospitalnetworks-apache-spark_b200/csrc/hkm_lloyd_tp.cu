@@ -21,9 +21,12 @@ bool lloyd_tp_eligible(const LloydParams& p, int mode) {
   return tp_choose(p.d, kp).stages >= 2;
 }
 
+static unsigned long long* g_tp_prof = nullptr;
+
 int launch_lloyd_tp(const LloydParams& p, cudaStream_t st) {
   const int kp = ((p.k + 15) / 16) * 16;
-  const TpPlan L = tp_choose(p.d, kp);
+  TpPlan L = tp_choose(p.d, kp);
+  L.prof = g_tp_prof;
   switch (kp) {
     case 16: return dispatch_lloyd_tp16(p, L, st);
     case 32: return dispatch_lloyd_tp32(p, L, st);
@@ -35,3 +38,7 @@ int launch_lloyd_tp(const LloydParams& p, cudaStream_t st) {
 }
 
 }  // namespace hkm
+
+// Developer hook (not part of include/hkm.h): device buffer of 18 x 8 u64 that CTA 0 of the pipelined pass fills with
+// per-warp cycle counters (total, wait sites, refine, listed rows, tiles); null switches the profile off.
+extern "C" __attribute__((visibility("default"))) void hkm_debug_tp_profile(void* buf) { hkm::g_tp_prof = reinterpret_cast<unsigned long long*>(buf); }

@@ -51,6 +51,7 @@ struct TpPlan {
   int r_lpr, r_g, ald, nsets;  // reducer: lanes per row, rows per instruction, accumulator row (doubles), sets
   int kchunks, lbo_a, lbo_b, a_bytes;
   int x_off, a_off, b_off, acc_off, cn_off, mu_off, cnt_off, lab_off, list_off, lcnt_off, red_off, bar_off, tmem_off, total;
+  unsigned long long* prof;   // developer profile (tools/tp_check.py prof): [warp][8] cycle counters of CTA 0, or null
 };
 
 __host__ __device__ inline TpPlan tp_plan(int d, int kp, int stages, int rmode, int na, int sg) {
@@ -144,6 +145,13 @@ __device__ __forceinline__ void tp_wait(uint32_t bar, uint32_t parity, int tag) 
   if (mbar_test_a(bar, parity)) return;
   tp_wait_timeout(bar, parity, tag);
 }
+// wait that adds the cycles it spent to *acc when profiling
+__device__ __forceinline__ void tp_wait_p(uint32_t bar, uint32_t parity, int tag, bool prof, long long& acc) {
+  if (!prof) { tp_wait(bar, parity, tag); return; }
+  const long long t0 = clock64();
+  tp_wait(bar, parity, tag);
+  acc += clock64() - t0;
+}
 __device__ __forceinline__ void tp_tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 __device__ __forceinline__ void mbar_arrive_a(uint32_t bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
 __device__ __forceinline__ void lds_v2f64(uint32_t a, double& x, double& y) { asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(x), "=d"(y) : "r"(a)); }
@@ -186,6 +194,8 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
   const int my_tiles = full_tiles > (int64_t)blockIdx.x ? (int)((full_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
   const bool tail_mine = tail_rows > 0 && (int)(full_tiles % gridDim.x) == (int)blockIdx.x;
   const int T = my_tiles + (tail_mine ? 1 : 0);    // the ragged tail is this CTA's last tile
+  const bool prof = L.prof != nullptr && blockIdx.x == 0;
+  long long pw0 = 0, pw1 = 0, pw2 = 0, pw3 = 0, pcnt = 0;     // profile: cycles in wait sites 0..3, an event counter
   const bool do_reduce = p.do_reduce == 1;
   const int xx_mode = p.xx_mode;
   const bool na2 = L.na == 2;
@@ -260,6 +270,7 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
   const uint32_t tmem = *reinterpret_cast<const uint32_t*>(smem + L.tmem_off);
 
   double cost = 0, xxs = 0;
+  const long long pt0 = prof ? clock64() : 0;
 
   if (warp == kTpProdWarp) {
     // ===================================================================== producer
@@ -269,7 +280,7 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
     const size_t src_step = (size_t)gridDim.x * tile_gbytes;
     int s = 0; uint32_t ph = 0;
     for (int i = 0; i < T; ++i) {
-      if (lane == 0) tp_wait(b_sempty + 8u * (uint32_t)s, ph ^ 1u, 7);
+      if (lane == 0) tp_wait_p(b_sempty + 8u * (uint32_t)s, ph ^ 1u, 7, prof, pw0);
       __syncwarp();
       const uint32_t bar = b_full + 8u * (uint32_t)s, dst = a_x + (uint32_t)s * sbytes;
       if (i < my_tiles) {
@@ -299,8 +310,8 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
       for (int i = 0; i < T; ++i) {
         const uint32_t b = (uint32_t)(i & 1), ph = (uint32_t)((i >> 1) & 1);          // TMEM buffer / phase
         const uint32_t ab = na2 ? b : 0u, aph = na2 ? ph : (uint32_t)(i & 1);          // operand buffer / phase
-        tp_wait(b_afull + 8u * ab, aph, 1);
-        tp_wait(b_tempty + 8u * b, ph ^ 1u, 2);
+        tp_wait_p(b_afull + 8u * ab, aph, 1, prof, pw0);
+        tp_wait_p(b_tempty + 8u * b, ph ^ 1u, 2, prof, pw1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint32_t abase = a_A + ab * (uint32_t)L.a_bytes, dcol = tmem + b * (uint32_t)TSTRIDE;
         for (int ks = 0; ks < nmma; ++ks) {
@@ -329,8 +340,8 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
     int s = 0; uint32_t sph = 0;
     for (int i = 0; i < T; ++i) {
       const uint32_t b = na2 ? (uint32_t)(i & 1) : 0u, ph = na2 ? (uint32_t)((i >> 1) & 1) : (uint32_t)(i & 1);
-      tp_wait(b_full + 8u * (uint32_t)s, sph, 3);
-      tp_wait(b_aempty + 8u * b, ph ^ 1u, 4);
+      tp_wait_p(b_full + 8u * (uint32_t)s, sph, 3, prof, pw0);
+      tp_wait_p(b_aempty + 8u * b, ph ^ 1u, 4, prof, pw1);
       const uint32_t xs = a_x + (uint32_t)s * sbytes, ab = a_A + b * (uint32_t)L.a_bytes;
 #pragma unroll 1
       for (int cc = cw; cc < kChunks; cc += kTpConvWarps) {
@@ -375,7 +386,7 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
       const uint32_t lab_b = a_lab + (uint32_t)s * (kTileRows * 4);
       const uint32_t list_b = a_list + (uint32_t)((grp * 2 + (li & 1)) * kTileRows) * 16u;
       const uint32_t lc_cur = a_lcnt + (uint32_t)(grp * 4 + li % 3) * 4u, lc_next = a_lcnt + (uint32_t)(grp * 4 + (li + 1) % 3) * 4u;
-      tp_wait(b_tfull + 8u * b, ph, 5);
+      tp_wait_p(b_tfull + 8u * b, ph, 5, prof, pw0);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       // |x - mu|^2 of this row from the tf32 operand the tensor core just consumed
       const uint32_t abuf = na2 ? b : 0u;
@@ -440,9 +451,11 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
         }
       }
       if (wsub == 0 && lane == 0) sts_u32(lc_next, 0u);              // the counter two tiles back: all its readers passed the previous barrier
-      named_bar_sync(1 + grp, 128);
+      { const long long tb = prof ? clock64() : 0; named_bar_sync(1 + grp, 128); if (prof) pw1 += clock64() - tb; }
       // cooperative exact re-scoring of the listed rows: warp per row, lane = feature (pair), ascending centre index
       const unsigned namb = lds_u32(lc_cur);
+      const long long tr0 = prof ? clock64() : 0;
+      pcnt += namb;
       const uint32_t xs = a_x + (uint32_t)s * sbytes;
       for (unsigned e = (unsigned)wsub; e < namb; e += 4u) {
         const uint4 en = lds_v4(list_b + 16u * e);
@@ -474,6 +487,7 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
           if (do_reduce) asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(a_cnt + 4u * (uint32_t)bj) : "memory");
         }
       }
+      if (prof) pw2 += clock64() - tr0;
       __syncwarp();
       if (lane == 0) {
         mbar_arrive_a(b_lfull + 8u * (uint32_t)s);
@@ -495,7 +509,7 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
         const uint32_t acc_row = (uint32_t)L.ald * 8u;
         const uint32_t my_acc = a_acc + (uint32_t)(ridx * g + sub) * (uint32_t)KP * acc_row + (uint32_t)f * 8u;
         for (int i = 0; i < T; ++i) {
-          tp_wait(b_lfull + 8u * (uint32_t)s, sph, 6);
+          tp_wait_p(b_lfull + 8u * (uint32_t)s, sph, 6, prof, pw0);
           const uint32_t xs = a_x + (uint32_t)s * sbytes + (uint32_t)f * 8u, lab_b = a_lab + (uint32_t)s * (kTileRows * 4);
           for (int gi = ridx; gi < ng; gi += 2 * R) {
             // two groups in flight unless a sub-row would hit the same accumulator row in both
@@ -547,7 +561,7 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
         const bool act = 2 * lane < d;
         const uint32_t my_acc = a_acc + (uint32_t)lane * 16u;      // accumulator row j at j * 512 bytes
         for (int i = 0; i < T; ++i) {
-          tp_wait(b_lfull + 8u * (uint32_t)s, sph, 6);
+          tp_wait_p(b_lfull + 8u * (uint32_t)s, sph, 6, prof, pw0);
           const uint32_t xs = a_x + (uint32_t)s * sbytes + (uint32_t)lane * 16u, lab_b = a_lab + (uint32_t)s * (kTileRows * 4);
 #pragma unroll 1
           for (int gq = 0; gq < kTileRows / 32; ++gq) {
@@ -583,6 +597,11 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
     }
   }
 
+  if (prof && lane == 0) {
+    unsigned long long* o = L.prof + warp * 8;
+    o[0] = (unsigned long long)(clock64() - pt0); o[1] = (unsigned long long)pw0; o[2] = (unsigned long long)pw1; o[3] = (unsigned long long)pw2;
+    o[4] = (unsigned long long)pw3; o[5] = (unsigned long long)pcnt; o[6] = (unsigned long long)T; o[7] = 0ull;
+  }
   // ===================================================================== CTA-level combine (all warps)
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();

@@ -98,8 +98,61 @@ def bench(shapes, iters=10):
         print(json.dumps(row), flush=True)
 
 
+ROLE = ["screen"] * 8 + ["reduce"] * 4 + ["convert"] * 4 + ["producer", "mma"]
+
+
+def prof(shapes, iters=3):
+    """Per-warp cycle breakdown of CTA 0: where each role waits (site 0/1), refine cycles, listed rows."""
+    import ctypes
+    np, torch, N, O = _mods()
+    N.set_lloyd_variant(4)
+    for n, d, k in shapes:
+        g = torch.Generator(device="cuda"); g.manual_seed(1)
+        prof_c = torch.randn(k, d, dtype=torch.float64, device="cuda", generator=g) * 2
+        X = prof_c[torch.randint(0, k, (n,), device="cuda", generator=g)] + torch.randn(n, d, dtype=torch.float64, device="cuda", generator=g)
+        C = prof_c + 0.1
+        partial = torch.empty(k * d + k + 1, dtype=torch.float64, device="cuda"); scratch = N.new_scratch(d, k, "cuda")
+        xs = torch.zeros(1, dtype=torch.float64, device="cuda")
+        buf = torch.zeros(18 * 8, dtype=torch.int64, device="cuda")
+        N.assign_reduce(X, C, partial, scratch=scratch, xnorm2_sum=xs, xnorm2_mode=1)
+        fn = N.load().hkm_debug_tp_profile; fn.argtypes = [ctypes.c_void_p]; fn.restype = None
+        fn(ctypes.c_void_p(buf.data_ptr()))
+        for _ in range(iters):
+            N.assign_reduce(X, C, partial, scratch=scratch, xnorm2_sum=xs, xnorm2_mode=2)
+        torch.cuda.synchronize()
+        fn(None)
+        b = buf.cpu().numpy().reshape(18, 8)
+        tiles = max(int(b[16, 6]), 1)
+        print(json.dumps(dict(n=n, d=d, k=k, tiles_cta0=tiles, clk_per_tile=round(float(b[16, 0]) / tiles, 1))))
+        for w in range(18):
+            if b[w, 0] == 0:
+                continue
+            print(f"  warp {w:2d} {ROLE[w]:8s} total/tile {b[w, 0] / tiles:8.1f}  wait0 {b[w, 1] / tiles:8.1f}  wait1 {b[w, 2] / tiles:8.1f}  refine {b[w, 3] / tiles:7.1f}  listed/tile {b[w, 5] / tiles:6.2f}")
+        sys.stdout.flush()
+        del X
+    N.set_lloyd_variant(0)
+
+
 if __name__ == "__main__":
     cmd = sys.argv[1] if len(sys.argv) > 1 else "check"
+    if cmd == "single":     # python tools/tp_check.py single n d k [variant]: three passes, for ncu
+        np, torch, N, O = _mods()
+        n, d, k = int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4])
+        N.set_lloyd_variant(int(sys.argv[5]) if len(sys.argv) > 5 else 4)
+        g = torch.Generator(device="cuda"); g.manual_seed(1)
+        pc = torch.randn(k, d, dtype=torch.float64, device="cuda", generator=g) * 2
+        X = pc[torch.randint(0, k, (n,), device="cuda", generator=g)] + torch.randn(n, d, dtype=torch.float64, device="cuda", generator=g)
+        C = pc + 0.1
+        partial = torch.empty(k * d + k + 1, dtype=torch.float64, device="cuda"); scratch = N.new_scratch(d, k, "cuda")
+        xs = torch.zeros(1, dtype=torch.float64, device="cuda")
+        N.assign_reduce(X, C, partial, scratch=scratch, xnorm2_sum=xs, xnorm2_mode=1)
+        for _ in range(2):
+            N.assign_reduce(X, C, partial, scratch=scratch, xnorm2_sum=xs, xnorm2_mode=2)
+        torch.cuda.synchronize()
+        sys.exit(0)
+    if cmd == "prof":
+        prof([(20_000_000, 16, 16), (5_000_000, 24, 32), (20_000_000, 64, 64), (5_000_000, 24, 64)])
+        sys.exit(0)
     if cmd == "one":
         sys.exit(0 if one(int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4])) else 1)
     if cmd == "check":
