@@ -122,7 +122,8 @@ int assign_pass(const AssignArgs& a, const char* who) {
   const int mode = (a.mode == 0 && a.weights != nullptr) ? 3 : a.mode;   // weights are a compile-time property of the Lloyd kernels
   if (lloyd_tp_eligible(p, mode))                                        // k > 8 plain passes: pipelined tcgen05 screening + fp64 refinement
     return launch_lloyd_tp(p, reinterpret_cast<cudaStream_t>(a.stream));
-  if (lloyd_tc_eligible(p, mode) && lloyd_variant_override() != 1 && lloyd_variant_override() != 4)   // its unpipelined predecessor (weights / distances)
+  const int variant = lloyd_variant_override();
+  if (lloyd_tc_eligible(p, mode) && variant != 1 && variant != 4 && variant < 40)   // its unpipelined predecessor (weights / per-row distances)
     return launch_lloyd_tc(p, reinterpret_cast<cudaStream_t>(a.stream));
   return dispatch_lloyd(p, pl, grid, mode, reinterpret_cast<cudaStream_t>(a.stream));
 }
@@ -138,7 +139,7 @@ int hkm_version(void) { return 100; }
 int hkm_max_k(void) { return 64; }
 int hkm_max_d(void) { return 96; }
 int hkm_set_lloyd_variant(int variant) {
-  if (variant < 0 || variant > 5) { set_error("hkm_set_lloyd_variant: 0..5"); return HKM_ERR_INVALID; }
+  if (!((variant >= 0 && variant <= 5) || (variant >= 40 && variant <= 43))) { set_error("hkm_set_lloyd_variant: 0..5 (40..43: variant 4 with a pinned reduce scheme)"); return HKM_ERR_INVALID; }
   g_lloyd_variant = variant;
   return HKM_OK;
 }

@@ -8,27 +8,32 @@
 // rigorous error bound
 //     |approx_j - exact_j| <= eps = kappa |x - mu| max_j |c_j - mu| + eta max_j |c_j - mu|^2,   kappa = 1.04 * 2^-10
 // (two operands rounded to 11 bits each, fp32 accumulation over K <= 72 terms, 6 index bits packed into the score).
-// A row whose best approximate score beats the second best by more than 2 eps is decided; any other row goes to a
-// list and is re-scored exactly in fp64 against every centre within 2 eps of the best, with the same score, tie rule
-// (lowest index) and arithmetic as the fp64 kernels.  The tensor cores only prune; labels are the fp64 argmax.
+// A row whose best approximate score beats the second best by more than 2 eps is decided; any other row is re-scored
+// exactly in fp64 against every centre within 2 eps of the best, with the same score, tie rule (lowest index) and
+// arithmetic as the fp64 kernels.  The tensor cores only prune; labels are the fp64 argmax.
 //
 // Warp roles (18 warps, 576 threads, one CTA per SM):
 //   screen   4 or 8 warps (one or two groups of four; group g takes tiles i = g mod groups): thread = tile row; reads
 //            the row's tf32 operand back for |x - mu|, sweeps the TMEM accumulator once (top-2 with the centre index
-//            packed into the low mantissa bits), decides or lists the row, then the group re-scores its listed rows
-//            cooperatively (lane = feature pair) and publishes the tile's labels.
-//   reduce   8 or 4 warps: per-cluster fp64 sums in shared memory.  Small k*d: every warp owns private accumulator sets
-//            and a fixed share of the tile's rows (several rows per instruction, each in its own set; no ballots, no
-//            imbalance).  Large k*d: one shared set, warp r owns the clusters j = r mod R.
+//            packed into the low mantissa bits) and decides the row; undecided rows of the warp are then re-scored
+//            by that warp cooperatively (lane = feature pair).  Publishes the tile's labels.
+//   reduce   8 or 4 warps: per-cluster fp64 sums, three schemes picked per shape:
+//            k <= 16: S += onehot(labels)^T X on the fp64 tensor pipe (DMMA.8x8x4), accumulators in registers, every
+//                     warp a fixed share of the rows -- k*d/64 pipe clocks per row, 0.7 of the pipe at the HBM rate;
+//            small k*d: private accumulator sets in shared memory, a fixed share of the rows per warp, several rows
+//                     per instruction, each in its own set (no ballots, no imbalance, but 24 d bytes of shared-memory
+//                     traffic per row);
+//            otherwise: warp r owns the clusters j = r mod R, accumulators in registers, rows found by ballot.
 //   convert  4 warps: fp64 stage -> (x - mu) rounded to tf32 -> canonical K-major UMMA operand.
 //   producer 1 warp: 1-D bulk-async copies into the ring;   mma 1 warp: one thread issues tcgen05.mma + commit.
 // Everything meets through mbarriers (full/empty per ring stage, per operand buffer, per TMEM buffer, labels-ready
 // per stage); the only CTA barrier is at the end.  Constant -0.5|c - mu|^2 rides inside the MMA as three extra K
-// columns (a tf32 hi/mid/lo split against a column of ones), so the sweep is 4 instructions per centre.
+// columns (a tf32 hi/mid/lo split against a column of ones), so the sweep is ~4.5 instructions per centre.
 // Rows per cluster are counted with shared-memory integer atomics; the cost needs no per-row work:
 //     sum_rows (x.c_label - 0.5|c_label|^2) = sum_j S_j.c_j - 0.5 sum_j n_j |c_j|^2.
-// Summation order is fixed (row order within a reduce warp, set order in the combine, CTA order in the fold), so
-// results are bit-stable.  Plain passes only (unit weights, no per-row distances); the dispatcher sends the rest elsewhere.
+// Summation order is fixed (row order within a reduce warp, warp / set order in the combine, CTA order in the fold),
+// so results are bit-stable.  Plain passes only (unit weights, no per-row distances); the dispatcher sends the rest
+// elsewhere.
 #pragma once
 #include "hkm_lloyd.cuh"
 
@@ -40,36 +45,34 @@ constexpr int kTpConvWarps = 4;
 constexpr int kTpConvWarp0 = 12, kTpProdWarp = 16, kTpMmaWarp = 17;
 __host__ __device__ constexpr int tp_reduce_warps(int sg) { return 12 - 4 * sg; }   // screen groups of four warps + reduce warps = 12
 __host__ __device__ constexpr int tp_tmem_stride(int kp) { return kp <= 32 ? 32 : (kp <= 64 ? 64 : (kp <= 128 ? 128 : 256)); }
+// feature-count class of ND = ceil(d / 8): rows are handled as if they had 8, 16, 32 or 64 features
+__host__ __device__ constexpr int tp_dclass(int nd) { return nd <= 1 ? 8 : (nd <= 2 ? 16 : (nd <= 4 ? 32 : 64)); }
+__host__ __device__ constexpr int tp_lanes_per_row(int nd, int vec) { return tp_dclass(nd) / vec < 4 ? 4 : (tp_dclass(nd) / vec > 32 ? 32 : tp_dclass(nd) / vec); }
 
-__host__ __device__ inline int tp_pow2ceil(int v) { int p = 1; while (p < v) p <<= 1; return p; }
-
-// reduce modes: 0 private sets, lane = feature (d <= 32); 1 private sets, lane = feature pair (even d <= 64);
-//               2 one shared set, clusters owned per warp, lane = feature pair (even d <= 64)
+// reduce modes: 0 private sets in shared memory, lane = feature (d <= 32); 1 the same, lane = feature pair (even d <= 64);
+//               2 clusters owned per warp, accumulators in registers; 3 one-hot DMMA (k <= 16), accumulators in registers
 struct TpPlan {
-  int stages, rmode, na, sg;   // ring depth, reduce mode, tf32 operand buffers (1 or 2), screen groups (1 or 2)
-  int c_lpr, c_g;            // converter: lanes per row, rows per instruction
-  int r_lpr, r_g, ald, nsets;  // reducer: lanes per row, rows per instruction, accumulator row (doubles), sets
+  int stages, rmode, na, sg, nd;   // ring depth, reduce mode, tf32 operand buffers (1 or 2), screen groups (1 or 2), ceil(d/8)
+  int ald, nsets;                  // rmode 0/1: accumulator row (doubles), sets
   int kchunks, lbo_a, lbo_b, a_bytes;
-  int x_off, a_off, b_off, acc_off, cn_off, mu_off, cnt_off, lab_off, list_off, lcnt_off, red_off, bar_off, tmem_off, total;
+  int x_off, a_off, b_off, acc_off, cn_off, mu_off, cnt_off, lab_off, red_off, bar_off, tmem_off, total;
   unsigned long long* prof;   // developer profile (tools/tp_check.py prof): [warp][8] cycle counters of CTA 0, or null
 };
 
 __host__ __device__ inline TpPlan tp_plan(int d, int kp, int stages, int rmode, int na, int sg) {
   TpPlan L{};
-  L.stages = stages; L.rmode = rmode; L.na = na; L.sg = sg;
+  L.stages = stages; L.rmode = rmode; L.na = na; L.sg = sg; L.nd = (d + 7) / 8;
   const int cvec = (d & 1) ? 1 : 2;
-  int cl = tp_pow2ceil((d + cvec - 1) / cvec); if (cl < 4) cl = 4; if (cl > 32) cl = 32;
-  L.c_lpr = cl; L.c_g = 32 / cl;
+  const int c_g = 32 / tp_lanes_per_row(L.nd, cvec);
   const int R = tp_reduce_warps(sg);
-  if (rmode == 2) { L.r_lpr = 32; L.r_g = 1; L.ald = 64; L.nsets = 1; }
-  else {
+  if (rmode <= 1) {
     const int rvec = rmode == 0 ? 1 : 2;
-    int rl = tp_pow2ceil((d + rvec - 1) / rvec); if (rl < 4) rl = 4; if (rl > 32) rl = 32;
-    L.r_lpr = rl; L.r_g = 32 / rl; L.ald = rl * rvec; L.nsets = R * L.r_g;
+    const int rl = tp_lanes_per_row(L.nd, rvec);
+    L.ald = rl * rvec; L.nsets = R * (32 / rl);
   }
   const int d8 = (d + 7) & ~7;
   L.kchunks = (d8 + 8) / 4;
-  const int pad_a = 8 * L.c_g > 16 ? 8 * L.c_g : 16;
+  const int pad_a = 8 * c_g > 16 ? 8 * c_g : 16;
   L.lbo_a = (kTileRows / 8) * 128 + pad_a;
   L.lbo_b = (kp / 8) * 128 + 16;
   L.a_bytes = (L.kchunks * L.lbo_a + 127) & ~127;
@@ -82,8 +85,6 @@ __host__ __device__ inline TpPlan tp_plan(int d, int kp, int stages, int rmode, 
   L.mu_off = o; o += (d8 + 8) * 8;
   L.cnt_off = o; o += kp * 4;
   L.lab_off = o; o += (stages > 0 ? stages : 2) * kTileRows * 4;
-  L.list_off = o; o += sg * 2 * kTileRows * 16;       // [group][parity][row] entries {row, mask_lo, mask_hi, -}
-  L.lcnt_off = o; o += 2 * 4 * 4;                     // [group][3] entry counters
   L.red_off = o; o += (2 * kTpWarps + 64) * 8;
   L.bar_off = o; o += (3 * kMaxStages + 8) * 8;
   L.tmem_off = o; o += 16;
@@ -92,19 +93,24 @@ __host__ __device__ inline TpPlan tp_plan(int d, int kp, int stages, int rmode, 
 }
 
 // Picks reduce mode, operand buffering, screen groups and ring depth for a shape; stages < 2 => the shape does not fit.
-// Preference: two screen groups for k > 32, private accumulator sets, two operand buffers -- whatever of that still
-// leaves three ring stages; failing that, the combination with the deepest ring.
-__host__ inline TpPlan tp_choose(int d, int kp) {
+// force_rmode >= 0 pins the reduce mode (tuning).
+__host__ inline TpPlan tp_choose(int d, int kp, int force_rmode = -1) {
   const int budget = 227 * 1024 - 1024;
   TpPlan best{}; best.stages = 0;
   const int sg_pref = kp >= 48 ? 2 : 1;
   for (int si = 0; si < 2; ++si) {
     const int sg = si == 0 ? sg_pref : 3 - sg_pref;
     if (sg == 2 && kp < 48) continue;
-    for (int mi = 0; mi < 2; ++mi) {
-      const int rm = mi == 0 ? (d <= 32 ? 0 : 1) : 2;
-      if (rm == 2 && (d & 1)) continue;
-      if (rm == 1 && (d & 1)) continue;
+    // order of preference: DMMA reduce for k <= 16; else register-owned clusters; private shared-memory sets on request
+    int modes[3]; int nm = 0;
+    if (force_rmode >= 0) modes[nm++] = force_rmode;
+    else { if (kp == 16) modes[nm++] = 3; modes[nm++] = 2; }
+    for (int mi = 0; mi < nm; ++mi) {
+      const int rm = modes[mi];
+      if (rm == 3 && (kp != 16 || sg != 1)) continue;
+      if (rm == 0 && d > 32) continue;
+      if (rm == 1 && ((d & 1) || d <= 32)) continue;
+      if (rm == 2 && (d & 1) && d > 32) continue;
       for (int na = 2; na >= 1; --na) {
         const int fixed = tp_plan(d, kp, 2, rm, na, sg).total - 2 * stage_bytes(d) - 2 * kTileRows * 4;
         int st = (budget - fixed) / (stage_bytes(d) + kTileRows * 4);
@@ -130,20 +136,22 @@ __device__ __forceinline__ void tp_tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) 
                  "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
                : "r"(taddr));
 }
-// mbarrier wait with a watchdog: a protocol bug must end the kernel with a message, not hang the GPU
-static __device__ __noinline__ void tp_wait_timeout(uint32_t bar, uint32_t parity, int tag) {
-  const long long t0 = clock64();
-  while (!mbar_test_a(bar, parity)) {
-    if (clock64() - t0 > 6000000000LL) {   // ~3 s
-      printf("lloyd_tp: block %d warp %d stuck on barrier tag %d (smem 0x%x, parity %u)\n", (int)blockIdx.x, (int)(threadIdx.x >> 5), tag, bar, parity);
-      __trap();
-    }
-  }
+// mbarrier wait: the thread sleeps in hardware until the phase flips (suspend-time hint 1 ms per try, so a waiting warp
+// costs no issue slots); a protocol bug ends the kernel with a message after ~3 s instead of hanging the GPU
+__device__ __forceinline__ bool tp_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\nselp.u32 %0, 1, 0, p;\n}\n"
+               : "=r"(ok) : "r"(bar), "r"(parity), "r"(1000000u) : "memory");
+  return ok != 0;
+}
+static __device__ __noinline__ void tp_wait_slow(uint32_t bar, uint32_t parity, int tag) {
+  for (int it = 0; it < 3000; ++it) if (tp_try_wait(bar, parity)) return;
+  printf("lloyd_tp: block %d warp %d stuck on barrier tag %d (smem 0x%x, parity %u)\n", (int)blockIdx.x, (int)(threadIdx.x >> 5), tag, bar, parity);
+  __trap();
 }
 __device__ __forceinline__ void tp_wait(uint32_t bar, uint32_t parity, int tag) {
-  if (mbar_test_a(bar, parity)) return;
-  if (mbar_test_a(bar, parity)) return;
-  tp_wait_timeout(bar, parity, tag);
+  if (tp_try_wait(bar, parity)) return;
+  tp_wait_slow(bar, parity, tag);
 }
 // wait that adds the cycles it spent to *acc when profiling
 __device__ __forceinline__ void tp_wait_p(uint32_t bar, uint32_t parity, int tag, bool prof, long long& acc) {
@@ -157,8 +165,8 @@ __device__ __forceinline__ void mbar_arrive_a(uint32_t bar) { asm volatile("mbar
 __device__ __forceinline__ void lds_v2f64(uint32_t a, double& x, double& y) { asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(x), "=d"(y) : "r"(a)); }
 __device__ __forceinline__ void sts_v2f64(uint32_t a, double x, double y) { asm volatile("st.shared.v2.f64 [%0], {%1,%2};" ::"r"(a), "d"(x), "d"(y) : "memory"); }
 
-// KP = padded cluster count (16, 32, 48, 64); CVEC = 2 (even d) or 1; RMODE as in TpPlan; SG = screen groups.
-template <int KP, int CVEC, int RMODE, int SG>
+// KP = padded cluster count (16, 32, 48, 64); CVEC = 2 (even d) or 1; RMODE as in TpPlan; SG = screen groups; ND = ceil(d/8).
+template <int KP, int CVEC, int RMODE, int SG, int ND>
 __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydParams p, const TpPlan L) {
   if (p.skip != nullptr && *p.skip != 0) return;
   constexpr int R = tp_reduce_warps(SG);
@@ -168,13 +176,14 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
   constexpr int IDXBITS = 6;
   constexpr uint32_t IDXMASK = (1u << IDXBITS) - 1u;
   static_assert(KP % 16 == 0 && KP >= 16 && KP <= 64, "k_pad: 16..64 in steps of 16");
+  static_assert(RMODE != 3 || (KP == 16 && SG == 1), "one-hot DMMA reduce: k <= 16, eight reduce warps");
 
   extern __shared__ __align__(1024) unsigned char smem[];
   const int d = p.d, k = p.k;
   const int S = L.stages;
   const uint32_t sb = smem_u32(smem);
   const uint32_t a_x = sb + L.x_off, a_A = sb + L.a_off, a_B = sb + L.b_off, a_acc = sb + L.acc_off;
-  const uint32_t a_lab = sb + L.lab_off, a_list = sb + L.list_off, a_lcnt = sb + L.lcnt_off, a_cnt = sb + L.cnt_off;
+  const uint32_t a_lab = sb + L.lab_off, a_cnt = sb + L.cnt_off;
   const uint32_t a_bar = sb + L.bar_off;
   const uint32_t b_full = a_bar, b_sempty = a_bar + 8u * kMaxStages, b_lfull = a_bar + 16u * kMaxStages;
   const uint32_t b_afull = a_bar + 24u * kMaxStages, b_aempty = b_afull + 16u, b_tfull = b_afull + 32u, b_tempty = b_afull + 48u;
@@ -195,7 +204,7 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
   const bool tail_mine = tail_rows > 0 && (int)(full_tiles % gridDim.x) == (int)blockIdx.x;
   const int T = my_tiles + (tail_mine ? 1 : 0);    // the ragged tail is this CTA's last tile
   const bool prof = L.prof != nullptr && blockIdx.x == 0;
-  long long pw0 = 0, pw1 = 0, pw2 = 0, pw3 = 0, pcnt = 0;     // profile: cycles in wait sites 0..3, an event counter
+  long long pw0 = 0, pw1 = 0, pw2 = 0, pcnt = 0;     // profile: cycles in wait sites 0/1, refine cycles, refined rows
   const bool do_reduce = p.do_reduce == 1;
   const int xx_mode = p.xx_mode;
   const bool na2 = L.na == 2;
@@ -220,11 +229,10 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(sb + L.tmem_off), "n"(TCOLS) : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
-  // zero: both A operands, B, the accumulators, counters
+  // zero: the A operands, B, the accumulators, counters
   for (int i = tid; i < (L.acc_off - L.a_off) / 16; i += kTpThreads) reinterpret_cast<uint4*>(smem + L.a_off)[i] = make_uint4(0, 0, 0, 0);
   for (int i = tid; i < (L.nsets * KP * L.ald) / 2; i += kTpThreads) reinterpret_cast<uint4*>(smem + L.acc_off)[i] = make_uint4(0, 0, 0, 0);
   for (int i = tid; i < KP; i += kTpThreads) cnt_s[i] = 0u;
-  if (tid < 8) reinterpret_cast<unsigned int*>(smem + L.lcnt_off)[tid] = 0u;
   if (tid < d8 + 8) { double s = 0; if (tid < d) for (int j = 0; j < k; ++j) s += p.C[(size_t)j * d + tid]; mu_s[tid] = tid < d ? s / k : 0.0; }   // mu = mean of the centres
   __syncthreads();
   double* h_s = red_s + 2 * kTpWarps;   // [KP] |c - mu|^2, later the centre-update scratch
@@ -270,6 +278,11 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
   const uint32_t tmem = *reinterpret_cast<const uint32_t*>(smem + L.tmem_off);
 
   double cost = 0, xxs = 0;
+  constexpr int RVEC2 = ND > 4 ? 2 : 1;                        // RMODE 2: lane = feature (d <= 32) or feature pair
+  constexpr int NM = KP / R;                                   // RMODE 2: clusters owned per warp
+  const int P = k * d + k + 1;
+  const int SL = P + 1 + k;
+  double* out = p.cta_partials + (size_t)blockIdx.x * SL;       // this CTA's slot of the scratch
   const long long pt0 = prof ? clock64() : 0;
 
   if (warp == kTpProdWarp) {
@@ -327,15 +340,15 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
     }
   } else if (warp >= kTpConvWarp0) {
     // ===================================================================== converters
+    // lane = (row of the group, feature pair); a warp converts chunks cw and cw + 4, C_G rows per instruction
+    constexpr int C_LPR = tp_lanes_per_row(ND, CVEC), C_G = 32 / C_LPR, NIT = kChunkRows / C_G;
     const int cw = warp - kTpConvWarp0;
-    const int lpr = L.c_lpr, g = L.c_g;
-    const int subc = lane / lpr, fc = (lane % lpr) * CVEC;
+    const int subc = lane / C_LPR, fc = (lane % C_LPR) * CVEC;
     const bool act = fc < d;
     const double mu0 = act ? mu_s[fc] : 0.0, mu1 = (CVEC == 2 && act) ? mu_s[fc + 1] : 0.0;
     const uint32_t dst_lane = (uint32_t)(fc >> 2) * LBO_A + (uint32_t)(fc & 3) * 4u + (uint32_t)subc * 16u;
     const uint32_t src_lane = (uint32_t)subc * row_bytes + (uint32_t)fc * 8u;
-    const int nit = kChunkRows / g;
-    const uint32_t src_it = (uint32_t)g * row_bytes, dst_it = (uint32_t)g * 16u;
+    const uint32_t src_it = (uint32_t)C_G * row_bytes;
     const bool need_xx = do_reduce && xx_mode != 2;
     int s = 0; uint32_t sph = 0;
     for (int i = 0; i < T; ++i) {
@@ -343,21 +356,33 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
       tp_wait_p(b_full + 8u * (uint32_t)s, sph, 3, prof, pw0);
       tp_wait_p(b_aempty + 8u * b, ph ^ 1u, 4, prof, pw1);
       const uint32_t xs = a_x + (uint32_t)s * sbytes, ab = a_A + b * (uint32_t)L.a_bytes;
-#pragma unroll 1
-      for (int cc = cw; cc < kChunks; cc += kTpConvWarps) {
-        const uint32_t src0 = xs + (uint32_t)cc * cstride + src_lane;
-        const uint32_t dst0 = ab + (uint32_t)cc * 256u + dst_lane;
-        if (act) {
-#pragma unroll 4
-          for (int it = 0; it < nit; ++it) {
-            double v0, v1 = 0.0;
-            if (CVEC == 2) lds_v2f64(src0 + (uint32_t)it * src_it, v0, v1); else v0 = lds_f64(src0 + (uint32_t)it * src_it);
-            if (need_xx) { xxs = fma(v0, v0, xxs); if (CVEC == 2) xxs = fma(v1, v1, xxs); }
-            const uint32_t t0 = f32_to_tf32_rn((float)(v0 - mu0));
-            if (CVEC == 2) {
-              const uint32_t t1 = f32_to_tf32_rn((float)(v1 - mu1));
-              asm volatile("st.shared.v2.u32 [%0], {%1,%2};" ::"r"(dst0 + (uint32_t)it * dst_it), "r"(t0), "r"(t1) : "memory");
-            } else sts_u32(dst0 + (uint32_t)it * dst_it, t0);
+      if (act) {
+#pragma unroll
+        for (int cq = 0; cq < kChunks / kTpConvWarps; ++cq) {
+          const int cc = cw + cq * kTpConvWarps;
+          const uint32_t src0 = xs + (uint32_t)cc * cstride + src_lane;
+          const uint32_t dst0 = ab + (uint32_t)cc * 256u + dst_lane;
+          constexpr int NB = NIT > 8 ? 8 : NIT;              // rows in flight per lane (register budget)
+#pragma unroll
+          for (int it0 = 0; it0 < NIT; it0 += NB) {
+            double v0[NB], v1[NB];
+#pragma unroll
+            for (int it = 0; it < NB; ++it) {
+              v1[it] = 0.0;
+              if (CVEC == 2) lds_v2f64(src0 + (uint32_t)(it0 + it) * src_it, v0[it], v1[it]); else v0[it] = lds_f64(src0 + (uint32_t)(it0 + it) * src_it);
+            }
+            if (need_xx) {
+#pragma unroll
+              for (int it = 0; it < NB; ++it) { xxs = fma(v0[it], v0[it], xxs); if (CVEC == 2) xxs = fma(v1[it], v1[it], xxs); }
+            }
+#pragma unroll
+            for (int it = 0; it < NB; ++it) {
+              const uint32_t t0 = f32_to_tf32_rn((float)(v0[it] - mu0));
+              if (CVEC == 2) {
+                const uint32_t t1 = f32_to_tf32_rn((float)(v1[it] - mu1));
+                asm volatile("st.shared.v2.u32 [%0], {%1,%2};" ::"r"(dst0 + (uint32_t)((it0 + it) * C_G * 16)), "r"(t0), "r"(t1) : "memory");
+              } else sts_u32(dst0 + (uint32_t)((it0 + it) * C_G * 16), t0);
+            }
           }
         }
       }
@@ -373,30 +398,29 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
     const uint32_t tlane = ((uint32_t)(32 * wsub)) << 16;
     const float kapv = 1.04f * 0.0009765625f * vmax;               // kappa * max|c - mu|
     const float etab = 0.5f * 1.52587890625e-05f * vmax * vmax;    // eta * max 0.5|c - mu|^2, eta = 2^-16
-    const int dch = d8 / 4;
+    constexpr int DCH = 2 * ND;                                    // 16-byte chunks of the converted row
     const bool conv2 = (d & 1) == 0;
     const int rlane = conv2 ? 2 * lane : lane;                     // refine: first feature of this lane
     const bool ract = rlane < d;
+    int s = grp % S;
     for (int i = grp; i < T; i += SG) {
-      const int s = i % S;
       const uint32_t b = (uint32_t)(i & 1), ph = (uint32_t)((i >> 1) & 1);
       const int rows_valid = i < my_tiles ? kTileRows : tail_rows;
       const int64_t r0 = i < my_tiles ? ((int64_t)blockIdx.x + (int64_t)i * gridDim.x) * kTileRows : full_tiles * kTileRows;
-      const int li = i / SG;                                       // this group's tile counter
       const uint32_t lab_b = a_lab + (uint32_t)s * (kTileRows * 4);
-      const uint32_t list_b = a_list + (uint32_t)((grp * 2 + (li & 1)) * kTileRows) * 16u;
-      const uint32_t lc_cur = a_lcnt + (uint32_t)(grp * 4 + li % 3) * 4u, lc_next = a_lcnt + (uint32_t)(grp * 4 + (li + 1) % 3) * 4u;
       tp_wait_p(b_tfull + 8u * b, ph, 5, prof, pw0);
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       // |x - mu|^2 of this row from the tf32 operand the tensor core just consumed
       const uint32_t abuf = na2 ? b : 0u;
       const uint32_t arow = a_A + abuf * (uint32_t)L.a_bytes + (uint32_t)row * 16u;
-      float xn2 = 0.f;
-      for (int c = 0; c < dch; ++c) {
+      float xa = 0.f, xb = 0.f;
+#pragma unroll
+      for (int c = 0; c < DCH; ++c) {
         float4 a;
         asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "r"(arow + (uint32_t)c * LBO_A));
-        xn2 = fmaf(a.x, a.x, xn2); xn2 = fmaf(a.y, a.y, xn2); xn2 = fmaf(a.z, a.z, xn2); xn2 = fmaf(a.w, a.w, xn2);
+        xa = fmaf(a.x, a.x, xa); xb = fmaf(a.y, a.y, xb); xa = fmaf(a.z, a.z, xa); xb = fmaf(a.w, a.w, xb);
       }
+      const float xn2 = xa + xb;
       __syncwarp();
       if (lane == 0) mbar_arrive_a(b_aempty + 8u * abuf);        // the operand buffer can take the next conversion
       // sweep 1: best and second best approximate score, centre index in the low mantissa bits
@@ -420,11 +444,12 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
       const float thr = m1 - 2.0f * eps;
       const bool amb = valid && !(m2 < thr);
       const int j1 = (int)(__float_as_uint(m1) & IDXMASK);
-      if (__any_sync(0xffffffffu, amb)) {
-        // sweep 2 (only when some row of the warp is undecided): every centre within 2 eps of the best is a candidate
-        uint32_t w[NW];
+      unsigned ambmask = __ballot_sync(0xffffffffu, amb);
+      uint32_t w[NW];
 #pragma unroll
-        for (int q = 0; q < NW; ++q) w[q] = 0u;
+      for (int q = 0; q < NW; ++q) w[q] = 0u;
+      if (ambmask) {
+        // sweep 2 (only when some row of the warp is undecided): every centre within 2 eps of the best is a candidate
 #pragma unroll
         for (int ch = 0; ch < KP / 16; ++ch) {
           uint32_t v[16];
@@ -433,122 +458,139 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
 #pragma unroll
           for (int c = 0; c < 16; ++c) w[ch >> 1] |= (__uint_as_float(v[c]) >= thr) ? (1u << ((ch & 1) * 16 + c)) : 0u;
         }
-        if (amb) {
-          unsigned slot;
-          asm volatile("atom.shared.add.u32 %0, [%1], 1;" : "=r"(slot) : "r"(lc_cur) : "memory");
-          asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(list_b + 16u * slot), "r"((uint32_t)row), "r"(w[0]), "r"(NW > 1 ? w[NW - 1] : 0u), "r"(0u) : "memory");
-        }
       }
       // the TMEM buffer is free again
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
       __syncwarp();
       if (lane == 0) mbar_arrive_a(b_tempty + 8u * b);
       if (!amb) {
-        sts_u32(lab_b + 4u * (uint32_t)row, valid ? (uint32_t)j1 : 0xffffffffu);
+        // rows past the end of the table are zero filled: label 0 adds nothing to the sums and is never counted or stored
+        sts_u32(lab_b + 4u * (uint32_t)row, valid ? (uint32_t)j1 : 0u);
         if (valid) {
           if (p.labels_out != nullptr) p.labels_out[r0 + row] = j1;
           if (do_reduce) asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(a_cnt + 4u * (uint32_t)j1) : "memory");
         }
       }
-      if (wsub == 0 && lane == 0) sts_u32(lc_next, 0u);              // the counter two tiles back: all its readers passed the previous barrier
-      { const long long tb = prof ? clock64() : 0; named_bar_sync(1 + grp, 128); if (prof) pw1 += clock64() - tb; }
-      // cooperative exact re-scoring of the listed rows: warp per row, lane = feature (pair), ascending centre index
-      const unsigned namb = lds_u32(lc_cur);
-      const long long tr0 = prof ? clock64() : 0;
-      pcnt += namb;
-      const uint32_t xs = a_x + (uint32_t)s * sbytes;
-      for (unsigned e = (unsigned)wsub; e < namb; e += 4u) {
-        const uint4 en = lds_v4(list_b + 16u * e);
-        const int rr = (int)en.x;
-        const uint32_t ra = xs + (uint32_t)(rr >> 4) * cstride + (uint32_t)(rr & 15) * row_bytes + (uint32_t)rlane * 8u;
-        double x0 = 0.0, x1 = 0.0;
-        if (ract) { if (conv2) lds_v2f64(ra, x0, x1); else x0 = lds_f64(ra); }
-        double best = -__longlong_as_double(0x7ff0000000000000LL); int bj = -1;
+      if (ambmask) {
+        // exact re-scoring of this warp's undecided rows, one at a time, lane = feature (pair), ascending centre index
+        const long long tr0 = prof ? clock64() : 0;
+        const uint32_t xs = a_x + (uint32_t)s * sbytes;
+        while (ambmask) {
+          const int src = __ffs(ambmask) - 1; ambmask &= ambmask - 1;
+          const int rr = 32 * wsub + src;
+          uint32_t cm[NW];
 #pragma unroll
-        for (int q = 0; q < NW; ++q) {
-          uint32_t msk = q == 0 ? en.y : en.z;
-          while (msk) {
-            const int j = 32 * q + __ffs(msk) - 1; msk &= msk - 1;
-            double c0 = 0.0, c1 = 0.0;
-            if (ract) {
-              if (conv2) { const double2 cc = __ldg(reinterpret_cast<const double2*>(p.C + (size_t)j * d + rlane)); c0 = cc.x; c1 = cc.y; }
-              else c0 = __ldg(p.C + (size_t)j * d + rlane);
+          for (int q = 0; q < NW; ++q) cm[q] = __shfl_sync(0xffffffffu, w[q], src);
+          const uint32_t ra = xs + (uint32_t)(rr >> 4) * cstride + (uint32_t)(rr & 15) * row_bytes + (uint32_t)rlane * 8u;
+          double x0 = 0.0, x1 = 0.0;
+          if (ract) { if (conv2) lds_v2f64(ra, x0, x1); else x0 = lds_f64(ra); }
+          double best = -__longlong_as_double(0x7ff0000000000000LL); int bj = -1;
+#pragma unroll
+          for (int q = 0; q < NW; ++q) {
+            uint32_t msk = cm[q];
+            while (msk) {
+              const int j = 32 * q + __ffs(msk) - 1; msk &= msk - 1;
+              double c0 = 0.0, c1 = 0.0;
+              if (ract) {
+                if (conv2) { const double2 cc = __ldg(reinterpret_cast<const double2*>(p.C + (size_t)j * d + rlane)); c0 = cc.x; c1 = cc.y; }
+                else c0 = __ldg(p.C + (size_t)j * d + rlane);
+              }
+              double sdot = fma(x0, c0, x1 * c1);
+#pragma unroll
+              for (int mk = 16; mk >= 1; mk >>= 1) sdot += shfl_xor_d(sdot, mk);
+              const double sc = sdot + cn_s[j];
+              if (sc > best) { best = sc; bj = j; }
             }
-            double sdot = fma(x0, c0, x1 * c1);
-#pragma unroll
-            for (int mk = 16; mk >= 1; mk >>= 1) sdot += shfl_xor_d(sdot, mk);
-            const double sc = sdot + cn_s[j];
-            if (sc > best) { best = sc; bj = j; }
           }
+          if (lane == 0) {
+            sts_u32(lab_b + 4u * (uint32_t)rr, (uint32_t)bj);
+            if (p.labels_out != nullptr) p.labels_out[r0 + rr] = bj;
+            if (do_reduce) asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(a_cnt + 4u * (uint32_t)bj) : "memory");
+          }
+          ++pcnt;
         }
-        if (lane == 0) {
-          sts_u32(lab_b + 4u * (uint32_t)rr, (uint32_t)bj);
-          if (p.labels_out != nullptr) p.labels_out[r0 + rr] = bj;
-          if (do_reduce) asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(a_cnt + 4u * (uint32_t)bj) : "memory");
-        }
+        if (prof) pw2 += clock64() - tr0;
       }
-      if (prof) pw2 += clock64() - tr0;
       __syncwarp();
       if (lane == 0) {
         mbar_arrive_a(b_lfull + 8u * (uint32_t)s);
         if (!do_reduce) mbar_arrive_a(b_sempty + 8u * (uint32_t)s);
       }
+      s += SG; if (s >= S) s -= S;
     }
   } else {
     // ===================================================================== reduce warps
     const int ridx = warp - 4 * SG;
     if (do_reduce) {
       int s = 0; uint32_t sph = 0;
-      if constexpr (RMODE != 2) {
-        // private sets: this warp's rows are the groups gi = ridx, ridx + R, ... of r_g consecutive rows; sub-row `sub` of a
-        // group accumulates into set ridx * r_g + sub, so no two lanes ever meet on an address
-        constexpr int RVEC = RMODE == 0 ? 1 : 2;
-        const int lpr = L.r_lpr, g = L.r_g, ng = kTileRows / g;
-        const int sub = lane / lpr, f = (lane % lpr) * RVEC;
+      if constexpr (RMODE == 3) {
+        // S[k, d] += onehot(labels)^T X on the fp64 tensor pipe.  The warp takes sub-tiles i0 = ridx and i1 = ridx + 8: row i of
+        // every 16-row chunk, so the four rows of a k-step sit in four different chunks (32 bytes apart modulo 128: the
+        // fragment loads are conflict free).  racc[(mt * ND + nd) * 2 + e] = S[8 mt + g][8 nd + 2 t + e].
+        const int g = lane >> 2, t = lane & 3;
+        double racc[2 * ND * 2];
+#pragma unroll
+        for (int q = 0; q < 2 * ND * 2; ++q) racc[q] = 0.0;
+        const uint32_t b_frag = (uint32_t)t * cstride + (uint32_t)g * 8u;
+        const uint32_t l_frag = (uint32_t)(16 * t) * 4u;
+        for (int i = 0; i < T; ++i) {
+          tp_wait_p(b_lfull + 8u * (uint32_t)s, sph, 6, prof, pw0);
+          const uint32_t xs = a_x + (uint32_t)s * sbytes + b_frag, lab_b = a_lab + (uint32_t)s * (kTileRows * 4) + l_frag;
+#pragma unroll
+          for (int ks = 0; ks < 4; ++ks) {
+            const int isub = (ks < 2) ? ridx : ridx + 8;           // sub-tile: row isub of chunks 4 (ks & 1) + t
+            const int labt = (int)lds_u32(lab_b + (uint32_t)(64 * (ks & 1) + isub) * 4u);
+            const double a0 = labt == g ? 1.0 : 0.0, a1 = labt == g + 8 ? 1.0 : 0.0;
+            const uint32_t xb = xs + (uint32_t)(4 * (ks & 1)) * cstride + (uint32_t)isub * row_bytes;
+#pragma unroll
+            for (int nd = 0; nd < ND; ++nd) {
+              const bool ok = (nd < ND - 1) || (8 * nd + g < d);
+              const double b2 = ok ? lds_f64(xb + 64u * nd) : 0.0;
+              dmma884(racc[(0 * ND + nd) * 2], racc[(0 * ND + nd) * 2 + 1], a0, b2);
+              dmma884(racc[(1 * ND + nd) * 2], racc[(1 * ND + nd) * 2 + 1], a1, b2);
+            }
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive_a(b_sempty + 8u * (uint32_t)s);
+          if (++s == S) { s = 0; sph ^= 1u; }
+        }
+        // every tile is reduced, so the ring is idle: the reduce warps park their fragments there, slab r = [KP][8 ND] doubles
+        named_bar_sync(1, R * 32);
+        {
+          double* slab = reinterpret_cast<double*>(smem + L.x_off) + (size_t)ridx * KP * (8 * ND);
+#pragma unroll
+          for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int nd = 0; nd < ND; ++nd) {
+              double* c2 = slab + (8 * mt + g) * (8 * ND) + 8 * nd + 2 * t;
+              c2[0] = racc[(mt * ND + nd) * 2]; c2[1] = racc[(mt * ND + nd) * 2 + 1];
+            }
+        }
+      } else if constexpr (RMODE == 2) {
+        // warp r owns the clusters r + R m; accumulators in registers; rows found by ballot, in tile order
+        const int f = lane * RVEC2;
         const bool act = f < d;
-        const uint32_t acc_row = (uint32_t)L.ald * 8u;
-        const uint32_t my_acc = a_acc + (uint32_t)(ridx * g + sub) * (uint32_t)KP * acc_row + (uint32_t)f * 8u;
+        double racc[NM * RVEC2];
+#pragma unroll
+        for (int q = 0; q < NM * RVEC2; ++q) racc[q] = 0.0;
         for (int i = 0; i < T; ++i) {
           tp_wait_p(b_lfull + 8u * (uint32_t)s, sph, 6, prof, pw0);
           const uint32_t xs = a_x + (uint32_t)s * sbytes + (uint32_t)f * 8u, lab_b = a_lab + (uint32_t)s * (kTileRows * 4);
-          for (int gi = ridx; gi < ng; gi += 2 * R) {
-            // two groups in flight unless a sub-row would hit the same accumulator row in both
-            const int rA = gi * g + sub, rB = (gi + R) * g + sub;
-            const bool hasB = gi + R < ng;
-            const int labA = (int)lds_u32(lab_b + 4u * (uint32_t)rA);
-            const int labB = hasB ? (int)lds_u32(lab_b + 4u * (uint32_t)rB) : -1;
-            const uint32_t xA = xs + (uint32_t)(rA >> 4) * cstride + (uint32_t)(rA & 15) * row_bytes;
-            const uint32_t xB = xs + (uint32_t)(rB >> 4) * cstride + (uint32_t)(rB & 15) * row_bytes;
-            const bool doA = act && labA >= 0, doB = act && labB >= 0;
-            const uint32_t aA = my_acc + (uint32_t)(doA ? labA : 0) * acc_row, aB = my_acc + (uint32_t)(doB ? labB : 0) * acc_row;
-            const bool clash = __any_sync(0xffffffffu, doA && doB && labA == labB);
-            if constexpr (RVEC == 1) {
-              double vA = 0, vB = 0;
-              if (doA) vA = lds_f64(xA);
-              if (doB) vB = lds_f64(xB);
-              if (!clash) {
-                double sA = 0, sB = 0;
-                if (doA) sA = lds_f64(aA);
-                if (doB) sB = lds_f64(aB);
-                if (doA) sts_f64(aA, sA + vA);
-                if (doB) sts_f64(aB, sB + vB);
-              } else {
-                if (doA) sts_f64(aA, lds_f64(aA) + vA);
-                if (doB) sts_f64(aB, lds_f64(aB) + vB);
-              }
-            } else {
-              double vA0 = 0, vA1 = 0, vB0 = 0, vB1 = 0;
-              if (doA) lds_v2f64(xA, vA0, vA1);
-              if (doB) lds_v2f64(xB, vB0, vB1);
-              if (!clash) {
-                double sA0 = 0, sA1 = 0, sB0 = 0, sB1 = 0;
-                if (doA) lds_v2f64(aA, sA0, sA1);
-                if (doB) lds_v2f64(aB, sB0, sB1);
-                if (doA) sts_v2f64(aA, sA0 + vA0, sA1 + vA1);
-                if (doB) sts_v2f64(aB, sB0 + vB0, sB1 + vB1);
-              } else {
-                if (doA) { double t0, t1; lds_v2f64(aA, t0, t1); sts_v2f64(aA, t0 + vA0, t1 + vA1); }
-                if (doB) { double t0, t1; lds_v2f64(aB, t0, t1); sts_v2f64(aB, t0 + vB0, t1 + vB1); }
+#pragma unroll 1
+          for (int gq = 0; gq < kTileRows / 32; ++gq) {
+            const int lab = (int)lds_u32(lab_b + 4u * (uint32_t)(gq * 32 + lane));
+            const uint32_t xg = xs + (uint32_t)(2 * gq) * cstride;       // rows 32 gq .. 32 gq + 31 = chunks 2 gq, 2 gq + 1
+            if (__ballot_sync(0xffffffffu, (lab & (R - 1)) == ridx) == 0u) continue;
+#pragma unroll
+            for (int m = 0; m < NM; ++m) {
+              unsigned mask = __ballot_sync(0xffffffffu, lab == ridx + R * m);
+              while (mask) {
+                const int q = __ffs(mask) - 1; mask &= mask - 1;
+                const uint32_t xa = xg + (uint32_t)(q >> 4) * cstride + (uint32_t)(q & 15) * row_bytes;
+                if (act) {
+                  if (RVEC2 == 2) { double v0, v1; lds_v2f64(xa, v0, v1); racc[m * RVEC2] += v0; racc[m * RVEC2 + RVEC2 - 1] += v1; }
+                  else racc[m] += lds_f64(xa);
+                }
               }
             }
           }
@@ -556,36 +598,47 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
           if (lane == 0) mbar_arrive_a(b_sempty + 8u * (uint32_t)s);
           if (++s == S) { s = 0; sph ^= 1u; }
         }
+        // every cluster has exactly one owner: its registers go straight to the CTA's slot
+#pragma unroll
+        for (int m = 0; m < NM; ++m) {
+          const int j = ridx + R * m;
+#pragma unroll
+          for (int e = 0; e < RVEC2; ++e)
+            if (j < k && f + e < d) { const double v = racc[m * RVEC2 + e]; out[(size_t)j * d + f + e] = v; cost = fma(v, p.C[(size_t)j * d + f + e], cost); }
+        }
       } else {
-        // one shared set: warp r owns the clusters j = r mod R; lane = feature pair; rows in tile order, two per step
-        const bool act = 2 * lane < d;
-        const uint32_t my_acc = a_acc + (uint32_t)lane * 16u;      // accumulator row j at j * 512 bytes
+        // private sets in shared memory: this warp's rows are the groups gi = ridx, ridx + R, ... of R_G consecutive rows;
+        // sub-row `sub` of a group accumulates into set ridx * R_G + sub, so no two lanes ever meet on an address
+        constexpr int RVEC = RMODE == 0 ? 1 : 2;
+        constexpr int R_LPR = tp_lanes_per_row(ND, RVEC), R_G = 32 / R_LPR, NG = kTileRows / R_G;
+        const int sub = lane / R_LPR, f = (lane % R_LPR) * RVEC;
+        const bool act = f < d;
+        const uint32_t acc_row = (uint32_t)L.ald * 8u;
+        const uint32_t my_acc = a_acc + (uint32_t)(ridx * R_G + sub) * (uint32_t)KP * acc_row + (uint32_t)f * 8u;
         for (int i = 0; i < T; ++i) {
           tp_wait_p(b_lfull + 8u * (uint32_t)s, sph, 6, prof, pw0);
-          const uint32_t xs = a_x + (uint32_t)s * sbytes + (uint32_t)lane * 16u, lab_b = a_lab + (uint32_t)s * (kTileRows * 4);
-#pragma unroll 1
-          for (int gq = 0; gq < kTileRows / 32; ++gq) {
-            const int lab = (int)lds_u32(lab_b + 4u * (uint32_t)(gq * 32 + lane));
-            unsigned mask = __ballot_sync(0xffffffffu, lab >= 0 && (lab & (R - 1)) == ridx);
-            while (mask) {
-              const int q0 = __ffs(mask) - 1; mask &= mask - 1;
-              bool two = mask != 0;
-              const int q1 = two ? __ffs(mask) - 1 : q0; mask &= mask - 1;
-              const int l0 = __shfl_sync(0xffffffffu, lab, q0), l1 = __shfl_sync(0xffffffffu, lab, q1);
-              const int t0 = gq * 32 + q0, t1 = gq * 32 + q1;
-              double v00 = 0, v01 = 0, v10 = 0, v11 = 0;
-              if (act) {
-                lds_v2f64(xs + (uint32_t)(t0 >> 4) * cstride + (uint32_t)(t0 & 15) * row_bytes, v00, v01);
-                if (two) lds_v2f64(xs + (uint32_t)(t1 >> 4) * cstride + (uint32_t)(t1 & 15) * row_bytes, v10, v11);
-              }
-              if (two && l1 == l0) { v00 += v10; v01 += v11; two = false; }
-              const uint32_t aa0 = my_acc + (uint32_t)l0 * 512u, aa1 = my_acc + (uint32_t)l1 * 512u;
-              if (act) {
-                double s00, s01, s10 = 0, s11 = 0;
-                lds_v2f64(aa0, s00, s01);
-                if (two) lds_v2f64(aa1, s10, s11);
-                sts_v2f64(aa0, s00 + v00, s01 + v01);
-                if (two) sts_v2f64(aa1, s10 + v10, s11 + v11);
+          const uint32_t xs = a_x + (uint32_t)s * sbytes + (uint32_t)f * 8u, lab_b = a_lab + (uint32_t)s * (kTileRows * 4);
+          if (act) {
+#pragma unroll
+            for (int gi0 = 0; gi0 < NG; gi0 += 2 * R) {
+              // two groups in flight; if a sub-row meets the same accumulator row in both, the second carries the sum
+              const int rA = (gi0 + ridx) * R_G + sub, rB = (gi0 + R + ridx) * R_G + sub;
+              const int labA = (int)lds_u32(lab_b + 4u * (uint32_t)rA), labB = (int)lds_u32(lab_b + 4u * (uint32_t)rB);
+              const uint32_t xA = xs + (uint32_t)(rA >> 4) * cstride + (uint32_t)(rA & 15) * row_bytes;
+              const uint32_t xB = xs + (uint32_t)(rB >> 4) * cstride + (uint32_t)(rB & 15) * row_bytes;
+              const uint32_t aA = my_acc + (uint32_t)labA * acc_row, aB = my_acc + (uint32_t)labB * acc_row;
+              const bool same = labA == labB;
+              if constexpr (RVEC == 1) {
+                const double vA = lds_f64(xA), vB = lds_f64(xB);
+                const double sA = lds_f64(aA), sB = lds_f64(aB);
+                if (!same) sts_f64(aA, sA + vA);
+                sts_f64(aB, sB + (same ? vA + vB : vB));
+              } else {
+                double vA0, vA1, vB0, vB1, sA0, sA1, sB0, sB1;
+                lds_v2f64(xA, vA0, vA1); lds_v2f64(xB, vB0, vB1);
+                lds_v2f64(aA, sA0, sA1); lds_v2f64(aB, sB0, sB1);
+                if (!same) sts_v2f64(aA, sA0 + vA0, sA1 + vA1);
+                sts_v2f64(aB, sB0 + (same ? vA0 + vB0 : vB0), sB1 + (same ? vA1 + vB1 : vB1));
               }
             }
           }
@@ -600,7 +653,7 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
   if (prof && lane == 0) {
     unsigned long long* o = L.prof + warp * 8;
     o[0] = (unsigned long long)(clock64() - pt0); o[1] = (unsigned long long)pw0; o[2] = (unsigned long long)pw1; o[3] = (unsigned long long)pw2;
-    o[4] = (unsigned long long)pw3; o[5] = (unsigned long long)pcnt; o[6] = (unsigned long long)T; o[7] = 0ull;
+    o[4] = 0ull; o[5] = (unsigned long long)pcnt; o[6] = (unsigned long long)T; o[7] = 0ull;
   }
   // ===================================================================== CTA-level combine (all warps)
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -608,21 +661,31 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
   if (warp == kTpProdWarp) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(TCOLS) : "memory");
   if (!p.do_reduce) return;
 
-  const int P = k * d + k + 1;
-  const int SL = P + 1 + k;
-  double* out = p.cta_partials + (size_t)blockIdx.x * SL;
-  const double* acc0 = reinterpret_cast<const double*>(smem + L.acc_off);
-  {
+  if constexpr (RMODE == 3) {
+    const double* slab = reinterpret_cast<const double*>(smem + L.x_off);
+    constexpr int LDS_ = 8 * ND;
+    for (int i = tid; i < k * d; i += kTpThreads) {
+      const int j = i / d, f = i - j * d;
+      double sacc = 0;
+#pragma unroll
+      for (int w = 0; w < R; ++w) sacc += slab[(size_t)w * KP * LDS_ + j * LDS_ + f];
+      out[i] = sacc;
+      cost = fma(sacc, p.C[i], cost);                           // sum_j S_j . c_j
+    }
+  } else if constexpr (RMODE == 2) {
+    // written by the owners above
+  } else {
+    const double* acc0 = reinterpret_cast<const double*>(smem + L.acc_off);
     const int ald = L.ald, setn = KP * L.ald, nsets = L.nsets;
     for (int i = tid; i < k * d; i += kTpThreads) {
       const int j = i / d, f = i - j * d;
       double sacc = 0;
       for (int w = 0; w < nsets; ++w) sacc += acc0[w * setn + j * ald + f];
       out[i] = sacc;
-      cost = fma(sacc, p.C[i], cost);                           // sum_j S_j . c_j
+      cost = fma(sacc, p.C[i], cost);
     }
-    if (tid < k) { const double nj = (double)cnt_s[tid]; out[(size_t)k * d + tid] = nj; cost = fma(nj, cn_s[tid], cost); }
   }
+  if (tid < k) { const double nj = (double)cnt_s[tid]; out[(size_t)k * d + tid] = nj; cost = fma(nj, cn_s[tid], cost); }
 #pragma unroll
   for (int msk = 16; msk >= 1; msk >>= 1) { cost += shfl_xor_d(cost, msk); xxs += shfl_xor_d(xxs, msk); }
   if (lane == 0) { red_s[warp] = cost; red_s[kTpWarps + warp] = xxs; }
@@ -662,7 +725,7 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
       __syncthreads();
       peer_ok = peer_allreduce(p, p.partial_out, P, tid, kTpThreads, [] { __syncthreads(); });
     }
-    if (p.C_update != nullptr && peer_ok) {                                 // fused driver step
+    if (p.C_update != nullptr && peer_ok) {                      // fused driver step
       __threadfence_block();
       __syncthreads();
       update_centers_body(p.partial_out, k, d, p.C_update, p.tol2, p.state_rw, red_s + 2 * kTpWarps, tid);

@@ -26,7 +26,7 @@ def _mods():
     return np, torch, N, O
 
 
-def one(n, d, k, seed=0):
+def one(n, d, k, seed=0, tpv=4):
     np, torch, N, O = _mods()
     rng = np.random.default_rng(seed + n + 31 * d + 977 * k)
     prof = rng.normal(size=(k, d)) * 1.5
@@ -36,7 +36,7 @@ def one(n, d, k, seed=0):
     P = k * d + k + 1
     scratch = N.new_scratch(d, k, "cuda")
     res = {}
-    for variant in (5, 4):
+    for variant in (5, tpv):
         N.set_lloyd_variant(variant)
         partial = torch.full((P,), -7.0, dtype=torch.float64, device="cuda")
         labels = torch.full((n,), -9, dtype=torch.int32, device="cuda")
@@ -47,7 +47,7 @@ def one(n, d, k, seed=0):
         N.assign_reduce(X, C, p2, scratch=scratch, xnorm2_sum=xs, xnorm2_mode=2)                  # REUSE
         N.assign_reduce(X, C, None, lab2, do_reduce=False)                                        # predict
         torch.cuda.synchronize()
-        res[variant] = (partial.cpu().numpy(), labels.cpu().numpy(), p1.cpu().numpy(), p2.cpu().numpy(), lab2.cpu().numpy(), xs.item())
+        res[4 if variant == tpv else 5] = (partial.cpu().numpy(), labels.cpu().numpy(), p1.cpu().numpy(), p2.cpu().numpy(), lab2.cpu().numpy(), xs.item())
     N.set_lloyd_variant(0)
     sums, wsum, cost, lab = O.lloyd_pass(Xh, Ch, P=1, want_labels=True)
     p, labels, p1, p2, lab2, xs = res[4]
@@ -59,12 +59,12 @@ def one(n, d, k, seed=0):
     same_modes = bool(np.array_equal(p, p1) and np.array_equal(p[:-1], p2[:-1]) and np.array_equal(labels, lab2))
     xs_ok = abs(xs - float((Xh * Xh).sum())) <= 1e-12 * float((Xh * Xh).sum())
     ok = agree == 1.0 and es < 1e-11 and ew == 0 and ec < 1e-9 and ec2 < 1e-9 and same_modes and xs_ok
-    print(json.dumps(dict(n=n, d=d, k=k, agree=agree, agree_round1=agree_old, sums_rel=es, wsum_abs=ew, cost_rel=[ec, ec2], same_modes=same_modes,
+    print(json.dumps(dict(n=n, d=d, k=k, v=tpv, agree=agree, agree_round1=agree_old, sums_rel=es, wsum_abs=ew, cost_rel=[ec, ec2], same_modes=same_modes,
                           xs_ok=bool(xs_ok), cost_vs_round1=abs(p[-1] - po[-1]) / max(po[-1], 1e-300), ok=bool(ok))), flush=True)
     return ok
 
 
-def bench(shapes, iters=10):
+def bench(shapes, iters=10, extra=()):
     np, torch, N, O = _mods()
     peak = 6554.6
     try:
@@ -79,7 +79,7 @@ def bench(shapes, iters=10):
         partial = torch.empty(k * d + k + 1, dtype=torch.float64, device="cuda"); scratch = N.new_scratch(d, k, "cuda")
         xs = torch.zeros(1, dtype=torch.float64, device="cuda")
         row = dict(n=n, d=d, k=k)
-        for variant, name in ((5, "round1"), (4, "tp")):
+        for variant, name in ((5, "round1"), (4, "tp")) + tuple(extra):
             N.set_lloyd_variant(variant)
             try:
                 for _ in range(3):
@@ -154,12 +154,16 @@ if __name__ == "__main__":
         prof([(20_000_000, 16, 16), (5_000_000, 24, 32), (20_000_000, 64, 64), (5_000_000, 24, 64)])
         sys.exit(0)
     if cmd == "one":
-        sys.exit(0 if one(int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4])) else 1)
+        sys.exit(0 if one(int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]), tpv=int(sys.argv[5]) if len(sys.argv) > 5 else 4) else 1)
     if cmd == "check":
         bad = 0
-        for n, d, k in CHECK_SHAPES:
+        # default scheme for every shape, then the other reduce schemes pinned (42 register-owned, 40/41 private sets) on a subset
+        cases = [(n, d, k, 4) for n, d, k in CHECK_SHAPES]
+        cases += [(n, d, k, 42) for n, d, k in CHECK_SHAPES if k <= 16 and (d <= 32 or d % 2 == 0)]
+        cases += [(n, d, k, 40 if d <= 32 else 41) for n, d, k in CHECK_SHAPES[::2] if (d <= 32 or d % 2 == 0) and not (d > 32 and k > 32)]
+        for n, d, k, v in cases:
             try:
-                r = subprocess.run([sys.executable, __file__, "one", str(n), str(d), str(k)], capture_output=True, text=True, timeout=180)
+                r = subprocess.run([sys.executable, __file__, "one", str(n), str(d), str(k), str(v)], capture_output=True, text=True, timeout=180)
                 out = (r.stdout.strip().splitlines() or ["(no output)"])[-1]
                 if r.returncode != 0:
                     bad += 1
@@ -167,8 +171,11 @@ if __name__ == "__main__":
                 print(out, flush=True)
             except subprocess.TimeoutExpired:
                 bad += 1
-                print(json.dumps(dict(n=n, d=d, k=k, timeout=True)), flush=True)
+                print(json.dumps(dict(n=n, d=d, k=k, v=v, timeout=True)), flush=True)
         print("ALL OK" if bad == 0 else f"FAILED {bad}")
         sys.exit(0 if bad == 0 else 1)
     if cmd == "bench":
-        bench(BENCH_SHAPES + (WIDE if "wide" in sys.argv else []))
+        extra = []
+        if "modes" in sys.argv:
+            extra = [(42, "tp_own"), (40, "tp_priv0"), (41, "tp_priv1")]
+        bench(BENCH_SHAPES + (WIDE if "wide" in sys.argv else []), extra=extra)
