@@ -139,7 +139,7 @@ int hkm_version(void) { return 100; }
 int hkm_max_k(void) { return 64; }
 int hkm_max_d(void) { return 96; }
 int hkm_set_lloyd_variant(int variant) {
-  if (!((variant >= 0 && variant <= 5) || (variant >= 40 && variant <= 43))) { set_error("hkm_set_lloyd_variant: 0..5 (40..43: variant 4 with a pinned reduce scheme)"); return HKM_ERR_INVALID; }
+  if (!((variant >= 0 && variant <= 5) || (variant == 40 || variant == 42 || variant == 43))) { set_error("hkm_set_lloyd_variant: 0..5 (40..43: variant 4 with a pinned reduce scheme)"); return HKM_ERR_INVALID; }
   g_lloyd_variant = variant;
   return HKM_OK;
 }

@@ -13,7 +13,7 @@ int dispatch_lloyd_tp64(const LloydParams&, const TpPlan&, cudaStream_t);
 // Plain passes (unit weights, labels and/or sums, no per-row distances) with 8 < k <= 64 and d <= 64 (odd d only up to 32).
 bool lloyd_tp_eligible(const LloydParams& p, int mode) {
   const int variant = lloyd_variant_override();
-  if (variant != 0 && variant != 4 && !(variant >= 40 && variant <= 43)) return false;
+  if (variant != 0 && variant != 4 && !(variant == 40 || variant == 42 || variant == 43)) return false;
   if (mode != 0 || p.w != nullptr || p.out_mode != 0 || p.mind2_out != nullptr || p.do_reduce > 1) return false;
   if (p.k > 64 || p.d > 64 || ((p.d & 1) && p.d > 32)) return false;
   if (p.k <= 8 && variant == 0) return false;               // k <= 8 stays on the fp64 tensor-pipe kernel (HBM-bound already)

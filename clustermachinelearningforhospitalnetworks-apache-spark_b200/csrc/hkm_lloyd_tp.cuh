@@ -39,37 +39,38 @@
 
 namespace hkm {
 
-constexpr int kTpWarps = 18;
-constexpr int kTpThreads = kTpWarps * 32;
-constexpr int kTpConvWarps = 4;
-constexpr int kTpConvWarp0 = 12, kTpProdWarp = 16, kTpMmaWarp = 17;
-__host__ __device__ constexpr int tp_reduce_warps(int sg) { return 12 - 4 * sg; }   // screen groups of four warps + reduce warps = 12
+// warp budgets (WCFG): 0 = 1 screen group + 8 reduce + 4 convert (18 warps), 1 = 2 + 8 + 8 (26 warps, thin rows: every role is
+// latency bound, so more warps per role), 2 = 2 + 4 + 4 (18 warps, k > 32 with private sets); + producer + MMA issuer
+constexpr int kTpMaxWarps = 26;
+__host__ __device__ constexpr int tp_sg(int wcfg) { return wcfg == 0 ? 1 : 2; }
+__host__ __device__ constexpr int tp_reduce_warps(int wcfg) { return wcfg == 2 ? 4 : 8; }
+__host__ __device__ constexpr int tp_conv_warps(int wcfg) { return wcfg == 1 ? 8 : 4; }
+__host__ __device__ constexpr int tp_warps(int wcfg) { return 4 * tp_sg(wcfg) + tp_reduce_warps(wcfg) + tp_conv_warps(wcfg) + 2; }
 __host__ __device__ constexpr int tp_tmem_stride(int kp) { return kp <= 32 ? 32 : (kp <= 64 ? 64 : (kp <= 128 ? 128 : 256)); }
 // feature-count class of ND = ceil(d / 8): rows are handled as if they had 8, 16, 32 or 64 features
 __host__ __device__ constexpr int tp_dclass(int nd) { return nd <= 1 ? 8 : (nd <= 2 ? 16 : (nd <= 4 ? 32 : 64)); }
 __host__ __device__ constexpr int tp_lanes_per_row(int nd, int vec) { return tp_dclass(nd) / vec < 4 ? 4 : (tp_dclass(nd) / vec > 32 ? 32 : tp_dclass(nd) / vec); }
 
-// reduce modes: 0 private sets in shared memory, lane = feature (d <= 32); 1 the same, lane = feature pair (even d <= 64);
-//               2 clusters owned per warp, accumulators in registers; 3 one-hot DMMA (k <= 16), accumulators in registers
+// reduce modes: 0 private sets in shared memory, lane = feature (d <= 32); 2 one shared set, clusters owned per warp, lane =
+//               feature pair (even d <= 64); 3 one-hot DMMA (k <= 16), accumulators in registers
 struct TpPlan {
-  int stages, rmode, na, sg, nd;   // ring depth, reduce mode, tf32 operand buffers (1 or 2), screen groups (1 or 2), ceil(d/8)
+  int stages, rmode, na, wcfg, nd;   // ring depth, reduce mode, tf32 operand buffers (1 or 2), warp budget, ceil(d/8)
   int ald, nsets;                  // rmode 0/1: accumulator row (doubles), sets
   int kchunks, lbo_a, lbo_b, a_bytes;
   int x_off, a_off, b_off, acc_off, cn_off, mu_off, cnt_off, lab_off, red_off, bar_off, tmem_off, total;
   unsigned long long* prof;   // developer profile (tools/tp_check.py prof): [warp][8] cycle counters of CTA 0, or null
 };
 
-__host__ __device__ inline TpPlan tp_plan(int d, int kp, int stages, int rmode, int na, int sg) {
+__host__ __device__ inline TpPlan tp_plan(int d, int kp, int stages, int rmode, int na, int wcfg) {
   TpPlan L{};
-  L.stages = stages; L.rmode = rmode; L.na = na; L.sg = sg; L.nd = (d + 7) / 8;
+  L.stages = stages; L.rmode = rmode; L.na = na; L.wcfg = wcfg; L.nd = (d + 7) / 8;
   const int cvec = (d & 1) ? 1 : 2;
   const int c_g = 32 / tp_lanes_per_row(L.nd, cvec);
-  const int R = tp_reduce_warps(sg);
-  if (rmode <= 1) {
-    const int rvec = rmode == 0 ? 1 : 2;
-    const int rl = tp_lanes_per_row(L.nd, rvec);
-    L.ald = rl * rvec; L.nsets = R * (32 / rl);
-  }
+  const int R = tp_reduce_warps(wcfg);
+  if (rmode == 0) {
+    const int rl = tp_lanes_per_row(L.nd, 1);
+    L.ald = rl; L.nsets = R * (32 / rl);
+  } else if (rmode == 2) { L.ald = 64; L.nsets = 1; }
   const int d8 = (d + 7) & ~7;
   L.kchunks = (d8 + 8) / 4;
   const int pad_a = 8 * c_g > 16 ? 8 * c_g : 16;
@@ -85,42 +86,35 @@ __host__ __device__ inline TpPlan tp_plan(int d, int kp, int stages, int rmode, 
   L.mu_off = o; o += (d8 + 8) * 8;
   L.cnt_off = o; o += kp * 4;
   L.lab_off = o; o += (stages > 0 ? stages : 2) * kTileRows * 4;
-  L.red_off = o; o += (2 * kTpWarps + 64) * 8;
+  L.red_off = o; o += (2 * kTpMaxWarps + 64) * 8;
   L.bar_off = o; o += (3 * kMaxStages + 8) * 8;
   L.tmem_off = o; o += 16;
   L.total = o;
   return L;
 }
 
-// Picks reduce mode, operand buffering, screen groups and ring depth for a shape; stages < 2 => the shape does not fit.
+// Picks reduce mode, warp budget, operand buffering and ring depth for a shape; stages < 2 => the shape does not fit.
 // force_rmode >= 0 pins the reduce mode (tuning).
 __host__ inline TpPlan tp_choose(int d, int kp, int force_rmode = -1) {
   const int budget = 227 * 1024 - 1024;
+  const int nd = (d + 7) / 8;
+  // candidates in order of preference: (reduce mode, warp budget)
+  int cand[8][2]; int nc = 0;
+  auto add = [&](int rm, int w) { cand[nc][0] = rm; cand[nc][1] = w; ++nc; };
+  if (kp == 16 && (force_rmode < 0 || force_rmode == 3)) add(3, nd <= 4 ? 1 : 0);
+  if (d <= 32 && (force_rmode < 0 || force_rmode == 0)) { add(0, 1); if (kp >= 48) add(0, 2); add(0, 0); }
+  if (!(d & 1) && (force_rmode < 0 || force_rmode == 2)) add(2, 0);
   TpPlan best{}; best.stages = 0;
-  const int sg_pref = kp >= 48 ? 2 : 1;
-  for (int si = 0; si < 2; ++si) {
-    const int sg = si == 0 ? sg_pref : 3 - sg_pref;
-    if (sg == 2 && kp < 48) continue;
-    // order of preference: DMMA reduce for k <= 16; else register-owned clusters; private shared-memory sets on request
-    int modes[3]; int nm = 0;
-    if (force_rmode >= 0) modes[nm++] = force_rmode;
-    else { if (kp == 16) modes[nm++] = 3; modes[nm++] = 2; }
-    for (int mi = 0; mi < nm; ++mi) {
-      const int rm = modes[mi];
-      if (rm == 3 && (kp != 16 || sg != 1)) continue;
-      if (rm == 0 && d > 32) continue;
-      if (rm == 1 && ((d & 1) || d <= 32)) continue;
-      if (rm == 2 && (d & 1) && d > 32) continue;
-      for (int na = 2; na >= 1; --na) {
-        const int fixed = tp_plan(d, kp, 2, rm, na, sg).total - 2 * stage_bytes(d) - 2 * kTileRows * 4;
-        int st = (budget - fixed) / (stage_bytes(d) + kTileRows * 4);
-        if (st > kMaxStages) st = kMaxStages;
-        if (st < 2) continue;
-        if (st >= 3) return tp_plan(d, kp, st, rm, na, sg);
-        if (st > best.stages) best = tp_plan(d, kp, st, rm, na, sg);
-      }
+  for (int ci = 0; ci < nc; ++ci)
+    for (int na = 2; na >= 1; --na) {
+      const int rm = cand[ci][0], w = cand[ci][1];
+      const int fixed = tp_plan(d, kp, 2, rm, na, w).total - 2 * stage_bytes(d) - 2 * kTileRows * 4;
+      int st = (budget - fixed) / (stage_bytes(d) + kTileRows * 4);
+      if (st > kMaxStages) st = kMaxStages;
+      if (st < 2) continue;
+      if (st >= 3) return tp_plan(d, kp, st, rm, na, w);
+      if (st > best.stages) best = tp_plan(d, kp, st, rm, na, w);
     }
-  }
   return best;
 }
 
@@ -165,18 +159,21 @@ __device__ __forceinline__ void mbar_arrive_a(uint32_t bar) { asm volatile("mbar
 __device__ __forceinline__ void lds_v2f64(uint32_t a, double& x, double& y) { asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(x), "=d"(y) : "r"(a)); }
 __device__ __forceinline__ void sts_v2f64(uint32_t a, double x, double y) { asm volatile("st.shared.v2.f64 [%0], {%1,%2};" ::"r"(a), "d"(x), "d"(y) : "memory"); }
 
-// KP = padded cluster count (16, 32, 48, 64); CVEC = 2 (even d) or 1; RMODE as in TpPlan; SG = screen groups; ND = ceil(d/8).
-template <int KP, int CVEC, int RMODE, int SG, int ND>
-__global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydParams p, const TpPlan L) {
+// KP = padded cluster count (16, 32, 48, 64); CVEC = 2 (even d) or 1; RMODE as in TpPlan; WCFG = warp budget; ND = ceil(d/8).
+template <int KP, int CVEC, int RMODE, int WCFG, int ND>
+__global__ void __launch_bounds__(tp_warps(WCFG) * 32, 1) lloyd_tp_kernel(const LloydParams p, const TpPlan L) {
   if (p.skip != nullptr && *p.skip != 0) return;
-  constexpr int R = tp_reduce_warps(SG);
+  constexpr int SG = tp_sg(WCFG), R = tp_reduce_warps(WCFG), CW = tp_conv_warps(WCFG);
+  constexpr int kTpWarps = tp_warps(WCFG), kTpThreads = kTpWarps * 32;
+  constexpr int kTpConvWarp0 = 4 * SG + R, kTpProdWarp = kTpConvWarp0 + CW, kTpMmaWarp = kTpProdWarp + 1;
   constexpr int NW = (KP + 31) / 32;              // candidate mask words
   constexpr int TSTRIDE = tp_tmem_stride(KP);
   constexpr int TCOLS = 2 * TSTRIDE;
   constexpr int IDXBITS = 6;
   constexpr uint32_t IDXMASK = (1u << IDXBITS) - 1u;
   static_assert(KP % 16 == 0 && KP >= 16 && KP <= 64, "k_pad: 16..64 in steps of 16");
-  static_assert(RMODE != 3 || (KP == 16 && SG == 1), "one-hot DMMA reduce: k <= 16, eight reduce warps");
+  static_assert(RMODE != 3 || (KP == 16 && R == 8), "one-hot DMMA reduce: k <= 16, eight reduce warps");
+  static_assert(RMODE == 0 || RMODE == 2 || RMODE == 3, "reduce mode");
 
   extern __shared__ __align__(1024) unsigned char smem[];
   const int d = p.d, k = p.k;
@@ -218,7 +215,7 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
       mbar_init(bars + 2 * kMaxStages + s, 4);
     }
     for (int b = 0; b < 2; ++b) {
-      mbar_init(bars + 3 * kMaxStages + b, kTpConvWarps);      // afull
+      mbar_init(bars + 3 * kMaxStages + b, CW);                // afull
       mbar_init(bars + 3 * kMaxStages + 2 + b, 4);             // aempty
       mbar_init(bars + 3 * kMaxStages + 4 + b, 1);             // tfull
       mbar_init(bars + 3 * kMaxStages + 6 + b, 4);             // tempty
@@ -235,7 +232,7 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
   for (int i = tid; i < KP; i += kTpThreads) cnt_s[i] = 0u;
   if (tid < d8 + 8) { double s = 0; if (tid < d) for (int j = 0; j < k; ++j) s += p.C[(size_t)j * d + tid]; mu_s[tid] = tid < d ? s / k : 0.0; }   // mu = mean of the centres
   __syncthreads();
-  double* h_s = red_s + 2 * kTpWarps;   // [KP] |c - mu|^2, later the centre-update scratch
+  double* h_s = red_s + 2 * kTpMaxWarps;   // [KP] |c - mu|^2, later the centre-update scratch
   if (tid < KP) {
     double s = 0, sc = 0;
     if (tid < k) for (int f = 0; f < d; ++f) { const double c = p.C[(size_t)tid * d + f], cc = c - mu_s[f]; s = fma(c, c, s); sc = fma(cc, cc, sc); }
@@ -278,8 +275,6 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
   const uint32_t tmem = *reinterpret_cast<const uint32_t*>(smem + L.tmem_off);
 
   double cost = 0, xxs = 0;
-  constexpr int RVEC2 = ND > 4 ? 2 : 1;                        // RMODE 2: lane = feature (d <= 32) or feature pair
-  constexpr int NM = KP / R;                                   // RMODE 2: clusters owned per warp
   const int P = k * d + k + 1;
   const int SL = P + 1 + k;
   double* out = p.cta_partials + (size_t)blockIdx.x * SL;       // this CTA's slot of the scratch
@@ -340,7 +335,8 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
     }
   } else if (warp >= kTpConvWarp0) {
     // ===================================================================== converters
-    // lane = (row of the group, feature pair); a warp converts chunks cw and cw + 4, C_G rows per instruction
+    // lane = (row of the group, feature pair); a warp converts chunks cw, cw + CW, ..., C_G rows per instruction.  The fp32
+    // values are stored as they are: the tensor core reads their top 19 bits (tf32), the bound below allows for that
     constexpr int C_LPR = tp_lanes_per_row(ND, CVEC), C_G = 32 / C_LPR, NIT = kChunkRows / C_G;
     const int cw = warp - kTpConvWarp0;
     const int subc = lane / C_LPR, fc = (lane % C_LPR) * CVEC;
@@ -358,11 +354,11 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
       const uint32_t xs = a_x + (uint32_t)s * sbytes, ab = a_A + b * (uint32_t)L.a_bytes;
       if (act) {
 #pragma unroll
-        for (int cq = 0; cq < kChunks / kTpConvWarps; ++cq) {
-          const int cc = cw + cq * kTpConvWarps;
+        for (int cq = 0; cq < kChunks / CW; ++cq) {
+          const int cc = cw + cq * CW;
           const uint32_t src0 = xs + (uint32_t)cc * cstride + src_lane;
           const uint32_t dst0 = ab + (uint32_t)cc * 256u + dst_lane;
-          constexpr int NB = NIT > 8 ? 8 : NIT;              // rows in flight per lane (register budget)
+          constexpr int NB = NIT > 4 ? 4 : NIT;              // rows in flight per lane (register budget)
 #pragma unroll
           for (int it0 = 0; it0 < NIT; it0 += NB) {
             double v0[NB], v1[NB];
@@ -377,9 +373,9 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
             }
 #pragma unroll
             for (int it = 0; it < NB; ++it) {
-              const uint32_t t0 = f32_to_tf32_rn((float)(v0[it] - mu0));
+              const uint32_t t0 = __float_as_uint((float)(v0[it] - mu0));
               if (CVEC == 2) {
-                const uint32_t t1 = f32_to_tf32_rn((float)(v1[it] - mu1));
+                const uint32_t t1 = __float_as_uint((float)(v1[it] - mu1));
                 asm volatile("st.shared.v2.u32 [%0], {%1,%2};" ::"r"(dst0 + (uint32_t)((it0 + it) * C_G * 16)), "r"(t0), "r"(t1) : "memory");
               } else sts_u32(dst0 + (uint32_t)((it0 + it) * C_G * 16), t0);
             }
@@ -396,7 +392,7 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
     const int grp = warp >> 2, wsub = warp & 3;
     const int row = 32 * wsub + lane;                              // tile row of this thread = TMEM lane
     const uint32_t tlane = ((uint32_t)(32 * wsub)) << 16;
-    const float kapv = 1.04f * 0.0009765625f * vmax;               // kappa * max|c - mu|
+    const float kapv = 1.6f * 0.0009765625f * vmax;                // kappa * max|c - mu|
     const float etab = 0.5f * 1.52587890625e-05f * vmax * vmax;    // eta * max 0.5|c - mu|^2, eta = 2^-16
     constexpr int DCH = 2 * ND;                                    // 16-byte chunks of the converted row
     const bool conv2 = (d & 1) == 0;
@@ -567,30 +563,33 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
             }
         }
       } else if constexpr (RMODE == 2) {
-        // warp r owns the clusters r + R m; accumulators in registers; rows found by ballot, in tile order
-        const int f = lane * RVEC2;
-        const bool act = f < d;
-        double racc[NM * RVEC2];
-#pragma unroll
-        for (int q = 0; q < NM * RVEC2; ++q) racc[q] = 0.0;
+        // one shared set (row j at j * 512 bytes): warp r owns the clusters j = r mod R, lane = feature pair; its rows come from
+        // one ballot per 32 rows, two rows in flight -- when both carry the same label the second one stores the sum of both
+        const bool act = 2 * lane < d;
+        const uint32_t my_acc = a_acc + (uint32_t)lane * 16u;
         for (int i = 0; i < T; ++i) {
           tp_wait_p(b_lfull + 8u * (uint32_t)s, sph, 6, prof, pw0);
-          const uint32_t xs = a_x + (uint32_t)s * sbytes + (uint32_t)f * 8u, lab_b = a_lab + (uint32_t)s * (kTileRows * 4);
+          const uint32_t xs = a_x + (uint32_t)s * sbytes + (uint32_t)lane * 16u, lab_b = a_lab + (uint32_t)s * (kTileRows * 4);
 #pragma unroll 1
           for (int gq = 0; gq < kTileRows / 32; ++gq) {
             const int lab = (int)lds_u32(lab_b + 4u * (uint32_t)(gq * 32 + lane));
+            unsigned mask = __ballot_sync(0xffffffffu, (lab & (R - 1)) == ridx);
             const uint32_t xg = xs + (uint32_t)(2 * gq) * cstride;       // rows 32 gq .. 32 gq + 31 = chunks 2 gq, 2 gq + 1
-            if (__ballot_sync(0xffffffffu, (lab & (R - 1)) == ridx) == 0u) continue;
-#pragma unroll
-            for (int m = 0; m < NM; ++m) {
-              unsigned mask = __ballot_sync(0xffffffffu, lab == ridx + R * m);
-              while (mask) {
-                const int q = __ffs(mask) - 1; mask &= mask - 1;
-                const uint32_t xa = xg + (uint32_t)(q >> 4) * cstride + (uint32_t)(q & 15) * row_bytes;
-                if (act) {
-                  if (RVEC2 == 2) { double v0, v1; lds_v2f64(xa, v0, v1); racc[m * RVEC2] += v0; racc[m * RVEC2 + RVEC2 - 1] += v1; }
-                  else racc[m] += lds_f64(xa);
-                }
+            while (mask) {
+              const int q0 = __ffs(mask) - 1; mask &= mask - 1;
+              const bool two = mask != 0;
+              const int q1 = two ? __ffs(mask) - 1 : q0; mask &= mask - 1;
+              const int l0 = __shfl_sync(0xffffffffu, lab, q0), l1 = __shfl_sync(0xffffffffu, lab, q1);
+              if (act) {
+                const uint32_t aa0 = my_acc + (uint32_t)l0 * 512u, aa1 = my_acc + (uint32_t)l1 * 512u;
+                double v00, v01, v10, v11, s00, s01, s10, s11;
+                lds_v2f64(xg + (uint32_t)(q0 >> 4) * cstride + (uint32_t)(q0 & 15) * row_bytes, v00, v01);
+                lds_v2f64(xg + (uint32_t)(q1 >> 4) * cstride + (uint32_t)(q1 & 15) * row_bytes, v10, v11);
+                lds_v2f64(aa0, s00, s01); lds_v2f64(aa1, s10, s11);
+                const bool same = l0 == l1;                      // also when the second row is the first one again (odd count)
+                if (!same) sts_v2f64(aa0, s00 + v00, s01 + v01);
+                const double w0 = two ? v10 : 0.0, w1 = two ? v11 : 0.0;
+                sts_v2f64(aa1, s10 + (same ? v00 + w0 : w0), s11 + (same ? v01 + w1 : w1));
               }
             }
           }
@@ -598,20 +597,11 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
           if (lane == 0) mbar_arrive_a(b_sempty + 8u * (uint32_t)s);
           if (++s == S) { s = 0; sph ^= 1u; }
         }
-        // every cluster has exactly one owner: its registers go straight to the CTA's slot
-#pragma unroll
-        for (int m = 0; m < NM; ++m) {
-          const int j = ridx + R * m;
-#pragma unroll
-          for (int e = 0; e < RVEC2; ++e)
-            if (j < k && f + e < d) { const double v = racc[m * RVEC2 + e]; out[(size_t)j * d + f + e] = v; cost = fma(v, p.C[(size_t)j * d + f + e], cost); }
-        }
       } else {
         // private sets in shared memory: this warp's rows are the groups gi = ridx, ridx + R, ... of R_G consecutive rows;
         // sub-row `sub` of a group accumulates into set ridx * R_G + sub, so no two lanes ever meet on an address
-        constexpr int RVEC = RMODE == 0 ? 1 : 2;
-        constexpr int R_LPR = tp_lanes_per_row(ND, RVEC), R_G = 32 / R_LPR, NG = kTileRows / R_G;
-        const int sub = lane / R_LPR, f = (lane % R_LPR) * RVEC;
+        constexpr int R_LPR = tp_lanes_per_row(ND, 1), R_G = 32 / R_LPR, NG = kTileRows / R_G;
+        const int sub = lane / R_LPR, f = lane % R_LPR;
         const bool act = f < d;
         const uint32_t acc_row = (uint32_t)L.ald * 8u;
         const uint32_t my_acc = a_acc + (uint32_t)(ridx * R_G + sub) * (uint32_t)KP * acc_row + (uint32_t)f * 8u;
@@ -628,18 +618,10 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
               const uint32_t xB = xs + (uint32_t)(rB >> 4) * cstride + (uint32_t)(rB & 15) * row_bytes;
               const uint32_t aA = my_acc + (uint32_t)labA * acc_row, aB = my_acc + (uint32_t)labB * acc_row;
               const bool same = labA == labB;
-              if constexpr (RVEC == 1) {
-                const double vA = lds_f64(xA), vB = lds_f64(xB);
-                const double sA = lds_f64(aA), sB = lds_f64(aB);
-                if (!same) sts_f64(aA, sA + vA);
-                sts_f64(aB, sB + (same ? vA + vB : vB));
-              } else {
-                double vA0, vA1, vB0, vB1, sA0, sA1, sB0, sB1;
-                lds_v2f64(xA, vA0, vA1); lds_v2f64(xB, vB0, vB1);
-                lds_v2f64(aA, sA0, sA1); lds_v2f64(aB, sB0, sB1);
-                if (!same) sts_v2f64(aA, sA0 + vA0, sA1 + vA1);
-                sts_v2f64(aB, sB0 + (same ? vA0 + vB0 : vB0), sB1 + (same ? vA1 + vB1 : vB1));
-              }
+              const double vA = lds_f64(xA), vB = lds_f64(xB);
+              const double sA = lds_f64(aA), sB = lds_f64(aB);
+              if (!same) sts_f64(aA, sA + vA);
+              sts_f64(aB, sB + (same ? vA + vB : vB));
             }
           }
           __syncwarp();
@@ -672,8 +654,6 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
       out[i] = sacc;
       cost = fma(sacc, p.C[i], cost);                           // sum_j S_j . c_j
     }
-  } else if constexpr (RMODE == 2) {
-    // written by the owners above
   } else {
     const double* acc0 = reinterpret_cast<const double*>(smem + L.acc_off);
     const int ald = L.ald, setn = KP * L.ald, nsets = L.nsets;
@@ -688,12 +668,12 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
   if (tid < k) { const double nj = (double)cnt_s[tid]; out[(size_t)k * d + tid] = nj; cost = fma(nj, cn_s[tid], cost); }
 #pragma unroll
   for (int msk = 16; msk >= 1; msk >>= 1) { cost += shfl_xor_d(cost, msk); xxs += shfl_xor_d(xxs, msk); }
-  if (lane == 0) { red_s[warp] = cost; red_s[kTpWarps + warp] = xxs; }
+  if (lane == 0) { red_s[warp] = cost; red_s[kTpMaxWarps + warp] = xxs; }
   __syncthreads();
   if (tid == 0) {
     double c = 0, x2 = 0;
 #pragma unroll
-    for (int wv = 0; wv < kTpWarps; ++wv) { c += red_s[wv]; x2 += red_s[kTpWarps + wv]; }
+    for (int wv = 0; wv < kTpWarps; ++wv) { c += red_s[wv]; x2 += red_s[kTpMaxWarps + wv]; }
     out[P - 1] = c; out[P] = x2;                                 // [sum of winner scores][sum |x|^2 of this CTA's rows]
   }
   // ===================================================================== last CTA folds all partials
@@ -728,7 +708,7 @@ __global__ void __launch_bounds__(kTpThreads, 1) lloyd_tp_kernel(const LloydPara
     if (p.C_update != nullptr && peer_ok) {                      // fused driver step
       __threadfence_block();
       __syncthreads();
-      update_centers_body(p.partial_out, k, d, p.C_update, p.tol2, p.state_rw, red_s + 2 * kTpWarps, tid);
+      update_centers_body(p.partial_out, k, d, p.C_update, p.tol2, p.state_rw, red_s + 2 * kTpMaxWarps, tid);
     }
   }
 }

@@ -159,8 +159,8 @@ if __name__ == "__main__":
         bad = 0
         # default scheme for every shape, then the other reduce schemes pinned (42 register-owned, 40/41 private sets) on a subset
         cases = [(n, d, k, 4) for n, d, k in CHECK_SHAPES]
-        cases += [(n, d, k, 42) for n, d, k in CHECK_SHAPES if k <= 16 and (d <= 32 or d % 2 == 0)]
-        cases += [(n, d, k, 40 if d <= 32 else 41) for n, d, k in CHECK_SHAPES[::2] if (d <= 32 or d % 2 == 0) and not (d > 32 and k > 32)]
+        cases += [(n, d, k, 42) for n, d, k in CHECK_SHAPES if d % 2 == 0 and (k <= 16 or d <= 32)]
+        cases += [(n, d, k, 40) for n, d, k in CHECK_SHAPES if d <= 32 and k <= 16]
         for n, d, k, v in cases:
             try:
                 r = subprocess.run([sys.executable, __file__, "one", str(n), str(d), str(k), str(v)], capture_output=True, text=True, timeout=180)
@@ -177,5 +177,5 @@ if __name__ == "__main__":
     if cmd == "bench":
         extra = []
         if "modes" in sys.argv:
-            extra = [(42, "tp_own"), (40, "tp_priv0"), (41, "tp_priv1")]
+            extra = [(42, "tp_own"), (40, "tp_priv")]
         bench(BENCH_SHAPES + (WIDE if "wide" in sys.argv else []), extra=extra)
