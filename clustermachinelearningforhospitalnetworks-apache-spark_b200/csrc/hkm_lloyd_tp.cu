@@ -18,6 +18,9 @@ bool lloyd_tp_eligible(const LloydParams& p, int mode) {
   if (p.k > 64 || p.d > 64 || ((p.d & 1) && p.d > 32)) return false;
   if (p.k <= 8 && variant == 0) return false;               // k <= 8 stays on the fp64 tensor-pipe kernel (HBM-bound already)
   const int kp = ((p.k + 15) / 16) * 16;
+  // measured against the fp64 kernels on the same box (tools/tp_check.py bench wide, profiles/r02_tp_vs_round1.jsonl): with k <= 16
+  // the pipelined variant wins for 8 < d <= 32; thin rows (d <= 8) and d > 32 stay on the fp64 tensor-pipe kernel
+  if (variant == 0 && kp == 16 && (p.d <= 8 || p.d > 32)) return false;
   return tp_choose(p.d, kp, variant >= 40 ? variant - 40 : -1).stages >= 2;
 }
 

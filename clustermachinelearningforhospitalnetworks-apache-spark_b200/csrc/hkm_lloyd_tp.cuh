@@ -268,6 +268,9 @@ __global__ void __launch_bounds__(tp_warps(WCFG) * 32, 1) lloyd_tp_kernel(const 
   float vmax2 = 0.f;
   for (int j = 0; j < k; ++j) vmax2 = fmaxf(vmax2, (float)h_s[j]);
   const float vmax = sqrtf(vmax2) * 1.0001f;
+  float mun2 = 0.f;
+  for (int f = 0; f < d; ++f) mun2 = fmaf((float)mu_s[f], (float)mu_s[f], mun2);
+  const float munorm = sqrtf(mun2) * 1.0001f;
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
@@ -341,7 +344,7 @@ __global__ void __launch_bounds__(tp_warps(WCFG) * 32, 1) lloyd_tp_kernel(const 
     const int cw = warp - kTpConvWarp0;
     const int subc = lane / C_LPR, fc = (lane % C_LPR) * CVEC;
     const bool act = fc < d;
-    const double mu0 = act ? mu_s[fc] : 0.0, mu1 = (CVEC == 2 && act) ? mu_s[fc + 1] : 0.0;
+    const float mu0 = act ? (float)mu_s[fc] : 0.f, mu1 = (CVEC == 2 && act) ? (float)mu_s[fc + 1] : 0.f;
     const uint32_t dst_lane = (uint32_t)(fc >> 2) * LBO_A + (uint32_t)(fc & 3) * 4u + (uint32_t)subc * 16u;
     const uint32_t src_lane = (uint32_t)subc * row_bytes + (uint32_t)fc * 8u;
     const uint32_t src_it = (uint32_t)C_G * row_bytes;
@@ -373,9 +376,9 @@ __global__ void __launch_bounds__(tp_warps(WCFG) * 32, 1) lloyd_tp_kernel(const 
             }
 #pragma unroll
             for (int it = 0; it < NB; ++it) {
-              const uint32_t t0 = __float_as_uint((float)(v0[it] - mu0));
+              const uint32_t t0 = __float_as_uint((float)v0[it] - mu0);
               if (CVEC == 2) {
-                const uint32_t t1 = __float_as_uint((float)(v1[it] - mu1));
+                const uint32_t t1 = __float_as_uint((float)v1[it] - mu1);
                 asm volatile("st.shared.v2.u32 [%0], {%1,%2};" ::"r"(dst0 + (uint32_t)((it0 + it) * C_G * 16)), "r"(t0), "r"(t1) : "memory");
               } else sts_u32(dst0 + (uint32_t)((it0 + it) * C_G * 16), t0);
             }
@@ -393,7 +396,9 @@ __global__ void __launch_bounds__(tp_warps(WCFG) * 32, 1) lloyd_tp_kernel(const 
     const int row = 32 * wsub + lane;                              // tile row of this thread = TMEM lane
     const uint32_t tlane = ((uint32_t)(32 * wsub)) << 16;
     const float kapv = 1.6f * 0.0009765625f * vmax;                // kappa * max|c - mu|
-    const float etab = 0.5f * 1.52587890625e-05f * vmax * vmax;    // eta * max 0.5|c - mu|^2, eta = 2^-16
+    // eta * max 0.5|c - mu|^2 (eta = 2^-16), plus the fp32 rounding of x and mu ahead of the subtraction: 2^-24 (|x| + |mu|) per
+    // feature, |x| <= |x - mu| + |mu| (the |x - mu| part is inside kappa's slack)
+    const float etab = 0.5f * 1.52587890625e-05f * vmax * vmax + 2.5e-7f * munorm * vmax;
     constexpr int DCH = 2 * ND;                                    // 16-byte chunks of the converted row
     const bool conv2 = (d & 1) == 0;
     const int rlane = conv2 ? 2 * lane : lane;                     // refine: first feature of this lane
