@@ -3,11 +3,15 @@
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg2|cfg4|cfg5] [--impl reference]
 
-One "step" = one Lloyd iteration over the resident batch: hkm_assign_reduce (fused assign + per-cluster
-reduce) -> all-reduce of k*(d+1)+1 doubles when N > 1 -> hkm_update_centers.  N > 1 runs under torchrun,
-one rank per GPU, rows sharded (weak scaling: per-GPU rows fixed).  Rank 0 prints ONE JSON line.
-`--impl reference` times the CPU restatement of the MLlib row solver (oracle/, all host threads) on a
-bounded sample of the same workload; Spark itself cannot run here (no JVM / pyspark).
+One "step" = one Lloyd iteration over the resident batch: one launch of the fused pass (assign + per-cluster
+reduce + cross-GPU sum over NVLink peer memory when N > 1 + centre update).  N > 1 runs under torchrun, one
+rank per GPU, rows sharded (weak scaling: per-GPU rows fixed).  Rank 0 prints ONE JSON line.  The headline
+workload is BASELINE configs[1] (cfg2); the same line carries, under "extra", 20 timed steps each of the
+configs[3] shard (cfg4) and of configs[2] (cfg3, its 100 M rows divided by N), at N > 1 a "parity_check" of the
+in-kernel peer reduction against a rank-ordered sum of the per-rank partials, and two end-to-end numbers
+through the public estimator (given initial centres, and the default k-means|| initialiser).
+`--impl reference` times the CPU restatement of the MLlib row solver (oracle/, all host threads) on the SAME
+host-built hospital table (same generator, seed and rows); Spark itself cannot run here (no JVM / pyspark).
 """
 from __future__ import annotations
 
@@ -140,26 +144,51 @@ def host_threads() -> int:
         return max(1, os.cpu_count() or 1)
 
 
+PARTITIONS = 8          # Spark partition layout both arms emulate
+
+
+def config_for(args, n, d, k, desc):
+    """The `config` object of the JSON line -- identical, key for key, in both arms."""
+    return {"workload": args.workload, "description": desc, "rows_per_gpu": n, "d": d, "k": k,
+            "table": "datagen.hospital_matrix(rows_per_gpu, d, profiles=k, seed=20250331 + rank): synthetic hospital table, StandardScaler defaults",
+            "partitions": PARTITIONS, "init": "first k rows of rank 0's shard", "iterations_forced": True}
+
+
+def host_table(n, d, k, rank):
+    from hkm_b200 import datagen
+    return datagen.hospital_matrix(n, d, profiles=k, seed=SEED + rank)
+
+
+def cpu_lloyd_throughput(Xh, Ch, threads, min_seconds, max_reps):
+    """rows*iter/s of the oracle's Lloyd pass (C, OpenMP over P Spark-style partitions) on all host threads."""
+    from oracle import hkm_oracle as O
+    O.lloyd_pass(Xh, Ch, P=PARTITIONS, threads=threads)
+    C, reps, t0 = Ch.copy(), 0, time.perf_counter()
+    while reps < 3 or (time.perf_counter() - t0 < min_seconds and reps < max_reps):
+        sums, wsum, cost, _ = O.lloyd_pass(Xh, C, P=PARTITIONS, threads=threads)
+        C, _ = O.update_centers(sums, wsum, C, 0.0)
+        reps += 1
+    dt = time.perf_counter() - t0
+    return Xh.shape[0] * reps / dt, reps, dt
+
+
 def run_reference(args):
     """CPU arm: the oracle's Lloyd pass (C, OpenMP over Spark-style partitions) on all host threads."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    import numpy as np
-    from oracle import hkm_oracle as O
+    import hkm_b200  # noqa: F401
     n_full, d, k, desc = WORKLOADS[args.workload]
     n = min(n_full, args.ref_rows)
-    rng = np.random.default_rng(SEED)
-    prof = rng.normal(size=(k, d)) * 2.0
-    X = prof[rng.integers(0, k, size=n)] + rng.normal(size=(n, d)) * 0.7
+    X = host_table(n, d, k, 0)
     C = X[:k].copy()
     threads = host_threads()
-    P = max(8, 4 * threads)
+    from oracle import hkm_oracle as O
     for _ in range(max(args.warmup, 1)):
-        O.lloyd_pass(X, C, P=P, threads=threads)
+        O.lloyd_pass(X, C, P=PARTITIONS, threads=threads)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        sums, wsum, cost, _ = O.lloyd_pass(X, C, P=P, threads=threads)
+        sums, wsum, cost, _ = O.lloyd_pass(X, C, P=PARTITIONS, threads=threads)
         C, _ = O.update_centers(sums, wsum, C, 0.0)
     dt = time.perf_counter() - t0
     val = n * args.steps / dt
@@ -167,9 +196,10 @@ def run_reference(args):
         "impl": "reference", "metric": "kmeans_rows_iter_per_sec", "value": val, "unit": "rows*iter/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": max(args.warmup, 1), "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": args.workload, "description": desc, "rows_per_step": n, "d": d, "k": k},
+        "config": config_for(args, n, d, k, desc),
         "cpu_baseline": {"value": val, "unit": "rows*iter/s", "cores": threads, "kind": "port",
-                         "sample": f"{n} of {n_full} rows x {d}, {args.steps} Lloyd passes; CPU restatement of the MLlib row solver (not Spark: no JVM here)"},
+                         "sample": f"{n} of {n_full} rows x {d}, {args.steps} Lloyd passes, P = {PARTITIONS} partitions; CPU restatement of the MLlib row solver "
+                                   "(not Spark: no JVM here); the same host-built hospital table as the GPU arm's rank 0"},
         "e2e": {"value": val, "unit": "rows*iter/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     emit(line)
@@ -200,6 +230,9 @@ def main():
     ap.add_argument("--ref-rows", type=int, default=10_000_000, help="rows per step of the CPU arm (bounded sample)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the cfg4 / cfg3 extras of the default (cfg2) run")
+    ap.add_argument("--extra-steps", type=int, default=20)
+    ap.add_argument("--extra-rows", type=int, default=0, help="cap the rows per GPU of the extra workloads (smoke runs)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3
@@ -228,102 +261,191 @@ def main():
         n //= world                       # configs[2] is a fixed 100M-row table sharded over the GPUs (strong scaling)
     if args.rows:
         n = args.rows
-
-    X = datagen.hospital_matrix_device(n, d, k, SEED + rank, dev)
-    C0 = X[:k].clone()
-    if world > 1:
-        dist.broadcast(C0, 0)
-    P = k * d + k + 1
-    partial = torch.zeros(P, dtype=torch.float64, device=dev)
-    scratch = N.new_scratch(d, k, dev)
-    state = N.new_state(dev)
-    xsum = torch.zeros(1, dtype=torch.float64, device=dev)
-    C = C0.clone()
-
-    xchg = hkm_b200._runtime.PeerExchange.get(dev) if world > 1 else None
-
-    def step(mode, ev=None):
-        if ev is not None:
-            ev[0].record()
-        # tol < 0: never "converged", every step does full work (rows*iter well defined)
-        if world == 1:
-            N.lloyd_step(X, C, partial, -1.0, state, scratch, xnorm2_sum=xsum, xnorm2_mode=mode)   # pass + centre update, one launch
-            if ev is not None:
-                ev[1].record()
-            return
-        if xchg is not None:     # ranks > 1: still one launch, the k*(d+1)+1 sums cross NVLink inside the kernel tail
-            N.lloyd_step_peer(X, C, partial, -1.0, state, scratch, xchg, xnorm2_sum=xsum, xnorm2_mode=mode)
-            if ev is not None:
-                ev[1].record()
-            return
-        N.assign_reduce(X, C, partial, state=state, scratch=scratch, xnorm2_sum=xsum, xnorm2_mode=mode)
-        if ev is not None:
-            ev[1].record()
-        dist.all_reduce(partial)
-        N.update_centers(partial, C, -1.0, state)
+    xchg_all = hkm_b200._runtime.PeerExchange.get(dev) if world > 1 else None
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    step(1)                                  # STORE pass: sum |x|^2 (outside the timed region, like the first Lloyd iteration)
-    for _ in range(args.warmup):
-        step(2)
-    # N == 1: a step IS one launch of the kernel, so the region's own events time it; N > 1: bracket each launch
-    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)] if world > 1 else None
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    sampler = make_sampler(local_rank) if rank == 0 else None
-    barrier()
-    if sampler:
-        sampler.start()
-    e0.record()
-    for i in range(args.steps):
-        step(2, kev[i] if kev else None)
-    e1.record()
-    barrier()
-    clocks = sampler.stop() if sampler else None
-    ms_total = e0.elapsed_time(e1)
-    kernel_ms = (sum(a.elapsed_time(b) for a, b in kev) / args.steps) if kev else ms_total / args.steps
-    t = torch.tensor([ms_total, kernel_ms], dtype=torch.float64, device=dev)
+    def kernel_name(d_, k_):
+        if k_ <= 8 or (k_ <= 16 and (d_ <= 8 or d_ > 32)):
+            return "lloyd_mma_kernel (hkm_lloyd_mma.cuh)"
+        return "lloyd_tp_kernel (hkm_lloyd_tp.cuh)"
+
+    def timed_loop(X, C0, steps, warmup, sample_clocks):
+        """`steps` Lloyd iterations over the resident shard X, device-timed; returns (ms_total, kernel_ms, clocks, state, C, partial)."""
+        k_, d_ = C0.shape
+        nloc = X.shape[0]
+        partial = torch.zeros(k_ * d_ + k_ + 1, dtype=torch.float64, device=dev)
+        scratch = N.new_scratch(d_, k_, dev)
+        state = N.new_state(dev)
+        xsum = torch.zeros(1, dtype=torch.float64, device=dev)
+        C = C0.clone()
+        xchg = xchg_all if (xchg_all is not None and xchg_all.fits(k_, d_)) else None
+
+        def step(mode, ev=None):
+            if ev is not None:
+                ev[0].record()
+            # tol < 0: never "converged", every step does full work (rows*iter well defined)
+            if world == 1:
+                N.lloyd_step(X, C, partial, -1.0, state, scratch, xnorm2_sum=xsum, xnorm2_mode=mode)   # pass + centre update, one launch
+            elif xchg is not None:    # ranks > 1: still one launch, the k*(d+1)+1 sums cross NVLink inside the kernel tail
+                N.lloyd_step_peer(X, C, partial, -1.0, state, scratch, xchg, xnorm2_sum=xsum, xnorm2_mode=mode)
+            else:
+                N.assign_reduce(X, C, partial, state=state, scratch=scratch, xnorm2_sum=xsum, xnorm2_mode=mode)
+                if ev is not None:
+                    ev[1].record()
+                dist.all_reduce(partial)
+                N.update_centers(partial, C, -1.0, state)
+                return
+            if ev is not None:
+                ev[1].record()
+
+        step(1)                                  # STORE pass: sum |x|^2 (outside the timed region, like the first Lloyd iteration)
+        for _ in range(warmup):
+            step(2)
+        # N == 1: a step IS one launch of the kernel, so the region's own events time it; N > 1: bracket each launch
+        kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)] if world > 1 else None
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sampler = make_sampler(local_rank) if (rank == 0 and sample_clocks) else None
+        barrier()
+        if sampler:
+            sampler.start()
+        e0.record()
+        for i in range(steps):
+            step(2, kev[i] if kev else None)
+        e1.record()
+        barrier()
+        clocks = sampler.stop() if sampler else None
+        ms_total = e0.elapsed_time(e1)
+        kernel_ms = (sum(a.elapsed_time(b) for a, b in kev) / steps) if kev else ms_total / steps
+        t = torch.tensor([ms_total, kernel_ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        st = N.read_state(state)
+        assert st.iter == 1 + warmup + steps, "device state says a step was skipped"
+        if xchg is not None:
+            xchg.check()
+        return float(t[0]), float(t[1]), clocks, (C, partial, scratch, state, xsum, xchg)
+
+    # ---------------- the table: built on the host by the same generator the CPU arm uses, then made resident
+    # (cfg2, the headline).  The larger workloads do not fit host RAM and are generated in HBM by the device twin of the generator.
+    on_host = n * d * 8 <= 4 << 30
+    Xh = host_table(n, d, k, rank) if on_host else None
+    X = torch.from_numpy(Xh).to(dev) if on_host else datagen.hospital_matrix_device(n, d, k, SEED + rank, dev)
+    C0 = X[:k].clone()
     if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, kernel_ms = float(t[0]), float(t[1])
-    st = N.read_state(state)
-    assert st.iter == 1 + args.warmup + args.steps, "device state says a step was skipped"
+        dist.broadcast(C0, 0)
+    ms_total, kernel_ms, clocks, (C, partial, scratch, state, xsum, xchg) = timed_loop(X, C0, args.steps, args.warmup, True)
     value = n * world * args.steps / (ms_total * 1e-3)
 
+    # ---------------- N > 1: the in-kernel peer reduction against a rank-ordered sum of the per-rank partials
+    parity = None
+    if world > 1 and xchg is not None:
+        Ca, Cb = C.clone(), C.clone()
+        pa = torch.zeros_like(partial); pb = torch.zeros_like(partial)
+        sa, sb = N.new_state(dev), N.new_state(dev)
+        N.lloyd_step_peer(X, Ca, pa, -1.0, sa, scratch, xchg, xnorm2_sum=xsum, xnorm2_mode=2)
+        N.assign_reduce(X, Cb, pb, state=sb, scratch=scratch, xnorm2_sum=xsum, xnorm2_mode=2)
+        gathered = [torch.empty_like(pb) for _ in range(world)]
+        dist.all_gather(gathered, pb)
+        tot = gathered[0].clone()
+        for g in gathered[1:]:
+            tot = tot + g                                   # rank order, the order the kernel's tail uses
+        N.update_centers(tot, Cb, -1.0, sb)
+        torch.cuda.synchronize()
+        xchg.check()
+        same_sum = torch.tensor([1 if torch.equal(pa, tot) else 0, 1 if torch.equal(Ca, Cb) else 0], dtype=torch.int32, device=dev)
+        dist.all_reduce(same_sum, op=dist.ReduceOp.MIN)
+        cmin, cmax = Ca.clone(), Ca.clone()
+        dist.all_reduce(cmin, op=dist.ReduceOp.MIN); dist.all_reduce(cmax, op=dist.ReduceOp.MAX)
+        parity = {"peer_vs_rank_ordered_sum_bitequal": bool(same_sum[0].item()), "centres_peer_vs_rank_ordered_bitequal": bool(same_sum[1].item()),
+                  "centres_identical_on_all_ranks": bool(torch.equal(cmin, cmax)), "ranks": world,
+                  "how": "one extra step from the same centres: hkm_lloyd_step_peer vs hkm_assign_reduce + all_gather + sum in rank order + hkm_update_centers"}
+    del C, partial
+
     # ---------------- e2e: the public estimator call on HOST (pinned) features
-    e2e = None
-    if not args.no_e2e:
+    e2e = e2e_default = None
+    if not args.no_e2e and on_host:
         from hkm_b200.ml.clustering import KMeans
         e2e_iters = 20
-        host = torch.empty((n, d), dtype=torch.float64, pin_memory=True)
-        host.copy_(X)
+        host = torch.from_numpy(Xh).pin_memory()
         init = C0.cpu().numpy()
-        km = KMeans(k=k, seed=42, maxIter=e2e_iters, tol=0.0).setInitialCenters(init)
         del X
         torch.cuda.empty_cache()
-        fits = 1
-        km.fit({"features": host})          # warm-up fit
-        times = []
-        for _ in range(5):                   # median of 5 single fits: the H2D copy shares the host's PCIe with other tenants
+        # the host -> device copy alone (same pinned buffer), for the breakdown
+        hcopy = []
+        for _ in range(3):
             barrier()
             t0 = time.perf_counter()
-            model = km.fit({"features": host})   # H2D of the features, 20 Lloyd steps, summary pass, D2H of centres/cost/sizes
-            _ = model.summary.trainingCost
+            tmp = host.to(dev, non_blocking=True)
             torch.cuda.synchronize()
-            tt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
-            if world > 1:
-                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-            times.append(float(tt[0]))
-        dt = statistics.median(times)
-        e2e = {"value": n * world * e2e_iters * fits / dt, "unit": "rows*iter/s",
-               "h2d_bytes_per_step": int(n * d * 8 / e2e_iters), "d2h_bytes_per_step": int((k * d * 8 + 64 + n * 0) / e2e_iters),
-               "call": f"KMeans(k={k}, maxIter={e2e_iters}, tol=0).fit(host table): one H2D of the pinned features per fit "
-                       f"({n * d * 8} B), {e2e_iters} Lloyd steps + summary pass on device, D2H of centres/cost/sizes",
-               "ms_per_fit": dt / fits * 1e3, "ms_per_fit_all": [round(t * 1e3, 2) for t in times]}
-        X = None
+            hcopy.append(time.perf_counter() - t0)
+            del tmp
+        ms_h2d = statistics.median(hcopy) * 1e3
+
+        def time_fits(km, reps):
+            km.fit({"features": host})          # warm-up fit
+            times = []
+            for _ in range(reps):                # median of single fits: the H2D copy shares the host's PCIe with other tenants
+                barrier()
+                t0 = time.perf_counter()
+                model = km.fit({"features": host})   # H2D of the features, init, Lloyd steps, summary pass, D2H of centres/cost/sizes
+                _ = model.summary.trainingCost
+                torch.cuda.synchronize()
+                tt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+                if world > 1:
+                    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                times.append(float(tt[0]))
+            return statistics.median(times), times, model
+
+        km = KMeans(k=k, seed=42, maxIter=e2e_iters, tol=0.0).setNumPartitions(PARTITIONS).setInitialCenters(init)
+        dt, times, _ = time_fits(km, 5)
+        e2e = {"value": n * world * e2e_iters / dt, "unit": "rows*iter/s",
+               "h2d_bytes_per_step": int(n * d * 8 / e2e_iters), "d2h_bytes_per_step": int((k * d * 8 + 64) / e2e_iters),
+               "call": f"KMeans(k={k}, maxIter={e2e_iters}, tol=0).setInitialCenters(first k rows).fit(host table): one H2D of the pinned features "
+                       f"per fit ({n * d * 8} B), {e2e_iters} Lloyd steps + summary pass on device, D2H of centres/cost/sizes",
+               "ms_per_fit": dt * 1e3, "ms_per_fit_all": [round(t * 1e3, 2) for t in times], "ms_h2d_alone": round(ms_h2d, 2),
+               "h2d_note": "every rank copies its shard from host memory of the same NUMA node; the copy, not the kernels, sets the fit time"}
+        kmd = KMeans(k=k, seed=42, maxIter=e2e_iters, tol=0.0).setNumPartitions(PARTITIONS)      # pyspark defaults: initMode k-means||, initSteps 2
+        dtd, timesd, md = time_fits(kmd, 3)
+        e2e_default = {"value": n * world * md.summary.numIter / dtd, "unit": "rows*iter/s", "h2d_bytes_per_step": int(n * d * 8 / max(md.summary.numIter, 1)),
+                       "d2h_bytes_per_step": int((k * d * 8 + 64) / max(md.summary.numIter, 1)),
+                       "call": f"KMeans(k={k}, maxIter={e2e_iters}, tol=0, seed=42).fit(host table) with the default k-means|| initialiser (initSteps 2, "
+                               f"P = {PARTITIONS}): H2D + k-means|| passes + LocalKMeans + {md.summary.numIter} Lloyd steps + summary pass",
+                       "ms_per_fit": dtd * 1e3, "ms_per_fit_all": [round(t * 1e3, 2) for t in timesd], "numIter": md.summary.numIter}
+        del host
+    else:
+        del X
+    torch.cuda.empty_cache()
+
+    # ---------------- extra workloads in the same line: configs[3] shard and configs[2], generated on device (too large for host RAM)
+    extra = {}
+    if args.workload == "cfg2" and not args.no_extra:
+        for name in ("cfg4", "cfg3"):
+            en, ed, ek, edesc = WORKLOADS[name]
+            if name == "cfg3":
+                en //= world
+            if args.extra_rows:
+                en = min(en, args.extra_rows)
+            try:
+                Xe = datagen.hospital_matrix_device(en, ed, ek, SEED + rank, dev)
+                Ce = Xe[:ek].clone()
+                if world > 1:
+                    dist.broadcast(Ce, 0)
+                ems, ekms, eclk, _st = timed_loop(Xe, Ce, args.extra_steps, 3, True)
+                del Xe, _st
+                torch.cuda.empty_cache()
+                ebytes = en * ed * 8
+                extra[name] = {"description": edesc, "rows_per_gpu": en, "d": ed, "k": ek, "steps": args.extra_steps, "ms_per_step": ems / args.extra_steps,
+                               "value": en * world * args.extra_steps / (ems * 1e-3), "unit": "rows*iter/s", "scaling": "strong" if name == "cfg3" else "weak",
+                               "kernel": kernel_name(ed, ek), "kernel_ms": ekms, "achieved_gbs": ebytes / (ekms * 1e-3) / 1e9,
+                               "frac": ebytes / (ekms * 1e-3) / 1e9 / measured_peak_gbs()[0], "clocks": eclk,
+                               "table": "datagen.hospital_matrix_device (generated in HBM, seed 20250331 + rank)"}
+            except Exception as ex:      # noqa: BLE001  (e.g. out of memory on a smaller GPU): report, do not lose the headline
+                extra[name] = {"error": f"{type(ex).__name__}: {str(ex)[:200]}"}
+                torch.cuda.empty_cache()
 
     if rank != 0:
         if world > 1:
@@ -337,34 +459,30 @@ def main():
         "metric": "kmeans_rows_iter_per_sec", "value": value, "unit": "rows*iter/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong" if args.workload == "cfg3" else "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": args.workload, "description": desc, "rows_per_gpu": n, "d": d, "k": k,
-                   "cache": f"inputs ({alg_bytes / 1e9:.2f} GB per GPU) are larger than the 126 MB L2; no flush needed",
-                   "step": ("hkm_lloyd_step (assign + reduce + centre update in one launch, xnorm2 REUSE)" if world == 1 else ("hkm_lloyd_step_peer (one launch: pass + NVLink peer-memory sum of k*(d+1)+1 f64 + centre update)" if xchg is not None else "hkm_assign_reduce (xnorm2 REUSE) + NCCL allreduce(k*(d+1)+1 f64) + hkm_update_centers")) + ", convergence test off"},
+        "config": config_for(args, n, d, k, desc) if on_host else dict(config_for(args, n, d, k, desc), table="datagen.hospital_matrix_device (generated in HBM)"),
+        "notes": {"cache": f"inputs ({alg_bytes / 1e9:.2f} GB per GPU) are larger than the 126 MB L2; no flush needed",
+                  "step": ("hkm_lloyd_step (assign + reduce + centre update in one launch, xnorm2 REUSE)" if world == 1 else ("hkm_lloyd_step_peer (one launch: pass + NVLink peer-memory sum of k*(d+1)+1 f64 + centre update)" if xchg is not None else "hkm_assign_reduce (xnorm2 REUSE) + NCCL allreduce(k*(d+1)+1 f64) + hkm_update_centers")) + ", convergence test off"},
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})", "kernel": "lloyd_tc_kernel (hkm_lloyd_tc.cuh)" if (k > 32 and d > 32) else ("lloyd_mma_kernel (hkm_lloyd_mma.cuh)" if k <= 16 else "lloyd_pass_kernel (hkm_lloyd.cuh)"),
+                     "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})", "kernel": kernel_name(d, k),
                      "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": alg_bytes, "traffic": ncu_traffic(args.workload)},
         "gpu_launches": (1 if (world == 1 or xchg is not None) else 2) * args.steps,
         "clocks": clocks,
     }
     if e2e:
         line["e2e"] = e2e
-    if not args.no_cpu_baseline and world == 1:
-        from oracle import hkm_oracle as O
-        rng = np.random.default_rng(SEED)
+    if e2e_default:
+        line["e2e_default_init"] = e2e_default
+    if extra:
+        line["extra"] = extra
+    if parity:
+        line["parity_check"] = parity
+    if not args.no_cpu_baseline and world == 1 and on_host:
         ns = min(n, 10_000_000)
-        prof = rng.normal(size=(k, d)) * 2.0
-        Xh = prof[rng.integers(0, k, size=ns)] + rng.normal(size=(ns, d)) * 0.7
-        Ch = Xh[:k].copy()
         threads = host_threads()
-        O.lloyd_pass(Xh, Ch, P=4 * threads, threads=threads)
-        reps, t0 = 0, time.perf_counter()
-        while reps < 3 or (time.perf_counter() - t0 < 10 and reps < 200):
-            O.lloyd_pass(Xh, Ch, P=4 * threads, threads=threads)
-            reps += 1
-        dt = time.perf_counter() - t0
-        line["cpu_baseline"] = {"value": ns * reps / dt, "unit": "rows*iter/s", "cores": threads, "kind": "port",
-                                "sample": f"{reps} Lloyd passes over {ns} x {d} rows (k={k}); C/OpenMP restatement of the MLlib row solver "
-                                          "(Spark local[N] cannot run here: no JVM/pyspark)"}
+        v, reps, dt = cpu_lloyd_throughput(Xh[:ns], Xh[:k].copy(), threads, 10.0, 200)
+        line["cpu_baseline"] = {"value": v, "unit": "rows*iter/s", "cores": threads, "kind": "port",
+                                "sample": f"{reps} Lloyd passes over the first {ns} rows x {d} of the same host-built table (k={k}, P = {PARTITIONS}); C/OpenMP "
+                                          "restatement of the MLlib row solver (Spark local[N] cannot run here: no JVM/pyspark)"}
     emit(line)
     if world > 1:
         dist.destroy_process_group()

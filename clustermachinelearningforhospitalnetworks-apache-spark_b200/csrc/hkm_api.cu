@@ -139,7 +139,7 @@ int hkm_version(void) { return 100; }
 int hkm_max_k(void) { return 64; }
 int hkm_max_d(void) { return 96; }
 int hkm_set_lloyd_variant(int variant) {
-  if (!((variant >= 0 && variant <= 5) || (variant == 40 || variant == 42 || variant == 43))) { set_error("hkm_set_lloyd_variant: 0..5 (40..43: variant 4 with a pinned reduce scheme)"); return HKM_ERR_INVALID; }
+  if (!((variant >= 0 && variant <= 5) || (variant == 40 || variant == 42 || variant == 43) || (variant >= 50 && variant <= 54))) { set_error("hkm_set_lloyd_variant: 0..5 (40..43 / 50..54: variant 4 with a pinned reduce scheme / warp budget)"); return HKM_ERR_INVALID; }
   g_lloyd_variant = variant;
   return HKM_OK;
 }
@@ -148,7 +148,7 @@ size_t hkm_assign_reduce_scratch_bytes(int d, int k) {
   if (d < 1 || k < 1) return 0;
   const int k_pad = ((k + 7) / 8) * 8;
   LaunchPlan pl = plan_lloyd(d, k_pad);
-  size_t grid = (size_t)sm_count() * pl.ctas_per_sm;
+  size_t grid = (size_t)sm_count() * (pl.ctas_per_sm > 2 ? pl.ctas_per_sm : 2);   // every variant launches at most this many CTAs
   return 256 + grid * ((size_t)k * d + 2 * (size_t)k + 2) * sizeof(double);
 }
 

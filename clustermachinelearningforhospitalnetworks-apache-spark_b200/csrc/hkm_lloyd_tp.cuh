@@ -41,10 +41,13 @@ namespace hkm {
 
 // warp budgets (WCFG): 0 = 1 screen group + 8 reduce + 4 convert (18 warps), 1 = 2 + 8 + 8 (26 warps, thin rows: every role is
 // latency bound, so more warps per role), 2 = 2 + 4 + 4 (18 warps, k > 32 with private sets); + producer + MMA issuer
-constexpr int kTpMaxWarps = 26;
-__host__ __device__ constexpr int tp_sg(int wcfg) { return wcfg == 0 ? 1 : 2; }
-__host__ __device__ constexpr int tp_reduce_warps(int wcfg) { return wcfg == 2 ? 4 : 8; }
-__host__ __device__ constexpr int tp_conv_warps(int wcfg) { return wcfg == 1 ? 8 : 4; }
+// 3 = 1 + 16 + 8 (30 warps: large k*d, where one tile's convert -> score -> reduce chain is what the two-stage ring waits for);
+// 4 = budget 0 with two CTAs per SM (thin rows: twice the warps per role, half the shared memory each)
+constexpr int kTpMaxWarps = 30;
+__host__ __device__ constexpr int tp_sg(int wcfg) { return (wcfg == 1 || wcfg == 2) ? 2 : 1; }
+__host__ __device__ constexpr int tp_reduce_warps(int wcfg) { return wcfg == 2 ? 4 : (wcfg == 3 ? 16 : 8); }
+__host__ __device__ constexpr int tp_conv_warps(int wcfg) { return (wcfg == 1 || wcfg == 3) ? 8 : 4; }
+__host__ __device__ constexpr int tp_ctas_per_sm(int wcfg) { return wcfg == 4 ? 2 : 1; }
 __host__ __device__ constexpr int tp_warps(int wcfg) { return 4 * tp_sg(wcfg) + tp_reduce_warps(wcfg) + tp_conv_warps(wcfg) + 2; }
 __host__ __device__ constexpr int tp_tmem_stride(int kp) { return kp <= 32 ? 32 : (kp <= 64 ? 64 : (kp <= 128 ? 128 : 256)); }
 // feature-count class of ND = ceil(d / 8): rows are handled as if they had 8, 16, 32 or 64 features
@@ -57,7 +60,7 @@ struct TpPlan {
   int stages, rmode, na, wcfg, nd;   // ring depth, reduce mode, tf32 operand buffers (1 or 2), warp budget, ceil(d/8)
   int ald, nsets;                  // rmode 0/1: accumulator row (doubles), sets
   int kchunks, lbo_a, lbo_b, a_bytes;
-  int x_off, a_off, b_off, acc_off, cn_off, mu_off, cnt_off, lab_off, red_off, bar_off, tmem_off, total;
+  int x_off, a_off, b_off, acc_off, cn_off, mu_off, cnt_off, lab_off, red_off, bar_off, tmem_off, cs_off, total;   // cs_off: fp64 centres for the refine (0: read from global)
   unsigned long long* prof;   // developer profile (tools/tp_check.py prof): [warp][8] cycle counters of CTA 0, or null
 };
 
@@ -89,25 +92,27 @@ __host__ __device__ inline TpPlan tp_plan(int d, int kp, int stages, int rmode, 
   L.red_off = o; o += (2 * kTpMaxWarps + 64) * 8;
   L.bar_off = o; o += (3 * kMaxStages + 8) * 8;
   L.tmem_off = o; o += 16;
+  // the exact re-scoring reads whole centres; a shared-memory copy keeps that off the L2 round trip when it is small
+  if (kp * d * 8 <= 8 * 1024) { L.cs_off = o; o += kp * d * 8; }
   L.total = o;
   return L;
 }
 
 // Picks reduce mode, warp budget, operand buffering and ring depth for a shape; stages < 2 => the shape does not fit.
-// force_rmode >= 0 pins the reduce mode (tuning).
-__host__ inline TpPlan tp_choose(int d, int kp, int force_rmode = -1) {
-  const int budget = 227 * 1024 - 1024;
+// force_rmode / force_wcfg >= 0 pin the reduce mode / warp budget (tuning).
+__host__ inline TpPlan tp_choose(int d, int kp, int force_rmode = -1, int force_wcfg = -1) {
   const int nd = (d + 7) / 8;
   // candidates in order of preference: (reduce mode, warp budget)
-  int cand[8][2]; int nc = 0;
-  auto add = [&](int rm, int w) { cand[nc][0] = rm; cand[nc][1] = w; ++nc; };
-  if (kp == 16 && (force_rmode < 0 || force_rmode == 3)) add(3, nd <= 4 ? 1 : 0);
-  if (d <= 32 && (force_rmode < 0 || force_rmode == 0)) { add(0, 1); if (kp >= 48) add(0, 2); add(0, 0); }
-  if (!(d & 1) && (force_rmode < 0 || force_rmode == 2)) add(2, 0);
+  int cand[10][2]; int nc = 0;
+  auto add = [&](int rm, int w) { if (force_wcfg < 0 || force_wcfg == w) { cand[nc][0] = rm; cand[nc][1] = w; ++nc; } };
+  if (kp == 16 && (force_rmode < 0 || force_rmode == 3)) { if (force_wcfg == 4) add(3, 4); add(3, nd <= 4 ? 1 : 0); if (force_wcfg == 0) add(3, 0); }
+  if (d <= 32 && (force_rmode < 0 || force_rmode == 0)) { if (force_wcfg == 4) add(0, 4); add(0, 1); if (kp >= 48) add(0, 2); add(0, 0); }
+  if (!(d & 1) && (force_rmode < 0 || force_rmode == 2)) { add(2, 3); add(2, 0); }
   TpPlan best{}; best.stages = 0;
   for (int ci = 0; ci < nc; ++ci)
     for (int na = 2; na >= 1; --na) {
       const int rm = cand[ci][0], w = cand[ci][1];
+      const int budget = (227 * 1024) / tp_ctas_per_sm(w) - 1024 - (tp_ctas_per_sm(w) > 1 ? 1024 : 0);
       const int fixed = tp_plan(d, kp, 2, rm, na, w).total - 2 * stage_bytes(d) - 2 * kTileRows * 4;
       int st = (budget - fixed) / (stage_bytes(d) + kTileRows * 4);
       if (st > kMaxStages) st = kMaxStages;
@@ -139,7 +144,13 @@ __device__ __forceinline__ bool tp_try_wait(uint32_t bar, uint32_t parity) {
   return ok != 0;
 }
 static __device__ __noinline__ void tp_wait_slow(uint32_t bar, uint32_t parity, int tag) {
-  for (int it = 0; it < 3000; ++it) if (tp_try_wait(bar, parity)) return;
+  // the sleep ends at every barrier event of the CTA, so a wait wakes a few dozen times per tile: keep the wake-up path short
+  // (eight tries per watchdog count)
+#pragma unroll 1
+  for (int it = 0; it < 400; ++it) {
+#pragma unroll
+    for (int u = 0; u < 8; ++u) if (tp_try_wait(bar, parity)) return;
+  }
   printf("lloyd_tp: block %d warp %d stuck on barrier tag %d (smem 0x%x, parity %u)\n", (int)blockIdx.x, (int)(threadIdx.x >> 5), tag, bar, parity);
   __trap();
 }
@@ -161,7 +172,7 @@ __device__ __forceinline__ void sts_v2f64(uint32_t a, double x, double y) { asm 
 
 // KP = padded cluster count (16, 32, 48, 64); CVEC = 2 (even d) or 1; RMODE as in TpPlan; WCFG = warp budget; ND = ceil(d/8).
 template <int KP, int CVEC, int RMODE, int WCFG, int ND>
-__global__ void __launch_bounds__(tp_warps(WCFG) * 32, 1) lloyd_tp_kernel(const LloydParams p, const TpPlan L) {
+__global__ void __launch_bounds__(tp_warps(WCFG) * 32, tp_ctas_per_sm(WCFG)) lloyd_tp_kernel(const LloydParams p, const TpPlan L) {
   if (p.skip != nullptr && *p.skip != 0) return;
   constexpr int SG = tp_sg(WCFG), R = tp_reduce_warps(WCFG), CW = tp_conv_warps(WCFG);
   constexpr int kTpWarps = tp_warps(WCFG), kTpThreads = kTpWarps * 32;
@@ -230,6 +241,7 @@ __global__ void __launch_bounds__(tp_warps(WCFG) * 32, 1) lloyd_tp_kernel(const 
   for (int i = tid; i < (L.acc_off - L.a_off) / 16; i += kTpThreads) reinterpret_cast<uint4*>(smem + L.a_off)[i] = make_uint4(0, 0, 0, 0);
   for (int i = tid; i < (L.nsets * KP * L.ald) / 2; i += kTpThreads) reinterpret_cast<uint4*>(smem + L.acc_off)[i] = make_uint4(0, 0, 0, 0);
   for (int i = tid; i < KP; i += kTpThreads) cnt_s[i] = 0u;
+  if (L.cs_off != 0) for (int i = tid; i < k * d; i += kTpThreads) reinterpret_cast<double*>(smem + L.cs_off)[i] = p.C[i];
   if (tid < d8 + 8) { double s = 0; if (tid < d) for (int j = 0; j < k; ++j) s += p.C[(size_t)j * d + tid]; mu_s[tid] = tid < d ? s / k : 0.0; }   // mu = mean of the centres
   __syncthreads();
   double* h_s = red_s + 2 * kTpMaxWarps;   // [KP] |c - mu|^2, later the centre-update scratch
@@ -338,8 +350,9 @@ __global__ void __launch_bounds__(tp_warps(WCFG) * 32, 1) lloyd_tp_kernel(const 
     }
   } else if (warp >= kTpConvWarp0) {
     // ===================================================================== converters
-    // lane = (row of the group, feature pair); a warp converts chunks cw, cw + CW, ..., C_G rows per instruction.  The fp32
-    // values are stored as they are: the tensor core reads their top 19 bits (tf32), the bound below allows for that
+    // lane = (row of the group, feature pair); a warp converts chunks cw, cw + CW, ..., C_G rows per instruction.  The tensor
+    // core TRUNCATES its fp32 operands to tf32 (it ignores the 13 low mantissa bits: tools/tf32_rounding_probe.cu), so half a
+    // tf32 ulp is added to the bit pattern first -- one integer add per value makes the truncation a round-to-nearest
     constexpr int C_LPR = tp_lanes_per_row(ND, CVEC), C_G = 32 / C_LPR, NIT = kChunkRows / C_G;
     const int cw = warp - kTpConvWarp0;
     const int subc = lane / C_LPR, fc = (lane % C_LPR) * CVEC;
@@ -376,9 +389,9 @@ __global__ void __launch_bounds__(tp_warps(WCFG) * 32, 1) lloyd_tp_kernel(const 
             }
 #pragma unroll
             for (int it = 0; it < NB; ++it) {
-              const uint32_t t0 = __float_as_uint((float)v0[it] - mu0);
+              const uint32_t t0 = __float_as_uint((float)v0[it] - mu0) + 0x1000u;
               if (CVEC == 2) {
-                const uint32_t t1 = __float_as_uint((float)v1[it] - mu1);
+                const uint32_t t1 = __float_as_uint((float)v1[it] - mu1) + 0x1000u;
                 asm volatile("st.shared.v2.u32 [%0], {%1,%2};" ::"r"(dst0 + (uint32_t)((it0 + it) * C_G * 16)), "r"(t0), "r"(t1) : "memory");
               } else sts_u32(dst0 + (uint32_t)((it0 + it) * C_G * 16), t0);
             }
@@ -395,7 +408,7 @@ __global__ void __launch_bounds__(tp_warps(WCFG) * 32, 1) lloyd_tp_kernel(const 
     const int grp = warp >> 2, wsub = warp & 3;
     const int row = 32 * wsub + lane;                              // tile row of this thread = TMEM lane
     const uint32_t tlane = ((uint32_t)(32 * wsub)) << 16;
-    const float kapv = 1.6f * 0.0009765625f * vmax;                // kappa * max|c - mu|
+    const float kapv = 1.04f * 0.0009765625f * vmax;               // kappa * max|c - mu|
     // eta * max 0.5|c - mu|^2 (eta = 2^-16), plus the fp32 rounding of x and mu ahead of the subtraction: 2^-24 (|x| + |mu|) per
     // feature, |x| <= |x - mu| + |mu| (the |x - mu| part is inside kappa's slack)
     const float etab = 0.5f * 1.52587890625e-05f * vmax * vmax + 2.5e-7f * munorm * vmax;
@@ -403,6 +416,8 @@ __global__ void __launch_bounds__(tp_warps(WCFG) * 32, 1) lloyd_tp_kernel(const 
     const bool conv2 = (d & 1) == 0;
     const int rlane = conv2 ? 2 * lane : lane;                     // refine: first feature of this lane
     const bool ract = rlane < d;
+    constexpr int RLANES = tp_dclass(ND) / CVEC > 32 ? 32 : tp_dclass(ND) / CVEC;   // lanes that hold features in the refine (power of two)
+    const double* Cr = L.cs_off != 0 ? reinterpret_cast<const double*>(smem + L.cs_off) : p.C;   // centres for the exact re-scoring
     int s = grp % S;
     for (int i = grp; i < T; i += SG) {
       const uint32_t b = (uint32_t)(i & 1), ph = (uint32_t)((i >> 1) & 1);
@@ -451,6 +466,7 @@ __global__ void __launch_bounds__(tp_warps(WCFG) * 32, 1) lloyd_tp_kernel(const 
       for (int q = 0; q < NW; ++q) w[q] = 0u;
       if (ambmask) {
         // sweep 2 (only when some row of the warp is undecided): every centre within 2 eps of the best is a candidate
+        const long long ts0 = prof ? clock64() : 0;
 #pragma unroll
         for (int ch = 0; ch < KP / 16; ++ch) {
           uint32_t v[16];
@@ -459,6 +475,7 @@ __global__ void __launch_bounds__(tp_warps(WCFG) * 32, 1) lloyd_tp_kernel(const 
 #pragma unroll
           for (int c = 0; c < 16; ++c) w[ch >> 1] |= (__uint_as_float(v[c]) >= thr) ? (1u << ((ch & 1) * 16 + c)) : 0u;
         }
+        if (prof) pw1 += clock64() - ts0;
       }
       // the TMEM buffer is free again
       asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -486,21 +503,32 @@ __global__ void __launch_bounds__(tp_warps(WCFG) * 32, 1) lloyd_tp_kernel(const 
           double x0 = 0.0, x1 = 0.0;
           if (ract) { if (conv2) lds_v2f64(ra, x0, x1); else x0 = lds_f64(ra); }
           double best = -__longlong_as_double(0x7ff0000000000000LL); int bj = -1;
+          // candidates in ascending index, four at a time: all centre loads first, then the four shuffle reductions interleaved
 #pragma unroll
           for (int q = 0; q < NW; ++q) {
             uint32_t msk = cm[q];
             while (msk) {
-              const int j = 32 * q + __ffs(msk) - 1; msk &= msk - 1;
-              double c0 = 0.0, c1 = 0.0;
-              if (ract) {
-                if (conv2) { const double2 cc = __ldg(reinterpret_cast<const double2*>(p.C + (size_t)j * d + rlane)); c0 = cc.x; c1 = cc.y; }
-                else c0 = __ldg(p.C + (size_t)j * d + rlane);
-              }
-              double sdot = fma(x0, c0, x1 * c1);
+              int jj[4]; double pp[4];
 #pragma unroll
-              for (int mk = 16; mk >= 1; mk >>= 1) sdot += shfl_xor_d(sdot, mk);
-              const double sc = sdot + cn_s[j];
-              if (sc > best) { best = sc; bj = j; }
+              for (int u = 0; u < 4; ++u) { jj[u] = msk ? 32 * q + __ffs(msk) - 1 : -1; msk &= msk - 1; }
+#pragma unroll
+              for (int u = 0; u < 4; ++u) {
+                double c0 = 0.0, c1 = 0.0;
+                if (ract && jj[u] >= 0) {
+                  const double* cr = Cr + (size_t)jj[u] * d + rlane;
+                  c0 = cr[0]; if (conv2) c1 = cr[1];
+                }
+                pp[u] = fma(x0, c0, x1 * c1);
+              }
+              // only the lanes below RLANES hold features: the butterfly starts at RLANES / 2 (lane 0 ends with the full sum)
+#pragma unroll
+              for (int mk = RLANES / 2; mk >= 1; mk >>= 1) {
+#pragma unroll
+                for (int u = 0; u < 4; ++u) pp[u] += shfl_xor_d(pp[u], mk);
+              }
+#pragma unroll
+              for (int u = 0; u < 4; ++u)
+                if (jj[u] >= 0) { const double sc = pp[u] + cn_s[jj[u]]; if (sc > best) { best = sc; bj = jj[u]; } }
             }
           }
           if (lane == 0) {

@@ -18,7 +18,7 @@ static int launch_tp(const LloydParams& p, const TpPlan& L, cudaStream_t st) {
     HKM_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
     if (dev < 64) attr_smem[dev] = L.total;
   }
-  kern<<<sm_count(), tp_warps(WCFG) * 32, L.total, st>>>(p, L);
+  kern<<<sm_count() * tp_ctas_per_sm(WCFG), tp_warps(WCFG) * 32, L.total, st>>>(p, L);
   HKM_CUDA_TRY(cudaGetLastError());
   return HKM_OK;
 }
@@ -46,9 +46,12 @@ int HKM_CAT(dispatch_lloyd_tp, HKM_TP_KP)(const LloydParams& p, const TpPlan& L,
   HKM_TP_TRY(1, 0, 1, 1, 4) HKM_TP_TRY(2, 0, 1, 1, 4) HKM_TP_TRY(1, 0, 0, 1, 4) HKM_TP_TRY(2, 0, 0, 1, 4)
   if constexpr (KP >= 48) { HKM_TP_TRY(1, 0, 2, 1, 4) HKM_TP_TRY(2, 0, 2, 1, 4) }
   // one shared set, clusters owned per warp (even d)
-  HKM_TP_TRY(2, 2, 0, 1, 8)
+  HKM_TP_TRY(2, 2, 0, 1, 8) HKM_TP_TRY(2, 2, 3, 1, 8)
   // one-hot DMMA (k <= 16)
-  if constexpr (KP == 16) { HKM_TP_TRY(1, 3, 1, 1, 4) HKM_TP_TRY(2, 3, 1, 1, 4) HKM_TP_TRY(2, 3, 0, 5, 8) }
+  if constexpr (KP == 16) {
+    HKM_TP_TRY(1, 3, 1, 1, 4) HKM_TP_TRY(2, 3, 1, 1, 4) HKM_TP_TRY(2, 3, 0, 1, 8)
+    HKM_TP_TRY(2, 3, 4, 1, 2) HKM_TP_TRY(2, 0, 4, 1, 2)     // two CTAs per SM (d <= 16)
+  }
 #undef HKM_TP_TRY
   set_error("lloyd_tp: no instantiation for d=%d k=%d (reduce mode %d, warp budget %d)", p.d, p.k, L.rmode, L.wcfg);
   return HKM_ERR_UNSUPPORTED;

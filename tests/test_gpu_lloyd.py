@@ -196,7 +196,9 @@ def test_tensor_core_variant_matches_oracle(hkm, oracle, n, d, k, offset, spread
     xs = torch.zeros(1, dtype=torch.float64, device="cuda")
     a = _pass(hkm._native, X, C, want=(), mode=1, xs=xs)
     b = _pass(hkm._native, X, C, want=(), mode=2, xs=xs)
-    assert np.array_equal(a["sums"], b["sums"]) and np.array_equal(a["wsum"], b["wsum"]) and np.array_equal(a["sums"], g["sums"])
+    assert np.array_equal(a["sums"], b["sums"]) and np.array_equal(a["wsum"], b["wsum"]) and np.array_equal(a["wsum"], g["wsum"])
+    # the pass that also returns per-row distances runs another kernel family: same rows per cluster, another summation order
+    assert np.abs(a["sums"] - g["sums"]).max() <= 1e-11 * max(1.0, np.abs(g["sums"]).max())
     assert b["cost"] == pytest.approx(cost, rel=1e-9, abs=1e-9 * float((X * X).sum()))
 
 
@@ -210,6 +212,71 @@ def test_tensor_core_variant_exact_ties(hkm, oracle):
     sums, wsum, cost, lab = oracle.lloyd_pass(X, C, P=1, want_labels=True)
     assert np.array_equal(g["labels"], lab) and wsum[7] == 0 and wsum[40] == 0 and wsum[20] == 0
     assert np.array_equal(g["sums"], sums) and np.array_equal(g["wsum"], wsum) and g["cost"] == cost
+
+
+# ---------------------------------------------------------------------------------------------
+# Pipelined tcgen05 variant (hkm_lloyd_tp.cuh): plain passes with k > 8 (labels and / or sums, no per-row distances).
+# Every reduce scheme it has (one-hot DMMA, private shared-memory sets, owned shared set) must give the oracle's labels,
+# sums, counts and cost, and the same results as the fp64 kernel families.
+# ---------------------------------------------------------------------------------------------
+TP_SHAPES = [(5000, 16, 16), (128, 16, 16), (100, 24, 9), (30011, 24, 17), (30000, 24, 32), (60000, 32, 64), (45000, 20, 50), (300000, 7, 33),
+             (20000, 64, 16), (20000, 64, 64), (6000, 48, 24), (4000, 62, 64), (9000, 12, 20), (3000, 31, 33), (70003, 5, 12), (33333, 2, 10),
+             (2000, 1, 9), (65, 64, 64), (200000, 16, 16)]
+
+
+@pytest.mark.parametrize("variant", [4, 40, 42, 43])
+@pytest.mark.parametrize("n,d,k", TP_SHAPES)
+def test_pipelined_variant_matches_oracle(hkm, oracle, n, d, k, variant):
+    if variant == 40 and d > 32 or variant == 42 and d % 2 or variant == 43 and (k > 16 or (d > 32 and d % 2)) or variant == 4 and d > 32 and d % 2:
+        pytest.skip("scheme not built for this shape")
+    N = hkm._native
+    rng = np.random.default_rng(n + 31 * d + 977 * k)
+    prof = rng.normal(size=(k, d)) * 1.5 + 3.0                       # a common offset, as withMean=False tables have
+    X = prof[rng.integers(0, k, size=n)] + rng.normal(size=(n, d))
+    C = prof + 0.05 * rng.normal(size=(k, d))
+    sums, wsum, cost, lab = oracle.lloyd_pass(X, C, P=1, want_labels=True)
+    N.set_lloyd_variant(variant)
+    try:
+        xs = torch.zeros(1, dtype=torch.float64, device="cuda")
+        a = _pass(N, X, C, want=("labels",))
+        b = _pass(N, X, C, want=(), mode=1, xs=xs)
+        c = _pass(N, X, C, want=(), mode=2, xs=xs)
+        Xd = torch.from_numpy(X).cuda(); Cd = torch.from_numpy(C).cuda()
+        pred = torch.full((n,), -5, dtype=torch.int32, device="cuda")
+        N.assign_reduce(Xd, Cd, None, pred, do_reduce=False)
+        N.set_lloyd_variant(5)
+        ref = _pass(N, X, C, want=("labels",))
+    finally:
+        N.set_lloyd_variant(0)
+    assert np.array_equal(a["labels"], lab) and np.array_equal(pred.cpu().numpy(), lab) and np.array_equal(ref["labels"], lab)
+    assert np.array_equal(a["wsum"], wsum)
+    assert np.abs(a["sums"] - sums).max() <= 1e-11 * max(1.0, np.abs(sums).max())
+    assert a["cost"] == pytest.approx(cost, rel=1e-9) and c["cost"] == pytest.approx(cost, rel=1e-9)
+    assert np.array_equal(a["sums"], b["sums"]) and a["cost"] == b["cost"] and np.array_equal(a["sums"], c["sums"])
+    assert xs.item() == pytest.approx(float((X * X).sum()), rel=1e-12)
+    assert a["cost"] == pytest.approx(ref["cost"], rel=1e-10)
+
+
+def test_pipelined_variant_near_ties_and_exact_ties(hkm, oracle):
+    """Centres that nearly coincide (most rows undecided by the tf32 screen -> exact fp64 re-scoring), a large common offset (loose
+    bound), and exact ties on an integer lattice (lowest index must win)."""
+    N = hkm._native
+    rng = np.random.default_rng(12)
+    for n, d, k, offset, spread in [(40_000, 16, 16, 0.0, 0.02), (30_000, 24, 32, 40.0, 1.0), (20_011, 32, 64, 3.0, 0.05), (30_000, 64, 40, 25.0, 1.0)]:
+        prof = rng.normal(size=(k, d)) * spread + offset
+        X = prof[rng.integers(0, k, size=n)] + rng.normal(size=(n, d))
+        C = prof + 0.05 * rng.normal(size=(k, d))
+        g = _pass(N, X, C, want=("labels",))
+        sums, wsum, cost, lab = oracle.lloyd_pass(X, C, P=1, want_labels=True)
+        assert np.array_equal(g["labels"], lab) and np.array_equal(g["wsum"], wsum)
+        assert g["cost"] == pytest.approx(cost, rel=1e-9, abs=1e-9 * float((X * X).sum()))
+    X = rng.integers(-2, 3, size=(30_000, 12)).astype(np.float64)
+    C = rng.integers(-2, 3, size=(14, 12)).astype(np.float64)
+    C[7] = C[3]; C[12] = C[3]; C[9] = C[1]
+    g = _pass(N, X, C, want=("labels",))
+    sums, wsum, cost, lab = oracle.lloyd_pass(X, C, P=1, want_labels=True)
+    assert np.array_equal(g["labels"], lab) and wsum[7] == 0 and wsum[12] == 0 and wsum[9] == 0
+    assert np.array_equal(g["sums"], sums) and np.array_equal(g["wsum"], wsum) and g["cost"] == pytest.approx(cost, rel=1e-12)
 
 
 @pytest.mark.parametrize("n,d,k", [(400_000, 24, 32), (300_001, 16, 48), (250_000, 32, 64), (300_000, 32, 8), (300_000, 16, 16)])

@@ -101,16 +101,25 @@ def bench(shapes, iters=10, extra=()):
 ROLE = ["screen"] * 8 + ["reduce"] * 4 + ["convert"] * 4 + ["producer", "mma"]
 
 
-def prof(shapes, iters=3):
+def prof(shapes, iters=3, hospital=False):
     """Per-warp cycle breakdown of CTA 0: where each role waits (site 0/1), refine cycles, listed rows."""
     import ctypes
     np, torch, N, O = _mods()
     N.set_lloyd_variant(4)
     for n, d, k in shapes:
         g = torch.Generator(device="cuda"); g.manual_seed(1)
-        prof_c = torch.randn(k, d, dtype=torch.float64, device="cuda", generator=g) * 2
-        X = prof_c[torch.randint(0, k, (n,), device="cuda", generator=g)] + torch.randn(n, d, dtype=torch.float64, device="cuda", generator=g)
-        C = prof_c + 0.1
+        if hospital:        # bench.py's table and centres: first k rows, then 10 Lloyd steps
+            import hkm_b200
+            from hkm_b200 import datagen
+            X = datagen.hospital_matrix_device(n, d, k, 20250331, torch.device("cuda"))
+            C = X[:k].clone()
+            pp = torch.empty(k * d + k + 1, dtype=torch.float64, device="cuda"); sc = N.new_scratch(d, k, "cuda"); st = N.new_state("cuda")
+            for _ in range(10):
+                N.lloyd_step(X, C, pp, -1.0, st, sc)
+        else:
+            prof_c = torch.randn(k, d, dtype=torch.float64, device="cuda", generator=g) * 2
+            X = prof_c[torch.randint(0, k, (n,), device="cuda", generator=g)] + torch.randn(n, d, dtype=torch.float64, device="cuda", generator=g)
+            C = prof_c + 0.1
         partial = torch.empty(k * d + k + 1, dtype=torch.float64, device="cuda"); scratch = N.new_scratch(d, k, "cuda")
         xs = torch.zeros(1, dtype=torch.float64, device="cuda")
         buf = torch.zeros(18 * 8, dtype=torch.int64, device="cuda")
@@ -127,7 +136,7 @@ def prof(shapes, iters=3):
         for w in range(18):
             if b[w, 0] == 0:
                 continue
-            print(f"  warp {w:2d} {ROLE[w]:8s} total/tile {b[w, 0] / tiles:8.1f}  wait0 {b[w, 1] / tiles:8.1f}  wait1 {b[w, 2] / tiles:8.1f}  refine {b[w, 3] / tiles:7.1f}  listed/tile {b[w, 5] / tiles:6.2f}")
+            print(f"  warp {w:2d} total/tile {b[w, 0] / tiles:8.1f}  wait0 {b[w, 1] / tiles:8.1f}  wait1 {b[w, 2] / tiles:8.1f}  refine {b[w, 3] / tiles:7.1f}  refined rows/tile {b[w, 5] / tiles:6.2f}")
         sys.stdout.flush()
         del X
     N.set_lloyd_variant(0)
@@ -151,7 +160,8 @@ if __name__ == "__main__":
         torch.cuda.synchronize()
         sys.exit(0)
     if cmd == "prof":
-        prof([(20_000_000, 16, 16), (5_000_000, 24, 32), (20_000_000, 64, 64), (5_000_000, 24, 64)])
+        prof([(20_000_000, 16, 16), (5_000_000, 24, 32), (20_000_000, 64, 64), (5_000_000, 24, 64)] if "hospital" not in sys.argv else
+             [(20_000_000, 16, 16), (20_000_000, 64, 64), (5_000_000, 24, 16)], hospital="hospital" in sys.argv)
         sys.exit(0)
     if cmd == "one":
         sys.exit(0 if one(int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4]), tpv=int(sys.argv[5]) if len(sys.argv) > 5 else 4) else 1)
@@ -178,4 +188,6 @@ if __name__ == "__main__":
         extra = []
         if "modes" in sys.argv:
             extra = [(42, "tp_own"), (40, "tp_priv")]
+        if "budgets" in sys.argv:
+            extra = [(50, "w0"), (51, "w1"), (53, "w3"), (54, "w4_2cta")]
         bench(BENCH_SHAPES + (WIDE if "wide" in sys.argv else []), extra=extra)
