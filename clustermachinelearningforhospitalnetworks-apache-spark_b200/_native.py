@@ -14,11 +14,11 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(_HERE, "csrc", "libhkm.so")
 
 EXPORTS = (
-    "hkm_last_error", "hkm_version", "hkm_max_k", "hkm_max_d", "hkm_set_lloyd_variant",
+    "hkm_last_error", "hkm_version", "hkm_max_k", "hkm_max_k_single_pass", "hkm_max_d", "hkm_needs_workspace", "hkm_set_lloyd_variant",
     "hkm_assign_reduce_scratch_bytes", "hkm_assign_reduce", "hkm_update_centers", "hkm_update_centers_cosine", "hkm_lloyd_step", "hkm_lloyd_step_peer", "hkm_peer_exchange_bytes", "hkm_peer_exchange_slot_doubles",
     "hkm_kmpar_scratch_bytes", "hkm_kmpar_cost_update", "hkm_kmpar_sample", "hkm_kmpar_strip_rows", "hkm_closest_counts",
-    "hkm_silhouette_stats", "hkm_silhouette_score",
-    "hkm_assemble_scratch_bytes", "hkm_assemble", "hkm_moments_scratch_bytes", "hkm_moments", "hkm_column_moments", "hkm_scale_rows", "hkm_normalize_rows", "hkm_local_kmeanspp",
+    "hkm_silhouette_stats", "hkm_silhouette_score", "hkm_label_range",
+    "hkm_assemble_scratch_bytes", "hkm_assemble", "hkm_assemble_filtered", "hkm_fill_f64", "hkm_moments_scratch_bytes", "hkm_moments", "hkm_column_moments", "hkm_scale_rows", "hkm_normalize_rows", "hkm_local_kmeanspp",
 )
 
 _lib = None
@@ -64,6 +64,8 @@ def load() -> ctypes.CDLL:
         L.hkm_assemble_scratch_bytes.restype = sz
         L.hkm_assemble_scratch_bytes.argtypes = [i64]
         L.hkm_assemble.argtypes = [vp, vp, vp, vp, i32, i64, vp, vp, i32, vp, vp, vp, vp, sz, vp]
+        L.hkm_assemble_filtered.argtypes = [vp, vp, vp, vp, i32, i64, vp, vp, vp, vp, i64, i64, vp, i32, vp, vp, vp, vp, vp, vp, sz, vp]
+        L.hkm_fill_f64.argtypes = [vp, i64, ctypes.c_double, vp]
         L.hkm_moments_scratch_bytes.restype = sz
         L.hkm_moments_scratch_bytes.argtypes = [i32]
         L.hkm_moments.argtypes = [vp, i64, i32, vp, vp, vp, sz, vp]
@@ -72,6 +74,7 @@ def load() -> ctypes.CDLL:
         L.hkm_normalize_rows.argtypes = [vp, vp, i64, i32, vp, vp]
         L.hkm_local_kmeanspp.argtypes = [ctypes.c_int32, vp, vp, i32, i32, i32, i32, vp]
         L.hkm_silhouette_stats.argtypes = [vp, vp, vp, i64, i32, i32, vp, vp, sz, vp]
+        L.hkm_label_range.argtypes = [vp, i64, vp, vp]
         L.hkm_silhouette_score.argtypes = [vp, vp, vp, i64, i32, i32, vp, vp, vp, vp, sz, vp]
         _lib = L
     return _lib
@@ -130,6 +133,14 @@ def assign_reduce(X, C, partial=None, labels=None, mind2=None, weights=None, sta
     require_cuda(C, "C", torch.float64)
     n, d = X.shape
     k = C.shape[0]
+    if load().hkm_needs_workspace(d, k):
+        # more centres than one launch scores, or a shape outside the tiled kernels: the library runs the pass in chunks of
+        # centres and needs per-row workspace
+        if labels is None:
+            labels = torch.empty(n, dtype=torch.int32, device=X.device)
+        if mind2 is None:
+            mind2 = torch.empty(n, dtype=torch.float64, device=X.device)
+        xnorm2_sum, xnorm2_mode = None, 0
     with torch.cuda.device(X.device):
         rc = load().hkm_assign_reduce(_ptr(X), n, d, _ptr(C), k, _ptr(weights), _ptr(partial), _ptr(labels), _ptr(mind2),
                                       _ptr(xnorm2_sum), int(xnorm2_mode), _ptr(state), int(do_reduce), _ptr(scratch),
@@ -210,6 +221,16 @@ def closest_counts(X, cand, labels_work, mind2_work, counts_out):
     _check(rc)
 
 
+def label_range(labels):
+    """(min, max) of an int32 device column in one pass (hkm_label_range); (None, None) for an empty column."""
+    require_cuda(labels, "labels", torch.int32)
+    out = torch.empty(2, dtype=torch.int32, device=labels.device)
+    with torch.cuda.device(labels.device):
+        _check(load().hkm_label_range(_ptr(labels), labels.numel(), _ptr(out), _stream()))
+    lo, hi = out.cpu().tolist()
+    return (None, None) if labels.numel() == 0 else (lo, hi)
+
+
 def silhouette_stats(X, labels, k, stats_out, scratch, weights=None):
     require_cuda(X, "X", torch.float64); require_cuda(labels, "labels", torch.int32)
     n, d = X.shape
@@ -268,6 +289,43 @@ def assemble(cols, valids, n, shift=None, scale=None, skip_invalid=False):
         return X, n, invalid          # no host sync: every row is kept; `invalid` is a device counter the caller may read
     n_keep, bad = int(n_out.item()), int(invalid.item())
     return X[:n_keep], n_keep, bad
+
+
+def assemble_filtered(cols, valids, n, window=None, extra_valid=(), shift=None, scale=None):
+    """hkm_assemble_filtered: WHERE ts BETWEEN lo AND hi + na.drop + VectorAssembler (+ scaling) in one compaction.
+    window = (ts int64 device tensor, validity byte tensor or None, lo, hi) or None; extra_valid = validity byte tensors of
+    columns that are not features.  Returns (X, keep mask (uint8 device tensor), rows outside the window, null rows inside it)."""
+    d = len(cols)
+    dev = cols[0].device
+    ptrs, dts, vptrs, vk = _col_tables(cols, valids)
+    X = torch.empty((n, d), dtype=torch.float64, device=dev)
+    n_out = torch.zeros(1, dtype=torch.int64, device=dev)
+    counts = torch.zeros(2, dtype=torch.int64, device=dev)
+    keep = torch.zeros(n, dtype=torch.uint8, device=dev)
+    ev = (ctypes.c_void_p * max(len(extra_valid), 1))()
+    for i, v in enumerate(extra_valid):
+        require_cuda(v, f"extra validity {i}", torch.uint8)
+        ev[i] = v.data_ptr()
+    ts, tsv, lo, hi = window if window is not None else (None, None, 0, 0)
+    if ts is not None:
+        require_cuda(ts, "window column", torch.int64)
+    with torch.cuda.device(dev):
+        sb = int(load().hkm_assemble_scratch_bytes(n))
+        scratch = torch.empty((sb + 7) // 8, dtype=torch.int64, device=dev)
+        rc = load().hkm_assemble_filtered(ptrs, dts, vptrs, vk, d, n, _ptr(shift), _ptr(scale), _ptr(ts), _ptr(tsv), int(lo), int(hi), ev, len(extra_valid),
+                                          _ptr(X), _ptr(n_out), ctypes.c_void_p(counts.data_ptr()), ctypes.c_void_p(counts.data_ptr() + 8), _ptr(keep),
+                                          _ptr(scratch), sb, _stream())
+    _check(rc)
+    n_keep = int(n_out.item())
+    bad, outside = counts.cpu().tolist()
+    return X[:n_keep], keep, outside, bad
+
+
+def fill_f64(t, value: float) -> None:
+    """hkm_fill_f64: t[:] = value on the current stream."""
+    require_cuda(t, "tensor", torch.float64)
+    with torch.cuda.device(t.device):
+        _check(load().hkm_fill_f64(_ptr(t), t.numel(), float(value), _stream()))
 
 
 def count_invalid_rows(cols, valids, n) -> int:

@@ -63,27 +63,29 @@ __global__ void update_centers_cosine_kernel(const double* __restrict__ partial,
   __shared__ double s_shift[64];
   const int tid = threadIdx.x;
   double shift = -1.0;
-  if (tid < k) {
-    const double wsum = partial[(size_t)k * d + tid];
-    if (wsum > 0) {
-      const double inv = 1.0 / wsum;
-      double nn = 0, oo = 0;
-      for (int f = 0; f < d; ++f) { const double v = partial[(size_t)tid * d + f] * inv; nn = fma(v, v, nn); const double o = C[(size_t)tid * d + f]; oo = fma(o, o, oo); }
-      const double inv2 = 1.0 / sqrt(nn), on = sqrt(oo);
-      double dot = 0;
-      for (int f = 0; f < d; ++f) {
-        const double nc = partial[(size_t)tid * d + f] * inv * inv2;
-        dot = fma(C[(size_t)tid * d + f], nc, dot);
-        C[(size_t)tid * d + f] = nc;
+  if (tid < 64) {
+    for (int j = tid; j < k; j += 64) {
+      const double wsum = partial[(size_t)k * d + j];
+      if (wsum > 0) {
+        const double inv = 1.0 / wsum;
+        double nn = 0, oo = 0;
+        for (int f = 0; f < d; ++f) { const double v = partial[(size_t)j * d + f] * inv; nn = fma(v, v, nn); const double o = C[(size_t)j * d + f]; oo = fma(o, o, oo); }
+        const double inv2 = 1.0 / sqrt(nn), on = sqrt(oo);
+        double dot = 0;
+        for (int f = 0; f < d; ++f) {
+          const double nc = partial[(size_t)j * d + f] * inv * inv2;
+          dot = fma(C[(size_t)j * d + f], nc, dot);
+          C[(size_t)j * d + f] = nc;
+        }
+        shift = fmax(shift, fmax(1.0 - dot / on, 0.0));
       }
-      shift = fmax(1.0 - dot / on, 0.0);
     }
+    s_shift[tid] = shift;
   }
-  if (tid < 64) s_shift[tid] = shift;
   __syncthreads();
   if (tid == 0) {
     double mx = -1.0;
-    for (int i = 0; i < k; ++i) mx = fmax(mx, s_shift[i]);
+    for (int i = 0; i < 64; ++i) mx = fmax(mx, s_shift[i]);
     state->cost = 0.5 * partial[(size_t)k * d + k];
     state->iter += 1;
     state->max_shift2 = mx < 0 ? 0.0 : mx;
@@ -95,10 +97,38 @@ __global__ void update_centers_cosine_kernel(const double* __restrict__ partial,
 
 namespace hkm {
 
+constexpr int kMaxFastK = 64;     // centres one launch handles; larger k runs in chunks (assign_pass_large)
+constexpr int kMaxFastD = 96;     // widest row of the tiled kernels; wider rows take the general kernels (hkm_generic.cu)
+
+// general-shape kernels (hkm_generic.cu)
+int generic_chunk_k(int d);
+size_t generic_scratch_bytes(int d);
+int generic_assign(const double* X, int64_t n, int d, const double* C, int k, int32_t* labels, double* mind2, int out_mode, int label_base,
+                   const int32_t* skip, double* cost_out, void* scratch, cudaStream_t st);
+int generic_reduce(const double* X, int64_t n, int d, int kc, const int32_t* labels, int label_base, const double* w, const double* mind2,
+                   const int32_t* skip, void* scratch, double* stats, cudaStream_t st);
+
+// the tiled (TMA ring) kernels take (d, k) when the row fits and at least two ring stages do
+static bool fits_fast(int d, int k) {
+  if (d > kMaxFastD || k > kMaxFastK) return false;
+  return plan_lloyd(d, ((k + 7) / 8) * 8).stages >= 2;
+}
+
 int assign_pass(const AssignArgs& a, const char* who) {
   const int d = a.d, k = a.k;
   if (a.n < 0 || d < 1 || k < 1 || (a.n > 0 && a.X == nullptr) || a.C == nullptr) { set_error("%s: bad X/C/n/d/k", who); return HKM_ERR_INVALID; }
-  if (d > hkm_max_d() || k > hkm_max_k()) { set_error("%s: d=%d k=%d outside fp64 kernel range (d<=%d, k<=%d)", who, d, k, hkm_max_d(), hkm_max_k()); return HKM_ERR_UNSUPPORTED; }
+  if (d > hkm_max_d() || k > kMaxFastK) { set_error("%s: d=%d k=%d outside fp64 kernel range (d<=%d, k<=%d per launch)", who, d, k, hkm_max_d(), kMaxFastK); return HKM_ERR_UNSUPPORTED; }
+  if (!fits_fast(d, k)) {
+    // general kernels: label / distance passes (plain or running-minimum) and the labels-given statistics of one chunk
+    cudaStream_t st = reinterpret_cast<cudaStream_t>(a.stream);
+    const int32_t* skip = a.state ? &a.state->converged : nullptr;
+    if (a.mode == 0 && a.weights == nullptr && a.do_reduce != 1 && a.C_update == nullptr && a.peer_bufs == nullptr) {
+      if (a.do_reduce == 2 && (a.partial_out == nullptr || a.scratch == nullptr || a.scratch_bytes < generic_scratch_bytes(d))) { set_error("%s: cost sum needs partial_out and scratch", who); return HKM_ERR_INVALID; }
+      return generic_assign(a.X, a.n, d, a.C, k, a.labels_out, a.mind2_out, a.out_mode, a.label_base, skip, a.do_reduce == 2 ? a.partial_out : nullptr, a.scratch, st);
+    }
+    set_error("%s: d=%d k=%d does not fit the tiled kernels (%s); this entry point has no general-shape path", who, d, k, d > kMaxFastD ? "d > 96" : "shared-memory ring");
+    return HKM_ERR_UNSUPPORTED;
+  }
   if ((reinterpret_cast<uintptr_t>(a.X) & 15) != 0) { set_error("%s: X must be 16-byte aligned", who); return HKM_ERR_INVALID; }
   if (a.do_reduce && (a.partial_out == nullptr || a.scratch == nullptr)) { set_error("%s: reduce needs partial_out and scratch", who); return HKM_ERR_INVALID; }
   if (a.do_reduce && a.scratch_bytes < hkm_assign_reduce_scratch_bytes(d, k)) { set_error("%s: scratch too small (%zu < %zu)", who, a.scratch_bytes, hkm_assign_reduce_scratch_bytes(d, k)); return HKM_ERR_INVALID; }
@@ -128,6 +158,82 @@ int assign_pass(const AssignArgs& a, const char* who) {
   return dispatch_lloyd(p, pl, grid, mode, reinterpret_cast<cudaStream_t>(a.stream));
 }
 
+// ------------------------------------------------------------------ k > 64: the pass in chunks of 64 centres
+constexpr int kChunkK = 64;
+__global__ void fill_inf_kernel(double* p, int64_t n) {
+  const double inf = __longlong_as_double(0x7ff0000000000000LL);
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = inf;
+}
+// chunk statistics [kc*d sums][kc N][-][kc Psi] -> rows c0 .. c0 + kc of partial_out's layout [k*d][k][cost]; the chunk's share of
+// cost = sum_j (Psi_j - 2 S_j.c_j + N_j |c_j|^2) = sum w |x - c_label|^2 is added to partial_out[k*d + k]
+// (cost_given: the general kernels hand the chunk's cost over directly, in the slot after the weights)
+__global__ void place_chunk_kernel(const double* __restrict__ st, int kc, int c0, int k, int d, const double* __restrict__ C, double* __restrict__ out, int cost_given) {
+  __shared__ double s_cost[256];
+  const int Pc = kc * d + kc + 1;
+  double cost = 0;
+  for (int i = threadIdx.x; i < kc * d; i += blockDim.x) out[(size_t)c0 * d + i] = st[i];
+  for (int j = threadIdx.x; j < kc; j += blockDim.x) {
+    const double N = st[kc * d + j];
+    out[(size_t)k * d + c0 + j] = N;
+    if (!cost_given) {
+      double sc = 0, cc = 0;
+      for (int f = 0; f < d; ++f) { const double c = C[(size_t)(c0 + j) * d + f]; sc = fma(st[j * d + f], c, sc); cc = fma(c, c, cc); }
+      cost += st[Pc + j] - 2.0 * sc + N * cc;
+    }
+  }
+  s_cost[threadIdx.x] = cost;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0;
+    for (int i = 0; i < (int)blockDim.x; ++i) t += s_cost[i];
+    if (cost_given) t = st[kc * d + kc];
+    out[(size_t)k * d + k] = (c0 == 0 ? 0.0 : out[(size_t)k * d + k]) + fmax(t, 0.0);
+  }
+}
+
+// One data pass for k > 64: running-minimum assignment over chunks of 64 centres (strict '<': the lower index keeps a tie, as
+// findClosest), then -- when sums are wanted -- the labels-given statistics pass per chunk.  Needs labels_out and mind2_out as
+// per-row workspace.  2 (or 1) passes over X per chunk: a general path, not a fast one.
+static int assign_pass_large(const AssignArgs& a, const char* who) {
+  const int d = a.d, k = a.k;
+  if (d < 1 || k < 1 || d > hkm_max_d() || k > hkm_max_k() || a.n < 0 || (a.n > 0 && a.X == nullptr) || a.C == nullptr) { set_error("%s: bad X/C/n/d/k (d <= %d, k <= %d)", who, hkm_max_d(), hkm_max_k()); return HKM_ERR_INVALID; }
+  const bool general = !fits_fast(d, k < kChunkK ? k : kChunkK);       // the chunks themselves do not fit the tiled kernels
+  const int chunk = general ? generic_chunk_k(d) : kChunkK;
+  if (a.labels_out == nullptr || a.mind2_out == nullptr) { set_error("%s: d=%d k=%d runs in centre chunks (k > %d, or a shape outside the tiled kernels) and needs labels_out and mind2_out (n entries each) as workspace", who, d, k, kChunkK); return HKM_ERR_INVALID; }
+  if (a.mode != 0 || a.out_mode != 0 || a.C_update != nullptr || a.peer_bufs != nullptr) { set_error("%s: k=%d > %d supports plain passes only", who, k, kChunkK); return HKM_ERR_UNSUPPORTED; }
+  if (a.do_reduce && (a.partial_out == nullptr || a.scratch == nullptr || a.scratch_bytes < hkm_assign_reduce_scratch_bytes(d, k))) { set_error("%s: reduce needs partial_out and scratch of hkm_assign_reduce_scratch_bytes(d, k)", who); return HKM_ERR_INVALID; }
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(a.stream);
+  if (a.n > 0) { fill_inf_kernel<<<sm_count() * 4, 256, 0, st>>>(a.mind2_out, a.n); HKM_CUDA_TRY(cudaGetLastError()); }
+  for (int c0 = 0; c0 < k; c0 += chunk) {
+    AssignArgs b{};
+    b.X = a.X; b.n = a.n; b.d = d; b.C = a.C + (size_t)c0 * d; b.k = (k - c0 < chunk) ? (k - c0) : chunk;
+    b.labels_out = a.labels_out; b.mind2_out = a.mind2_out; b.do_reduce = 0; b.out_mode = 1; b.label_base = c0; b.state = a.state; b.stream = a.stream;
+    const int rc = assign_pass(b, who);
+    if (rc != HKM_OK) return rc;
+  }
+  if (!a.do_reduce) return HKM_OK;
+  const int32_t* skip = a.state ? &a.state->converged : nullptr;
+  // chunk statistics land behind the per-CTA partials of one chunk pass
+  const size_t chunk_scratch = general ? generic_scratch_bytes(d) : hkm_assign_reduce_scratch_bytes(d, kChunkK);
+  double* stats = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(a.scratch) + chunk_scratch);
+  for (int c0 = 0; c0 < k; c0 += chunk) {
+    const int kc = (k - c0 < chunk) ? (k - c0) : chunk;
+    if (a.n == 0) HKM_CUDA_TRY(cudaMemsetAsync(stats, 0, sizeof(double) * ((size_t)kc * d + 2 * (size_t)kc + 1), st));
+    else if (general) {
+      const int rc = generic_reduce(a.X, a.n, d, kc, a.labels_out, c0, a.weights, a.mind2_out, skip, a.scratch, stats, st);
+      if (rc != HKM_OK) return rc;
+    } else {
+      AssignArgs b{};
+      b.X = a.X; b.n = a.n; b.d = d; b.C = a.X; b.k = kc; b.weights = a.weights; b.partial_out = stats; b.do_reduce = 1; b.mode = 1;
+      b.labels_in = a.labels_out; b.label_base = c0; b.state = a.state; b.scratch = a.scratch; b.scratch_bytes = chunk_scratch; b.stream = a.stream;
+      const int rc = assign_pass(b, who); if (rc != HKM_OK) return rc;
+    }
+    place_chunk_kernel<<<1, 256, 0, st>>>(stats, kc, c0, k, d, a.C, a.partial_out, general && a.n > 0 ? 1 : 0);
+    HKM_CUDA_TRY(cudaGetLastError());
+  }
+  return HKM_OK;
+}
+
 }  // namespace hkm
 
 using namespace hkm;
@@ -136,8 +242,10 @@ extern "C" {
 
 const char* hkm_last_error(void) { return g_err; }
 int hkm_version(void) { return 100; }
-int hkm_max_k(void) { return 64; }
-int hkm_max_d(void) { return 96; }
+int hkm_max_k(void) { return 4096; }
+int hkm_max_k_single_pass(void) { return 64; }
+int hkm_max_d(void) { return 4096; }
+int hkm_needs_workspace(int d, int k) { return (k > kMaxFastK || !fits_fast(d, k)) ? 1 : 0; }
 int hkm_set_lloyd_variant(int variant) {
   if (!((variant >= 0 && variant <= 5) || (variant == 40 || variant == 42 || variant == 43) || (variant >= 50 && variant <= 54))) { set_error("hkm_set_lloyd_variant: 0..5 (40..43 / 50..54: variant 4 with a pinned reduce scheme / warp budget)"); return HKM_ERR_INVALID; }
   g_lloyd_variant = variant;
@@ -146,6 +254,8 @@ int hkm_set_lloyd_variant(int variant) {
 
 size_t hkm_assign_reduce_scratch_bytes(int d, int k) {
   if (d < 1 || k < 1) return 0;
+  if (!fits_fast(d, k < 64 ? k : 64)) return generic_scratch_bytes(d) + ((size_t)64 * d + 2 * 64 + 2) * sizeof(double);   // general kernels: CTA partials + chunk statistics
+  if (k > 64) return hkm_assign_reduce_scratch_bytes(d, 64) + ((size_t)64 * d + 2 * 64 + 2) * sizeof(double);   // chunk pass + chunk statistics
   const int k_pad = ((k + 7) / 8) * 8;
   LaunchPlan pl = plan_lloyd(d, k_pad);
   size_t grid = (size_t)sm_count() * (pl.ctas_per_sm > 2 ? pl.ctas_per_sm : 2);   // every variant launches at most this many CTAs
@@ -159,13 +269,15 @@ int hkm_assign_reduce(const double* X, int64_t n, int d, const double* C, int k,
   a.X = X; a.n = n; a.d = d; a.C = C; a.k = k; a.weights = weights; a.partial_out = partial_out; a.labels_out = labels_out;
   a.mind2_out = mind2_out; a.xnorm2_sum = xnorm2_sum; a.xnorm2_mode = xnorm2_mode; a.state = state; a.do_reduce = do_reduce ? 1 : 0;
   a.scratch = scratch; a.scratch_bytes = scratch_bytes; a.stream = stream;
+  if (k > 64 || (d >= 1 && k >= 1 && !fits_fast(d, k))) return assign_pass_large(a, "hkm_assign_reduce");
   return assign_pass(a, "hkm_assign_reduce");
 }
 
 int hkm_lloyd_step(const double* X, int64_t n, int d, double* C_inout, int k, const double* weights, double* partial_out,
                    double* xnorm2_sum, int xnorm2_mode, double tol, hkm_lloyd_state* state, void* scratch, size_t scratch_bytes,
                    void* stream) {
-  if (state == nullptr || C_inout == nullptr || k > 64) { set_error("hkm_lloyd_step: bad arguments"); return HKM_ERR_INVALID; }
+  if (state == nullptr || C_inout == nullptr) { set_error("hkm_lloyd_step: bad arguments"); return HKM_ERR_INVALID; }
+  if (k > 64) { set_error("hkm_lloyd_step: k=%d > 64 has no fused step; use hkm_assign_reduce + hkm_update_centers", k); return HKM_ERR_UNSUPPORTED; }
   AssignArgs a{};
   a.X = X; a.n = n; a.d = d; a.C = C_inout; a.k = k; a.weights = weights; a.partial_out = partial_out; a.xnorm2_sum = xnorm2_sum;
   a.xnorm2_mode = xnorm2_mode; a.state = state; a.do_reduce = 1; a.scratch = scratch; a.scratch_bytes = scratch_bytes; a.stream = stream;

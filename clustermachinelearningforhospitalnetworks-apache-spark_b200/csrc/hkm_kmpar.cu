@@ -173,6 +173,12 @@ int hkm_kmpar_sample(const double* costs, int64_t n, const int64_t* part_rows, c
 
 int hkm_kmpar_strip_rows(void) { return kStripRows; }
 
+int hkm_fill_f64(double* p, int64_t n, double value, void* stream) {
+  if (n < 0 || (n > 0 && p == nullptr)) { set_error("hkm_fill_f64: bad arguments"); return HKM_ERR_INVALID; }
+  if (n > 0) { fill_double_kernel<<<sm_count() * 4, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(p, n, value); HKM_CUDA_TRY(cudaGetLastError()); }
+  return HKM_OK;
+}
+
 int hkm_closest_counts(const double* X, int64_t n, int d, const double* cand, int m, int32_t* labels_work, double* mind2_work,
                        unsigned long long* counts_out, void* stream) {
   if (m < 1 || labels_work == nullptr || mind2_work == nullptr || counts_out == nullptr) { set_error("hkm_closest_counts: bad arguments"); return HKM_ERR_INVALID; }

@@ -46,7 +46,7 @@ struct LloydParams {
   const int32_t* labels_in;  // MODE 1/2 (silhouette): given cluster ids; ids outside [0, k) are ignored
   const double* aux;         // MODE 2: [k] cluster weight sums N, then [k] Psi/N
   int out_mode;            // 0: labels/mind2 are written; 1: mind2_out = min(mind2_out, new), labels follow the winner
-  int label_base;          // added to labels written in out_mode 1 (centre chunk offset)
+  int label_base;          // added to labels written in out_mode 1, subtracted from labels_in in MODE 1 (centre chunk offset)
   double* xnorm2_sum;      // see xx_mode
   int xx_mode;             // 0: per-row |x|^2 in-pass; 1: same, and store sum_w|x|^2; 2: reuse stored sum, skip per-row norms
   double* C_update;        // nullable: fused driver step -- the last CTA also updates these centres in place
@@ -69,25 +69,27 @@ struct LloydParams {
 __device__ __forceinline__ void update_centers_body(const double* partial, int k, int d, double* C, double tol2,
                                                     hkm_lloyd_state* state, double* s_shift, int tid) {
   double shift = -1.0;
-  if (tid < k) {
-    const double wsum = partial[(size_t)k * d + tid];
-    if (wsum > 0) {
-      const double inv = 1.0 / wsum;  // scal(1.0 / weightSum, sum)
-      double s = 0;
-      for (int f = 0; f < d; ++f) {
-        const double nc = partial[(size_t)tid * d + f] * inv;
-        const double df = nc - C[(size_t)tid * d + f];
-        s = fma(df, df, s);
-        C[(size_t)tid * d + f] = nc;
+  if (tid < 64) {
+    for (int j = tid; j < k; j += 64) {                    // k <= 64 in the fused kernels; the stand-alone launch takes any k
+      const double wsum = partial[(size_t)k * d + j];
+      if (wsum > 0) {
+        const double inv = 1.0 / wsum;  // scal(1.0 / weightSum, sum)
+        double s = 0;
+        for (int f = 0; f < d; ++f) {
+          const double nc = partial[(size_t)j * d + f] * inv;
+          const double df = nc - C[(size_t)j * d + f];
+          s = fma(df, df, s);
+          C[(size_t)j * d + f] = nc;
+        }
+        shift = fmax(shift, s);
       }
-      shift = s;
     }
+    s_shift[tid] = shift;
   }
-  if (tid < 64) s_shift[tid] = shift;
   __syncthreads();
   if (tid == 0) {
     double mx = -1.0;
-    for (int i = 0; i < k; ++i) mx = fmax(mx, s_shift[i]);
+    for (int i = 0; i < 64; ++i) mx = fmax(mx, s_shift[i]);
     state->cost = partial[(size_t)k * d + k];
     state->iter += 1;
     state->max_shift2 = mx < 0 ? 0.0 : mx;
@@ -340,7 +342,7 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
       for (int msk = 1; msk <= 2; msk <<= 1) { xx0 += shfl_xor_d(xx0, msk); xx1 += shfl_xor_d(xx1, msk); }
       if (q == 0) {
         const bool v0 = t0 < rows_valid, v1 = t1 < rows_valid;
-        int l0 = v0 ? p.labels_in[row0 + t0] : -1, l1 = v1 ? p.labels_in[row0 + t1] : -1;
+        int l0 = v0 ? p.labels_in[row0 + t0] - p.label_base : -1, l1 = v1 ? p.labels_in[row0 + t1] - p.label_base : -1;   // label_base: centre chunk offset (k > 64)
         if (l0 >= k) l0 = -1;
         if (l1 >= k) l1 = -1;
         sts_u32(lab_b + 4u * t0, (uint32_t)l0); sts_u32(lab_b + 4u * t1, (uint32_t)l1);

@@ -140,8 +140,8 @@ __global__ void __launch_bounds__(kMmaThreads) __maxnreg__(MAXREG) lloyd_mma_ker
       // latency runs under the score tiles
       int lin0 = -1, lin1 = -1; double win0 = 1.0, win1 = 1.0;
       if constexpr (MODE == 1 || MODE == 2) {
-        if (t0 < rows_valid) { lin0 = __ldg(p.labels_in + row0 + t0); if (has_w) win0 = __ldg(p.w + row0 + t0); }
-        if (t1 < rows_valid) { lin1 = __ldg(p.labels_in + row0 + t1); if (has_w) win1 = __ldg(p.w + row0 + t1); }
+        if (t0 < rows_valid) { lin0 = __ldg(p.labels_in + row0 + t0) - (MODE == 1 ? p.label_base : 0); if (has_w) win0 = __ldg(p.w + row0 + t0); }
+        if (t1 < rows_valid) { lin1 = __ldg(p.labels_in + row0 + t1) - (MODE == 1 ? p.label_base : 0); if (has_w) win1 = __ldg(p.w + row0 + t1); }
         if (lin0 >= k) lin0 = -1;
         if (lin1 >= k) lin1 = -1;
       }

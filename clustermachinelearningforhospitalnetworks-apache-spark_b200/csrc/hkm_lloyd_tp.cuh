@@ -105,7 +105,7 @@ __host__ inline TpPlan tp_choose(int d, int kp, int force_rmode = -1, int force_
   // candidates in order of preference: (reduce mode, warp budget)
   int cand[10][2]; int nc = 0;
   auto add = [&](int rm, int w) { if (force_wcfg < 0 || force_wcfg == w) { cand[nc][0] = rm; cand[nc][1] = w; ++nc; } };
-  if (kp == 16 && (force_rmode < 0 || force_rmode == 3)) { if (force_wcfg == 4) add(3, 4); add(3, nd <= 4 ? 1 : 0); if (force_wcfg == 0) add(3, 0); }
+  if (kp == 16 && (force_rmode < 0 || force_rmode == 3)) { if (force_wcfg == 4) add(3, 4); add(3, nd <= 3 ? 1 : 0); if (force_wcfg == 0 || force_wcfg == 1) add(3, 1 - (nd <= 3 ? 1 : 0)); }   // measured: 26 warps up to d = 24, 18 above
   if (d <= 32 && (force_rmode < 0 || force_rmode == 0)) { if (force_wcfg == 4) add(0, 4); add(0, 1); if (kp >= 48) add(0, 2); add(0, 0); }
   if (!(d & 1) && (force_rmode < 0 || force_rmode == 2)) { add(2, 3); add(2, 0); }
   TpPlan best{}; best.stages = 0;

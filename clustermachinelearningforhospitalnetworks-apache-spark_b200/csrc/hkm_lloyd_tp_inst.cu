@@ -49,7 +49,7 @@ int HKM_CAT(dispatch_lloyd_tp, HKM_TP_KP)(const LloydParams& p, const TpPlan& L,
   HKM_TP_TRY(2, 2, 0, 1, 8) HKM_TP_TRY(2, 2, 3, 1, 8)
   // one-hot DMMA (k <= 16)
   if constexpr (KP == 16) {
-    HKM_TP_TRY(1, 3, 1, 1, 4) HKM_TP_TRY(2, 3, 1, 1, 4) HKM_TP_TRY(2, 3, 0, 1, 8)
+    HKM_TP_TRY(1, 3, 1, 1, 4) HKM_TP_TRY(2, 3, 1, 1, 4) HKM_TP_TRY(2, 3, 0, 1, 8) HKM_TP_TRY(1, 3, 0, 1, 4)
     HKM_TP_TRY(2, 3, 4, 1, 2) HKM_TP_TRY(2, 0, 4, 1, 2)     // two CTAs per SM (d <= 16)
   }
 #undef HKM_TP_TRY

@@ -25,7 +25,14 @@ struct AssembleParams {
   unsigned long long* invalid_count;            // rows holding a null or NaN
   int64_t* block_valid;                         // count mode: valid rows per block
   int mode;                                     // 0: write rows as they are (NaN for nulls); 1: compact valid rows; 2: only count
+  // row predicate fused into the compaction (hkm_assemble_filtered): `win_col BETWEEN win_lo AND win_hi` (null timestamps never
+  // match) and up to kMaxExtraValid further validity masks (na.drop over columns that are not features)
+  const int64_t* win_col; const uint8_t* win_valid; int64_t win_lo, win_hi;
+  const uint8_t* extra_valid[8]; int n_extra;
+  unsigned long long* outside_count;            // rows the window rejects
+  uint8_t* keep_out;                            // nullable: 1 for every row that is written
 };
+constexpr int kMaxExtraValid = 8;
 
 __device__ __forceinline__ double load_col(const ColDesc& c, int64_t i, bool& ok) {
   if (c.vkind == 1) ok = reinterpret_cast<const uint8_t*>(c.valid)[i] != 0;
@@ -59,7 +66,19 @@ __global__ void __launch_bounds__(256) assemble_kernel(const AssembleParams p) {
   const int64_t row0 = (int64_t)blockIdx.x * kRowsPerBlock;
   const int rows = (int)min((int64_t)kRowsPerBlock, p.n - row0);
   const int t = threadIdx.x & (kRowsPerBlock - 1), half = threadIdx.x / ROWS;
-  if (threadIdx.x < kRowsPerBlock) s_bad[threadIdx.x] = 0;
+  if (threadIdx.x < kRowsPerBlock) {
+    // bit 0: null / NaN somewhere in the row; bit 1: outside the time window
+    int b0 = 0;
+    if (threadIdx.x < rows) {
+      const int64_t r = row0 + threadIdx.x;
+      if (p.win_col != nullptr) {
+        const int64_t ts = p.win_col[r];
+        if ((p.win_valid != nullptr && p.win_valid[r] == 0) || ts < p.win_lo || ts > p.win_hi) b0 |= 2;
+      }
+      for (int e = 0; e < p.n_extra; ++e) if (p.extra_valid[e][r] == 0) b0 |= 1;
+    }
+    s_bad[threadIdx.x] = b0;
+  }
   __syncthreads();
   int bad = 0;
   for (int c = half; c < d; c += STEP) {
@@ -91,9 +110,17 @@ __global__ void __launch_bounds__(256) assemble_kernel(const AssembleParams p) {
     s_rank[threadIdx.x] = valid ? rank : -1;
   }
   if (threadIdx.x == 0) {
-    if (rows - nvalid > 0 && p.invalid_count != nullptr) atomicAdd(p.invalid_count, (unsigned long long)(rows - nvalid));
+    if (p.win_col == nullptr) {
+      if (rows - nvalid > 0 && p.invalid_count != nullptr) atomicAdd(p.invalid_count, (unsigned long long)(rows - nvalid));
+    } else if (p.invalid_count != nullptr || p.outside_count != nullptr) {
+      int nout = 0, nnull = 0;                       // WHERE first, na.drop second: nulls are counted among the rows inside the window
+      for (int r = 0; r < rows; ++r) { if (s_bad[r] & 2) ++nout; else if (s_bad[r] & 1) ++nnull; }
+      if (nnull && p.invalid_count != nullptr) atomicAdd(p.invalid_count, (unsigned long long)nnull);
+      if (nout && p.outside_count != nullptr) atomicAdd(p.outside_count, (unsigned long long)nout);
+    }
     if (p.block_valid != nullptr) p.block_valid[blockIdx.x] = nvalid;
   }
+  if (p.keep_out != nullptr && p.mode != 2 && threadIdx.x < rows) p.keep_out[row0 + threadIdx.x] = valid ? 1 : 0;
   if (p.mode == 2) return;
   __syncthreads();
   if (p.mode == 0) {
@@ -324,6 +351,48 @@ int hkm_assemble(const void* const* cols_host, const int32_t* dtypes_host, const
   HKM_CUDA_TRY(cudaGetLastError());
   p.mode = 1; p.block_valid = nullptr; p.block_base = base; p.invalid_count = nullptr;
   launch(p);
+  HKM_CUDA_TRY(cudaGetLastError());
+  return HKM_OK;
+}
+
+int hkm_assemble_filtered(const void* const* cols_host, const int32_t* dtypes_host, const void* const* valid_host, const int32_t* vkind_host,
+                          int d, int64_t n, const double* shift, const double* scale, const int64_t* window_col, const uint8_t* window_valid,
+                          int64_t window_lo, int64_t window_hi, const uint8_t* const* extra_valid_host, int n_extra, double* X_out,
+                          int64_t* n_out, unsigned long long* invalid_count, unsigned long long* outside_count, uint8_t* keep_out,
+                          void* scratch, size_t scratch_bytes, void* stream) {
+  AssembleParams p{};
+  int rc = fill_params(p, cols_host, dtypes_host, valid_host, vkind_host, d, n, "hkm_assemble_filtered");
+  if (rc != HKM_OK) return rc;
+  if (invalid_count == nullptr || outside_count == nullptr || n_out == nullptr || X_out == nullptr || n_extra < 0 || n_extra > kMaxExtraValid ||
+      (n_extra > 0 && extra_valid_host == nullptr)) { set_error("hkm_assemble_filtered: bad arguments (at most %d extra validity masks)", kMaxExtraValid); return HKM_ERR_INVALID; }
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  HKM_CUDA_TRY(cudaMemsetAsync(invalid_count, 0, sizeof(unsigned long long), st));
+  HKM_CUDA_TRY(cudaMemsetAsync(outside_count, 0, sizeof(unsigned long long), st));
+  if (n == 0) { HKM_CUDA_TRY(cudaMemsetAsync(n_out, 0, sizeof(int64_t), st)); return HKM_OK; }
+  const int rpb = assemble_rows_per_block(d);
+  const int64_t nb = (n + rpb - 1) / rpb;
+  if (nb > 0x7fffffff) { set_error("hkm_assemble_filtered: too many rows for one launch"); return HKM_ERR_UNSUPPORTED; }
+  if (scratch == nullptr || scratch_bytes < hkm_assemble_scratch_bytes(n)) { set_error("hkm_assemble_filtered: scratch too small"); return HKM_ERR_INVALID; }
+  p.X = X_out; p.shift = shift; p.scale = scale;
+  p.win_col = window_col; p.win_valid = window_valid; p.win_lo = window_lo; p.win_hi = window_hi;
+  p.n_extra = n_extra;
+  for (int e = 0; e < n_extra; ++e) { if (extra_valid_host[e] == nullptr) { set_error("hkm_assemble_filtered: null validity mask %d", e); return HKM_ERR_INVALID; } p.extra_valid[e] = extra_valid_host[e]; }
+  if (window_col == nullptr) { p.win_col = nullptr; }
+  const size_t smem = (size_t)rpb * (d | 1) * sizeof(double);
+  HKM_CUDA_TRY(cudaFuncSetAttribute(assemble_kernel<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * (kMaxCols | 1) * (int)sizeof(double)));
+  int64_t* counts = reinterpret_cast<int64_t*>(scratch);
+  int64_t* base = counts + nb;
+  // pass 1 counts (per block: rows kept; totals: nulls inside the window, rows outside it), pass 2 writes the kept rows in order
+  p.mode = 2; p.block_valid = counts; p.invalid_count = invalid_count; p.outside_count = outside_count;
+  if (window_col == nullptr) {            // no window: the plain counting rule (every dropped row is an invalid row)
+    p.outside_count = nullptr;
+  }
+  assemble_kernel<128><<<(unsigned)nb, 256, smem, st>>>(p);
+  HKM_CUDA_TRY(cudaGetLastError());
+  scan_blocks_kernel<<<1, 1024, 0, st>>>(counts, nb, base, n_out);
+  HKM_CUDA_TRY(cudaGetLastError());
+  p.mode = 1; p.block_valid = nullptr; p.block_base = base; p.invalid_count = nullptr; p.outside_count = nullptr; p.keep_out = keep_out;
+  assemble_kernel<128><<<(unsigned)nb, 256, smem, st>>>(p);
   HKM_CUDA_TRY(cudaGetLastError());
   return HKM_OK;
 }

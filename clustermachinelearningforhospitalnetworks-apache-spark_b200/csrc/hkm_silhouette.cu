@@ -24,11 +24,30 @@ __global__ void silhouette_prep_kernel(const double* __restrict__ stats, int k, 
   }
 }
 
+// smallest and largest cluster id of the prediction column in one pass (the evaluator needs the id range before it can size the
+// per-cluster statistics); out2 starts at {INT_MAX, INT_MIN}
+__global__ void __launch_bounds__(256) label_range_kernel(const int32_t* __restrict__ labels, int64_t n, int32_t* __restrict__ out2) {
+  int lo = 0x7fffffff, hi = (int)0x80000000;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) { const int l = labels[i]; lo = min(lo, l); hi = max(hi, l); }
+  lo = __reduce_min_sync(0xffffffffu, lo); hi = __reduce_max_sync(0xffffffffu, hi);
+  if ((threadIdx.x & 31) == 0) { atomicMin(out2, lo); atomicMax(out2 + 1, hi); }
+}
+__global__ void label_range_init_kernel(int32_t* out2) { out2[0] = 0x7fffffff; out2[1] = (int)0x80000000; }
+
 }  // namespace hkm
 
 using namespace hkm;
 
 extern "C" {
+
+int hkm_label_range(const int32_t* labels, int64_t n, int32_t* out2, void* stream) {
+  if (out2 == nullptr || (n > 0 && labels == nullptr)) { set_error("hkm_label_range: bad arguments"); return HKM_ERR_INVALID; }
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  label_range_init_kernel<<<1, 1, 0, st>>>(out2);
+  if (n > 0) label_range_kernel<<<sm_count() * 4, 256, 0, st>>>(labels, n, out2);
+  HKM_CUDA_TRY(cudaGetLastError());
+  return HKM_OK;
+}
 
 int hkm_silhouette_stats(const double* X, const int32_t* labels, const double* weights, int64_t n, int d, int k, double* stats_out,
                          void* scratch, size_t scratch_bytes, void* stream) {

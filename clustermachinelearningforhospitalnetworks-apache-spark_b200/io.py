@@ -49,21 +49,33 @@ def _to_us(v: Union[str, _dt.datetime, np.datetime64, int]) -> int:
     return int(np.datetime64(v, "us").astype(np.int64))
 
 
-def between(table: Table, column: str, start, end) -> Table:
+def window_int64(c: Column, start, end):
+    """A BETWEEN window in integer form: (values as int64, lo, hi), microseconds for timestamps; None when the column is
+    neither a timestamp nor an integer column (such windows are applied on the host)."""
+    vals = np.asarray(c.values)
+    if vals.dtype.kind == "M":
+        return vals.astype("datetime64[us]").astype(np.int64), _to_us(start), _to_us(end)
+    if vals.dtype == object:   # python datetimes
+        v = np.array([np.datetime64(x, "us").astype(np.int64) if x is not None else np.iinfo(np.int64).min for x in vals])
+        return v, _to_us(start), _to_us(end)
+    if vals.dtype.kind in "iu":
+        return vals.astype(np.int64), int(start), int(end)
+    return None
+
+
+def between(table: Table, column: str, start, end, lazy: bool = False) -> Table:
     """WHERE column BETWEEN start AND end (inclusive on both sides, like Spark SQL; ref:L123-127).
-    Null timestamps never match."""
+    Null timestamps never match.  lazy=True only records the window: `VectorAssembler` then applies it (and a following
+    `.na.drop()`) on the device, inside the loader's compaction pass; any other use of the table applies it on the host."""
+    if lazy:
+        if column not in table:
+            raise KeyError(column)
+        return table.with_pending(window=(column, start, end))
     c = table[column]
     if not isinstance(c, Column):
         raise TypeError(f"{column!r} is not a scalar column")
-    vals = np.asarray(c.values)
-    if vals.dtype.kind == "M":
-        v = vals.astype("datetime64[us]").astype(np.int64)
-        lo, hi = _to_us(start), _to_us(end)
-    elif vals.dtype == object:   # python datetimes
-        v = np.array([np.datetime64(x, "us").astype(np.int64) if x is not None else np.iinfo(np.int64).min for x in vals])
-        lo, hi = _to_us(start), _to_us(end)
-    else:
-        v, lo, hi = vals, start, end
+    w = window_int64(c, start, end)
+    v, lo, hi = w if w is not None else (np.asarray(c.values), start, end)
     keep = (v >= lo) & (v <= hi)
     if c.valid is not None:
         keep &= np.asarray(c.valid, dtype=bool)

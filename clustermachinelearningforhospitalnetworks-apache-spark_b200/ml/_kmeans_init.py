@@ -105,7 +105,8 @@ def init_kmeans_parallel(X: torch.Tensor, layout: PartitionLayout, k: int, init_
     centers = _gather_global_rows(X, layout, [first_idx])
     new = centers.copy()
 
-    costs = torch.full((n,), float("inf"), dtype=torch.float64, device=dev)
+    costs = torch.empty(n, dtype=torch.float64, device=dev)
+    N.fill_f64(costs, float("inf"))
     sum_costs = torch.zeros(1, dtype=torch.float64, device=dev)
     scratch = N.kmpar_new_scratch(d, dev)
     strip = N.kmpar_strip_rows()

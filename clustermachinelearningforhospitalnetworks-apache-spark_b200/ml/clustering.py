@@ -325,16 +325,19 @@ def lloyd(X: torch.Tensor, C0: np.ndarray, w: Optional[torch.Tensor], max_iter: 
     xsum = torch.zeros(1, dtype=torch.float64, device=dev)
     world = RT.dist_info()[1]
 
-    xchg = RT.PeerExchange.get(dev) if world > 1 and not cosine else None
+    big_k = bool(N.load().hkm_needs_workspace(d, k))     # k > 64 or a shape outside the tiled kernels: chunked pass + separate update
+    lab_ws = torch.empty(X.shape[0], dtype=torch.int32, device=dev) if big_k else None
+    d2_ws = torch.empty(X.shape[0], dtype=torch.float64, device=dev) if big_k else None
+    xchg = RT.PeerExchange.get(dev) if world > 1 and not cosine and not big_k else None
     if xchg is not None and not xchg.fits(k, d):
         xchg = None          # partial sums larger than an exchange slot: NCCL all-reduce + hkm_update_centers instead
 
     def one_iter(mode):
-        if cosine:       # X holds unit rows, C unit centres: same pass, CosineDistanceMeasure.centroid as the driver step
-            N.assign_reduce(X, C, partial, weights=w, state=state, scratch=scratch, xnorm2_sum=xsum, xnorm2_mode=mode)
+        if cosine or big_k:   # cosine: X holds unit rows, C unit centres, CosineDistanceMeasure.centroid as the driver step
+            N.assign_reduce(X, C, partial, lab_ws, d2_ws, weights=w, state=state, scratch=scratch, xnorm2_sum=xsum, xnorm2_mode=mode)
             if world > 1:
                 RT.all_reduce_sum(partial)
-            N.update_centers(partial, C, tol, state, cosine=True)
+            N.update_centers(partial, C, tol, state, cosine=cosine)
             return
         if world == 1:   # one launch: the last CTA of the pass also updates the centres
             N.lloyd_step(X, C, partial, tol, state, scratch, weights=w, xnorm2_sum=xsum, xnorm2_mode=mode)

@@ -75,15 +75,16 @@ def silhouette(X: torch.Tensor, labels: torch.Tensor, w=None, cosine: bool = Fal
             raise IllegalArgumentException("requirement failed: Cosine distance is not defined for zero-length vectors.")
     kmax = torch.zeros(1, dtype=torch.int64, device=X.device)
     if n:
-        if int(labels.min()) < 0:
+        lo, hi = N.label_range(labels)                     # one pass over the ids (hkm_label_range)
+        if lo < 0:
             raise IllegalArgumentException("prediction column holds negative cluster ids")
-        kmax[0] = int(labels.max()) + 1
+        kmax[0] = hi + 1
     import torch.distributed as dist
     if RT.dist_info()[1] > 1:
         dist.all_reduce(kmax, op=dist.ReduceOp.MAX)
     k = int(kmax.item())
-    if k > N.load().hkm_max_k() or d > N.load().hkm_max_d():
-        raise N.HkmError(f"silhouette: {k} cluster ids / d={d} outside the built CUDA kernels")
+    if k > N.load().hkm_max_k_single_pass() or N.load().hkm_needs_workspace(d, max(k, 1)):
+        raise N.HkmError(f"silhouette: {k} cluster ids / d={d} outside the silhouette kernels (ids < {N.load().hkm_max_k_single_pass()}, d <= 96)")
     k = max(k, 1)
     stats = torch.zeros(k * d + 2 * k + 1, dtype=torch.float64, device=X.device)
     scratch = N.new_scratch(d, k, X.device)

@@ -72,6 +72,9 @@ class VectorAssembler(Params):
         dev = RT.device()
         if not self.isDefined("inputCols"):
             raise IllegalArgumentException("VectorAssembler: inputCols is not set")
+        fused = self._fused_selection(t, dev)
+        if fused is not None:
+            return fused
         cols, valids, names = [], [], []
         for name in self.getInputCols():
             c = t[name]
@@ -87,15 +90,10 @@ class VectorAssembler(Params):
             raise N.HkmError("VectorAssembler: more than 64 assembled columns are not supported by hkm_assemble")
         mode = self.getHandleInvalid()
         if mode == "skip":
-            X, n_keep, bad = N.assemble(cols, valids, n, skip_invalid=True)
+            # one compaction on the device; its keep mask (a byte per row) filters the table's other columns
+            X, keep, _, bad = N.assemble_filtered(cols, valids, n)
             if bad:
-                keep = np.ones(n, dtype=bool)
-                for v, valid in zip(cols, valids):
-                    if valid is not None:
-                        keep &= valid.cpu().numpy().astype(bool)
-                    if v.dtype.is_floating_point:
-                        keep &= ~torch.isnan(v).cpu().numpy()
-                t = t.filter_rows(keep)
+                t = t.filter_rows(keep.cpu().numpy().astype(bool))
             return t.withColumn(self.getOutputCol(), DeviceMatrix(X.contiguous()))
         col = AssembledColumn(cols, valids, names, n)
         if mode == "error":
@@ -105,6 +103,79 @@ class VectorAssembler(Params):
                 raise SparkException(f"Encountered null while assembling a row with handleInvalid = \"error\". Consider removing "
                                      f"nulls from dataset or using handleInvalid = \"keep\" or \"skip\". ({bad} invalid rows)")
         return t.withColumn(self.getOutputCol(), col)
+
+
+def _host_validity(c: Column):
+    """uint8 validity of a scalar host column for na.drop: not null and (floats) not NaN; None when every row is present."""
+    vals = np.asarray(c.values) if not isinstance(c.values, torch.Tensor) else None
+    ok = None if c.valid is None else np.asarray(c.valid.cpu() if isinstance(c.valid, torch.Tensor) else c.valid, dtype=bool)
+    if vals is not None and vals.dtype.kind == "f":
+        nn = ~np.isnan(vals)
+        ok = nn if ok is None else ok & nn
+    elif vals is not None and vals.dtype == object:
+        nn = np.array([x is not None for x in vals], dtype=bool)
+        ok = nn if ok is None else ok & nn
+    if ok is None or ok.all():
+        return None
+    return np.ascontiguousarray(ok, dtype=np.uint8)
+
+
+def _fused_selection_impl(self, t: Table, dev):
+    """The reference's batch extraction (ref:L123-128: time window, then na.drop) fused with the assembly: the window predicate and the
+    null masks ride in the loader's compaction pass on the device, and only the keep mask (one byte per row) comes back to filter
+    the table's other columns."""
+    pend = t._pending
+    if pend is None or not (pend["dropna"] or self.getHandleInvalid() == "skip"):
+        return None
+    from .. import io
+    raw = t._cols
+    win = None
+    if pend["window"] is not None:
+        wname, lo, hi = pend["window"]
+        wc = raw[wname]
+        w = io.window_int64(wc, lo, hi) if isinstance(wc, Column) and not isinstance(wc.values, torch.Tensor) else None
+        if w is None:
+            return None                                          # not a timestamp / integer window: resolved on the host
+        ts = torch.from_numpy(np.ascontiguousarray(w[0])).to(dev)
+        tsv = None
+        if wc.valid is not None:
+            tsv = torch.from_numpy(np.ascontiguousarray(np.asarray(wc.valid, dtype=np.uint8))).to(dev)
+        win = (ts, tsv, w[1], w[2])
+    cols, valids = [], []
+    for name in self.getInputCols():
+        c = raw[name]
+        if not isinstance(c, Column):
+            return None                                          # vector inputs: the general path
+        v, valid = _to_device_scalar(c, dev)
+        cols.append(v); valids.append(valid)
+    if len(cols) > 64:
+        raise N.HkmError("VectorAssembler: more than 64 assembled columns are not supported by hkm_assemble")
+    extra = []
+    if pend["dropna"]:                                           # na.drop looks at every column, not only the features
+        for name, c in raw.items():
+            if name in self.getInputCols() or not isinstance(c, Column):
+                continue
+            ok = _host_validity(c)
+            if ok is not None:
+                extra.append(torch.from_numpy(ok).to(dev))
+    if len(extra) > 8:
+        return None
+    n = _nrows_raw(raw)
+    X, keep, outside, bad = N.assemble_filtered(cols, valids, n, window=win, extra_valid=extra)
+    if bad and not pend["dropna"] and self.getHandleInvalid() == "error":
+        raise SparkException(f"Encountered null while assembling a row with handleInvalid = \"error\". ({bad} invalid rows)")
+    keep_np = keep.cpu().numpy().astype(bool)
+    out = Table(raw).filter_rows(keep_np)
+    return out.withColumn(self.getOutputCol(), DeviceMatrix(X.contiguous()))
+
+
+def _nrows_raw(raw) -> int:
+    for c in raw.values():
+        return len(c.values) if isinstance(c, Column) else len(c)
+    return 0
+
+
+VectorAssembler._fused_selection = _fused_selection_impl
 
 
 def _count_invalid(cols, valids, n) -> int:

@@ -152,8 +152,12 @@ class _NaFunctions:
         self._t = table
 
     def drop(self, how: str = "any", subset: Optional[Iterable[str]] = None) -> "Table":
-        """DataFrame.na.drop (ref:L128): drop rows holding a null (or NaN) in `subset` columns."""
+        """DataFrame.na.drop (ref:L128): drop rows holding a null (or NaN) in `subset` columns.  On a table with a pending
+        (lazy) time window the drop stays pending too, so the loader can fuse both."""
         t = self._t
+        if t._pending is not None and how == "any" and subset is None:
+            return t.with_pending(dropna=True)
+        t = t.resolve()
         names = list(subset) if subset is not None else t.columns
         n = t.count()
         bad_any = np.zeros(n, dtype=bool)
@@ -180,7 +184,13 @@ class _NaFunctions:
 
 
 class Table:
+    """Columns by name.  A table may carry a PENDING row selection (`io.between(..., lazy=True)`, then `.na.drop()`): the
+    reference's `WHERE event_time BETWEEN ... ` + `.na.drop()` (ref:L123-128).  VectorAssembler fuses a pending selection into the
+    device loader's compaction pass; any other use of the table resolves it on the host first."""
+
     def __init__(self, columns=None):
+        self._pending = None          # {"window": (column, lo, hi) | None, "dropna": bool}
+        self._resolved = None
         self._cols: "OrderedDict[str, Any]" = OrderedDict()
         if columns is not None:
             items = columns.items() if hasattr(columns, "items") else columns
@@ -228,6 +238,34 @@ class Table:
             return Table(obj)
         raise TypeError(f"cannot interpret {type(obj).__name__} as a table (pass Table, pyarrow.Table, pandas.DataFrame or dict)")
 
+    # ---- pending row selection
+    def with_pending(self, window=None, dropna=None) -> "Table":
+        t = Table(self._cols)
+        cur = dict(self._pending or {"window": None, "dropna": False})
+        if window is not None:
+            if cur["window"] is not None:
+                raise ValueError("a pending time window is already set; resolve() the table before adding another")
+            cur["window"] = window
+        if dropna is not None:
+            cur["dropna"] = bool(dropna)
+        t._pending = cur
+        return t
+
+    def resolve(self) -> "Table":
+        """The table with its pending selection applied on the host (NumPy masks); a table without one is returned as is."""
+        if self._pending is None:
+            return self
+        if self._resolved is None:
+            t = Table(self._cols)
+            if self._pending["window"] is not None:
+                from . import io
+                col, lo, hi = self._pending["window"]
+                t = io.between(t, col, lo, hi)
+            if self._pending["dropna"]:
+                t = t.na.drop()
+            self._resolved = t
+        return self._resolved
+
     # ---- DataFrame-like surface
     @property
     def columns(self):
@@ -238,6 +276,8 @@ class Table:
         return _NaFunctions(self)
 
     def count(self) -> int:
+        if self._pending is not None:
+            return self.resolve().count()
         for c in self._cols.values():
             return _nrows(c)
         return 0
@@ -248,7 +288,7 @@ class Table:
     def __getitem__(self, name):
         if name not in self._cols:
             raise KeyError(f"column {name!r} does not exist; available: {self.columns}")
-        return self._cols[name]
+        return self.resolve()._cols[name]
 
     def select(self, *names) -> "Table":
         if len(names) == 1 and isinstance(names[0], (list, tuple)):
@@ -256,15 +296,15 @@ class Table:
         return Table(OrderedDict((n, self[n]) for n in names))
 
     def withColumn(self, name: str, col) -> "Table":
-        cols = OrderedDict(self._cols)
+        cols = OrderedDict(self.resolve()._cols)
         cols[name] = _as_column(col)
         return Table(cols)
 
     def drop(self, *names) -> "Table":
-        return Table(OrderedDict((k, v) for k, v in self._cols.items() if k not in names))
+        return Table(OrderedDict((k, v) for k, v in self.resolve()._cols.items() if k not in names))
 
     def filter_rows(self, keep: np.ndarray) -> "Table":
-        return Table(OrderedDict((k, _take(c, keep)) for k, c in self._cols.items()))
+        return Table(OrderedDict((k, _take(c, keep)) for k, c in self.resolve()._cols.items()))
 
     def to_numpy(self, name: str) -> np.ndarray:
         c = self[name]

@@ -57,9 +57,18 @@ typedef struct hkm_lloyd_state {
 HKM_API const char* hkm_last_error(void);
 HKM_API int hkm_version(void);
 
-/* Largest k and d the kernels accept (a (d, k) pair whose tile ring does not fit in shared memory is refused with HKM_ERR_UNSUPPORTED). */
+/* Largest k and d the library accepts (a (d, k) pair whose tile ring does not fit in shared memory is refused with
+ * HKM_ERR_UNSUPPORTED).  One launch scores up to hkm_max_k_single_pass() = 64 centres; hkm_assign_reduce, hkm_update_centers,
+ * hkm_kmpar_cost_update and hkm_closest_counts take larger k in chunks of 64 centres (a running-minimum assignment pass per chunk,
+ * then a labels-given statistics pass per chunk: 2 * ceil(k / 64) passes over X, with labels_out and mind2_out as workspace);
+ * the fused single-launch steps (hkm_lloyd_step, hkm_lloyd_step_peer) and the silhouette passes stay at k <= 64. */
 HKM_API int hkm_max_k(void);
+HKM_API int hkm_max_k_single_pass(void);
 HKM_API int hkm_max_d(void);
+/* 1 when hkm_assign_reduce runs (d, k) in chunks -- k > 64, d > 96 (general-shape kernels, hkm_generic.cu: plain loads, one warp per
+ * row, several times below the HBM rate) or a tile ring that does not fit in shared memory -- and therefore needs labels_out and
+ * mind2_out as per-row workspace; such shapes have no fused step (use hkm_assign_reduce + hkm_update_centers) and no silhouette pass. */
+HKM_API int hkm_needs_workspace(int d, int k);
 
 /* Tuning / test hook, process wide: pins the kernel family the Lloyd data passes use wherever that family is built for the
  * shape.  0 = pick per shape (default), 1 = gather, 2 = fp64 tensor pipe, 3 = warp-specialised fp64, 4 = pipelined tcgen05
@@ -200,6 +209,8 @@ HKM_API int hkm_kmpar_sample(const double* costs, int64_t n, const int64_t* part
                              int64_t total_strips, int P, int part_index0, int32_t seed, int step, int k,
                              const double* sum_costs, int64_t* idx_out, int cap, int32_t* count_out, void* stream);
 HKM_API int hkm_kmpar_strip_rows(void);
+/* p[0 .. n) = value: the +infinity start of the k-means|| cost column (initKMeansParallel: costs = Double.PositiveInfinity). */
+HKM_API int hkm_fill_f64(double* p, int64_t n, double value, void* stream);
 
 /*
  * counts_out[j] = number of rows whose closest candidate (strict '<', lowest index on ties) is j
@@ -213,6 +224,10 @@ HKM_API int hkm_closest_counts(const double* X, int64_t n, int d, const double* 
  * ClusteringEvaluator silhouette, squared Euclidean (ml/evaluation/ClusteringMetrics.scala,
  * SURVEY 8a-10 / 8a-11).  Scratch: hkm_assign_reduce_scratch_bytes(d, k).
  * ------------------------------------------------------------------------------------------- */
+
+/* Smallest and largest id of a prediction column in one pass: out2 = {min, max} (device int32[2]; {INT_MAX, INT_MIN} when
+ * n = 0).  ClusteringEvaluator needs the id range to size the per-cluster statistics (Spark gets it from groupBy(prediction)). */
+HKM_API int hkm_label_range(const int32_t* labels, int64_t n, int32_t* out2, void* stream);
 
 /*
  * computeClusterStats: for every cluster id G in [0, k): Y_G = sum w x, N_G = sum w, Psi_G = sum w |x|^2
@@ -262,6 +277,23 @@ HKM_API int hkm_assemble(const void* const* cols_host, const int32_t* dtypes_hos
                          const int32_t* vkind_host, int d, int64_t n, const double* shift, const double* scale,
                          int skip_invalid, double* X_out, int64_t* n_out, unsigned long long* invalid_count,
                          void* scratch, size_t scratch_bytes, void* stream);
+
+/*
+ * hkm_assemble with the row selection of the reference's batch extraction fused into the compaction pass:
+ *   SELECT * FROM t WHERE event_time BETWEEN start AND end   (ref:L123-127; window_col = the timestamps as int64, inclusive
+ *                                                              bounds, a null timestamp -- window_valid byte 0 -- never matches)
+ *   .na.drop()                                                (ref:L128; besides the assembled columns' own nulls / NaNs, up to 8
+ *                                                              more validity byte masks: columns that are not features)
+ * followed by VectorAssembler (+ the fused StandardScalerModel).  Kept rows are written in order, *n_out of them;
+ * *outside_count = rows the window rejects, *invalid_count = rows inside the window that hold a null; keep_out (nullable, n
+ * bytes) marks the kept rows so the caller can filter the table's other columns.  window_col = NULL: no window.
+ */
+HKM_API int hkm_assemble_filtered(const void* const* cols_host, const int32_t* dtypes_host, const void* const* valid_host,
+                                  const int32_t* vkind_host, int d, int64_t n, const double* shift, const double* scale,
+                                  const int64_t* window_col, const uint8_t* window_valid, int64_t window_lo, int64_t window_hi,
+                                  const uint8_t* const* extra_valid_host, int n_extra, double* X_out, int64_t* n_out,
+                                  unsigned long long* invalid_count, unsigned long long* outside_count, uint8_t* keep_out,
+                                  void* scratch, size_t scratch_bytes, void* stream);
 
 /*
  * Moments for StandardScaler.fit (Summarizer mean/std): out2d[2c] = sum_r (x_rc - pivot_c),

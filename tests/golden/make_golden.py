@@ -8,6 +8,13 @@ Sources of the constants (none come from /root/reference, which holds no KMeans 
     (relTol 1e-5), iris in the UCI variant (rows 35 and 38 differ from scikit-learn's copy)
   * KMeansSuite "single cluster": points (1,2,6),(1,3,0),(1,4,6), k=1 -> centre (1,3,4)
   * pyspark.ml.clustering.KMeans doctest: 4 weighted points, k=2 -> trainingCost 4.0
+  * pyspark.ml.evaluation.ClusteringEvaluator doctest (Spark 3.5 API docs, pyspark.ml.evaluation.ClusteringEvaluator): six points
+    ([0.0,0.5],0) ([0.5,0.0],0) ([10.0,11.0],1) ([10.5,11.5],1) ([1.0,1.0],0) ([8.0,6.0],1) -> evaluate() prints 0.9079...
+    The doctest then sets weightCol (weights 2.5 x4, 5.0 x2) and prints 0.9079... again in some doc versions; applying
+    ClusteringMetrics' published formulas to those weights gives 0.87153 (hand-checked point by point), so only the
+    UNWEIGHTED constant is treated as an upstream known answer; the weighted value recorded here is the formula's
+  * pyspark.ml.feature.StandardScaler doctest (API docs): rows [0.0], [2.0] -> mean [1.0], std [1.4142], transform -> [0.0], [1.4142]
+  * pyspark.ml.feature.VectorAssembler doctest (API docs): row (a=1, b=0, c=3) -> features [1.0, 0.0, 3.0]
 The iris matrix itself is written by this script from scikit-learn's copy with the two UCI rows patched.
 """
 import json
@@ -34,6 +41,11 @@ def main():
         "pyspark_doctest": {"points": [[0, 0], [1, 1], [9, 8], [8, 9]], "weights": [2, 2, 2, 2], "k": 2, "trainingCost": 4.0,
                             "centers_sorted": [[0.5, 0.5], [8.5, 8.5]]},
         "kmeans_default_seed": -1689246527,
+        "clustering_evaluator_doctest": {"points": [[0.0, 0.5], [0.5, 0.0], [10.0, 11.0], [10.5, 11.5], [1.0, 1.0], [8.0, 6.0]],
+                                         "prediction": [0, 0, 1, 1, 0, 1], "silhouette_prefix": 0.9079, "prefix_tol": 5e-5,
+                                         "weights": [2.5, 2.5, 2.5, 2.5, 5.0, 5.0], "weighted_by_formula": 0.8715279275368312},
+        "standard_scaler_doctest": {"rows": [[0.0], [2.0]], "mean": [1.0], "std": [1.4142], "scaled": [[0.0], [1.4142]], "print_tol": 5e-5},
+        "vector_assembler_doctest": {"a": [1], "b": [0], "c": [3], "features": [[1.0, 0.0, 3.0]]},
     }
     with open(os.path.join(HERE, "kat.json"), "w") as f:
         json.dump(kat, f, indent=1)

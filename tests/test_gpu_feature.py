@@ -94,6 +94,25 @@ def test_standard_scaler_fused_and_unfused(hkm, oracle, with_mean, with_std):
     assert np.allclose(m2.transform(dense).to_numpy("scaled"), Yo2, rtol=1e-14, atol=1e-14)
 
 
+def test_pyspark_feature_doctests(hkm):
+    """pyspark.ml.feature doctests (tests/golden/make_golden.py cites the API-doc pages): VectorAssembler (1, 0, 3) -> [1.0, 0.0, 3.0];
+    StandardScaler rows [0.0], [2.0] -> mean 1.0, std 1.4142, scaled [0.0], [1.4142]."""
+    import json, os
+    from hkm_b200.ml.feature import StandardScaler, VectorAssembler
+    kat = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "kat.json")))
+    va = kat["vector_assembler_doctest"]
+    t = VectorAssembler(inputCols=["a", "b", "c"], outputCol="features").transform(
+        {"a": np.array(va["a"], dtype=np.int64), "b": np.array(va["b"], dtype=np.int64), "c": np.array(va["c"], dtype=np.int64)})
+    assert np.array_equal(t.to_numpy("features"), np.array(va["features"]))
+    ss = kat["standard_scaler_doctest"]
+    data = {"a": np.array(ss["rows"], dtype=np.float64)}
+    model = StandardScaler(inputCol="a", outputCol="scaled").fit(data)
+    assert model.mean == pytest.approx(ss["mean"], abs=1e-15) and model.std == pytest.approx(ss["std"], abs=ss["print_tol"])
+    assert model.std[0] == pytest.approx(np.sqrt(2.0), rel=1e-15)
+    Y = model.transform(data).to_numpy("scaled")
+    assert Y == pytest.approx(np.array(ss["scaled"]), abs=ss["print_tol"]) and Y[0, 0] == 0.0
+
+
 def test_pipeline_assemble_scale_fit_evaluate(hkm, oracle):
     """The whole path on the hospital table: VectorAssembler -> StandardScaler -> KMeans -> ClusteringEvaluator."""
     from hkm_b200.ml.clustering import KMeans

@@ -210,3 +210,37 @@ def test_fit_and_evaluate_beyond_2_31_elements(hkm):
     assert torch.equal(torch.bincount(pred, minlength=k).cpu(), torch.tensor(s.clusterSizes))
     sil = ClusteringEvaluator().evaluate(s.predictions)
     assert -1.0 <= sil <= 1.0
+
+
+@pytest.mark.parametrize("n,d,k", [(30000, 16, 100), (20000, 8, 256), (5000, 24, 65),
+                                   # wide rows and (d, k) pairs whose tile ring does not fit: the general-shape kernels
+                                   (20000, 128, 8), (6000, 200, 70), (8000, 96, 64), (5000, 94, 25), (3000, 1000, 5)])
+def test_more_than_64_clusters(hkm, oracle, n, d, k):
+    """KMeans(k=100) and beyond, d = 128 and beyond (the pyspark estimator caps neither): the data pass runs in chunks of centres,
+    through the tiled kernels where the chunk fits them and through the general-shape kernels (hkm_generic.cu) where not."""
+    from hkm_b200.ml.clustering import KMeans
+    rng = np.random.default_rng(n + d + k)
+    prof = rng.normal(size=(k, d)) * 3.0
+    X = prof[rng.integers(0, k, size=n)] + rng.normal(size=(n, d)) * 0.5
+    N = hkm._native
+    C = X[rng.choice(n, k, replace=False)].copy()
+    Xd = torch.from_numpy(X).cuda(); Cd = torch.from_numpy(C).cuda()
+    partial = torch.empty(k * d + k + 1, dtype=torch.float64, device="cuda")
+    labels = torch.empty(n, dtype=torch.int32, device="cuda"); mind2 = torch.empty(n, dtype=torch.float64, device="cuda")
+    N.assign_reduce(Xd, Cd, partial, labels, mind2, scratch=N.new_scratch(d, k, "cuda"))
+    sums, wsum, cost, lab = oracle.lloyd_pass(X, C, P=1, want_labels=True)
+    p = partial.cpu().numpy()
+    assert np.array_equal(labels.cpu().numpy(), lab) and np.array_equal(p[k * d:k * d + k], wsum)
+    assert np.abs(p[:k * d].reshape(k, d) - sums).max() <= 1e-11 * max(1.0, np.abs(sums).max())
+    assert p[-1] == pytest.approx(cost, rel=1e-9)
+    pred = torch.empty(n, dtype=torch.int32, device="cuda")
+    N.assign_reduce(Xd, Cd, None, pred, do_reduce=False)
+    assert np.array_equal(pred.cpu().numpy(), lab)
+    # the estimator end to end: given initial centres, and the default k-means|| initialiser
+    model = KMeans(k=k, maxIter=5, tol=0.0, seed=3).setInitialCenters(C).fit({"features": X})
+    Co, it, cost5 = oracle.lloyd(X, C, max_iter=5, tol=0.0, P=1)
+    assert model.summary.numIter == it and np.allclose(model.clusterCenters(), Co, rtol=1e-6, atol=1e-9)
+    assert model.summary.trainingCost == pytest.approx(cost5, rel=1e-6) and sum(model.summary.clusterSizes) == n
+    m2, ref = _fit_both(hkm, oracle, X, k, 11, P=4, max_iter=3)
+    _assert_model_matches(m2, ref)
+    assert model.predict(X[0]) == int(model.summary.predictions.to_numpy("prediction")[0])

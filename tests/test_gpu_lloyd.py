@@ -135,8 +135,11 @@ def test_argument_errors(hkm):
         N.assign_reduce(X.cpu(), C, do_reduce=False)
     with pytest.raises(N.HkmError, match="reduce needs"):
         N.assign_reduce(X, C, do_reduce=True)
-    with pytest.raises(N.HkmError, match="outside fp64 kernel range"):
-        N.assign_reduce(torch.zeros(10, 500, dtype=torch.float64, device="cuda"), torch.zeros(2, 500, dtype=torch.float64, device="cuda"), do_reduce=False)
+    with pytest.raises(N.HkmError, match="d <= 4096"):
+        N.assign_reduce(torch.zeros(10, 5000, dtype=torch.float64, device="cuda"), torch.zeros(2, 5000, dtype=torch.float64, device="cuda"), do_reduce=False)
+    with pytest.raises(N.HkmError, match="no fused step|no general-shape path"):
+        Xw = torch.zeros(10, 500, dtype=torch.float64, device="cuda"); Cw = torch.zeros(2, 500, dtype=torch.float64, device="cuda")
+        N.lloyd_step(Xw, Cw, torch.zeros(2 * 500 + 3, dtype=torch.float64, device="cuda"), 0.0, N.new_state("cuda"), N.new_scratch(500, 2, "cuda"))
     with pytest.raises(N.HkmError, match="16-byte aligned"):
         N.assign_reduce(torch.zeros(41, dtype=torch.float64, device="cuda")[1:].view(10, 4), C, do_reduce=False)
 

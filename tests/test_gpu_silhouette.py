@@ -23,6 +23,19 @@ def test_iris_constant_from_spark_suite(hkm):
     assert ev.isLargerBetter() and ev.getMetricName() == "silhouette" and ev.getDistanceMeasure() == "squaredEuclidean"
 
 
+def test_pyspark_doctest_constant(hkm, oracle):
+    """pyspark.ml.evaluation.ClusteringEvaluator doctest: 0.9079... on six points; with the doctest's weights the value the
+    published formulas give (tests/golden/make_golden.py)."""
+    from hkm_b200.ml.evaluation import ClusteringEvaluator
+    k = KAT["clustering_evaluator_doctest"]
+    data = {"features": np.array(k["points"]), "prediction": np.array(k["prediction"], dtype=np.float64), "weight": np.array(k["weights"])}
+    ev = ClusteringEvaluator()
+    s = ev.evaluate(data)
+    assert f"{s:.10f}".startswith("0.9079") and s == pytest.approx(oracle.silhouette(data["features"], np.array(k["prediction"], dtype=np.int32)), abs=1e-12)
+    ev.setWeightCol("weight")
+    assert ev.evaluate(data) == pytest.approx(k["weighted_by_formula"], abs=1e-12)
+
+
 @pytest.mark.parametrize("n,d,k", [(500, 6, 3), (20000, 8, 5), (100_003, 24, 16), (30000, 32, 32), (5000, 3, 2), (40000, 64, 9), (129, 5, 64)])
 def test_matches_oracle(hkm, oracle, n, d, k):
     from hkm_b200.ml.evaluation import ClusteringEvaluator

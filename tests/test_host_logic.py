@@ -191,3 +191,7 @@ def test_ingest_csv_window_and_na_drop(hkm, tmp_path):
     clean = w.na.drop()
     assert clean.count() == 2 and clean.to_numpy("admission_count").tolist() == [11, 14]
     assert clean.to_numpy("length_of_stay").tolist() == [5.5, 8.5]
+    # the lazy form records the selection (the device loader fuses it); every other use resolves it on the host to the same rows
+    lz = io.between(t, "event_time", "2025-03-31 22:00:00", "2025-03-31 23:00:00", lazy=True).na.drop()
+    assert lz._pending == {"window": ("event_time", "2025-03-31 22:00:00", "2025-03-31 23:00:00"), "dropna": True}
+    assert lz.count() == 2 and lz.to_numpy("admission_count").tolist() == [11, 14] and lz["length_of_stay"].values.tolist() == [5.5, 8.5]

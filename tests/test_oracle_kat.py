@@ -52,6 +52,30 @@ def test_iris_silhouette_constants(oracle):
     assert oracle.np_silhouette(X, y) == pytest.approx(oracle.silhouette(X, y), rel=1e-12)
 
 
+def test_clustering_evaluator_doctest(oracle):
+    """pyspark.ml.evaluation.ClusteringEvaluator doctest: 0.9079... (unweighted: an upstream constant; weighted: the published
+    formulas applied to the doctest's weights, see make_golden.py)."""
+    k = KAT["clustering_evaluator_doctest"]
+    X = np.array(k["points"]); lab = np.array(k["prediction"], dtype=np.int32)
+    s = oracle.silhouette(X, lab, P=2)
+    assert abs(s - k["silhouette_prefix"]) < 1e-4 and f"{s:.10f}".startswith("0.9079")
+    assert oracle.np_silhouette(X, lab) == pytest.approx(s, rel=1e-13)
+    sw = oracle.silhouette(X, lab, w=np.array(k["weights"]), P=3)
+    assert sw == pytest.approx(k["weighted_by_formula"], rel=1e-12)
+    assert oracle.np_silhouette(X, lab, np.array(k["weights"])) == pytest.approx(sw, rel=1e-13)
+    # uniform weights change nothing
+    assert oracle.silhouette(X, lab, w=np.full(6, 2.5), P=2) == pytest.approx(s, rel=1e-13)
+
+
+def test_standard_scaler_doctest(oracle):
+    k = KAT["standard_scaler_doctest"]
+    X = np.array(k["rows"])
+    mean, std = oracle.scaler_fit(X, P=2)
+    assert mean == pytest.approx(k["mean"], abs=1e-15) and std == pytest.approx(k["std"], abs=k["print_tol"]) and std[0] == pytest.approx(np.sqrt(2.0), rel=1e-15)
+    Y = oracle.scaler_transform(X, mean, std, with_mean=False, with_std=True)      # pyspark defaults
+    assert Y == pytest.approx(np.array(k["scaled"]), abs=k["print_tol"]) and Y[0, 0] == 0.0
+
+
 def test_silhouette_equals_sklearn_sqeuclidean(oracle):
     from sklearn.metrics import silhouette_score
     rng = np.random.default_rng(3)
