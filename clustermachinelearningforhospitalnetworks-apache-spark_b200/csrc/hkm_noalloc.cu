@@ -9,6 +9,7 @@
 // until the process exits.
 #include "../../include/hkm.h"
 #include "hkm_lloyd_launch.cuh"
+#include <mutex>
 
 namespace {
 
@@ -24,6 +25,8 @@ int scratch_for_current_device(void** out) {
   int dev = 0;
   HKM_CUDA_TRY(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64) { hkm::set_error("hkm_assign_reduce_noalloc: device ordinal %d not supported", dev); return HKM_ERR_UNSUPPORTED; }
+  static std::mutex mu;                              // two host threads may make their first call on a device together
+  std::lock_guard<std::mutex> lock(mu);
   if (g_scratch_addr[dev] == nullptr) {
     void* ptr = nullptr;
     HKM_CUDA_TRY(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));  // with `dev` current: its copy of the array
@@ -40,6 +43,10 @@ extern "C" int hkm_assign_reduce_noalloc(const double* X, int64_t n, int d, cons
                                          double* partial_out, int32_t* labels_out, double* mind2_out, double* xnorm2_sum,
                                          int xnorm2_mode, const hkm_lloyd_state* state, int do_reduce, void* stream) {
   if (d < 1 || k < 1) { hkm::set_error("hkm_assign_reduce_noalloc: bad d/k"); return HKM_ERR_INVALID; }
+  if (hkm_needs_workspace(d, k)) {
+    hkm::set_error("hkm_assign_reduce_noalloc: k=%d, d=%d runs in centre chunks with per-row workspace; use hkm_assign_reduce for this shape", k, d);
+    return HKM_ERR_UNSUPPORTED;
+  }
   const size_t need = hkm_assign_reduce_scratch_bytes(d, k);
   if (need > (size_t)HKM_NOALLOC_SCRATCH_BYTES) {
     hkm::set_error("hkm_assign_reduce_noalloc: k=%d, d=%d needs %zu bytes of scratch but the built-in array holds %zu; "

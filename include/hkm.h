@@ -145,9 +145,11 @@ HKM_API int hkm_lloyd_step_peer(const double* X, int64_t n, int d, double* C_ino
  * HKM_NOALLOC_SCRATCH_BYTES array that lives inside libhkm.so on every GPU that loads it, until
  * the process exits.  Arguments and results are those of hkm_assign_reduce, minus scratch.
  *
- *  - Limit: hkm_assign_reduce_scratch_bytes(d, k) must fit in HKM_NOALLOC_SCRATCH_BYTES (4 MiB;
- *    on a 148-SM B200 that is k*d + k + 2 <= 1770, e.g. k = 32, d = 32).  Larger shapes are
- *    refused with HKM_ERR_UNSUPPORTED and a message naming both sizes.
+ *  - Limit: hkm_assign_reduce_scratch_bytes(d, k) = 256 + CTAs * (k*d + 2k + 2) * 8 must fit in
+ *    HKM_NOALLOC_SCRATCH_BYTES (4 MiB).  On a 148-SM B200 the pass launches 296 CTAs, so k*d + 2k + 2 <= 1771
+ *    (e.g. k = 32, d = 32 is the largest square shape), and 444 CTAs for thin rows (d <= 8 and k <= 8), so
+ *    k*d + 2k + 2 <= 1180 there (always met).  Larger shapes -- and every shape hkm_needs_workspace() reports --
+ *    are refused with HKM_ERR_UNSUPPORTED and a message naming both sizes.
  *  - The call itself performs no cudaMalloc / cudaFree and calls no allocating library routine.
  *  - The first call on each device looks up the array's device address (one cudaGetSymbolAddress
  *    with that device current).  Make that first call before starting any stream capture.
