@@ -325,9 +325,16 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         st = N.read_state(state)
         assert st.iter == 1 + warmup + steps, "device state says a step was skipped"
+        peer_t = None
         if xchg is not None:
             xchg.check()
-        return float(t[0]), float(t[1]), clocks, (C, partial, scratch, state, xsum, xchg)
+            # per-rank exchange timing the kernel tail accumulated (all steps incl. warm-up): store into the peers / wait for their flags
+            mine = torch.tensor([(st.reserved & 0xffffffff) / st.iter / 1e3, ((st.reserved >> 32) & 0xffffffff) / st.iter / 1e3], dtype=torch.float64, device=dev)
+            allr = [torch.empty_like(mine) for _ in range(world)]
+            dist.all_gather(allr, mine)
+            peer_t = {"store_us_per_step_by_rank": [round(float(a[0]), 2) for a in allr], "wait_us_per_step_by_rank": [round(float(a[1]), 2) for a in allr],
+                      "note": "inside the last CTA of every rank's pass: time to store the k*(d+1)+1 sums into every peer, then time until all peers' flags arrived (arrival skew between ranks + NVLink flight)"}
+        return float(t[0]), float(t[1]), clocks, (C, partial, scratch, state, xsum, xchg, peer_t)
 
     # ---------------- the table: built on the host by the same generator the CPU arm uses, then made resident
     # (cfg2, the headline).  The larger workloads do not fit host RAM and are generated in HBM by the device twin of the generator.
@@ -337,7 +344,7 @@ def main():
     C0 = X[:k].clone()
     if world > 1:
         dist.broadcast(C0, 0)
-    ms_total, kernel_ms, clocks, (C, partial, scratch, state, xsum, xchg) = timed_loop(X, C0, args.steps, args.warmup, True)
+    ms_total, kernel_ms, clocks, (C, partial, scratch, state, xsum, xchg, peer_t) = timed_loop(X, C0, args.steps, args.warmup, True)
     value = n * world * args.steps / (ms_total * 1e-3)
 
     # ---------------- N > 1: the in-kernel peer reduction against a rank-ordered sum of the per-rank partials
@@ -435,6 +442,7 @@ def main():
                 if world > 1:
                     dist.broadcast(Ce, 0)
                 ems, ekms, eclk, _st = timed_loop(Xe, Ce, args.extra_steps, 3, True)
+                epeer = _st[-1]
                 del Xe, _st
                 torch.cuda.empty_cache()
                 ebytes = en * ed * 8
@@ -443,6 +451,8 @@ def main():
                                "kernel": kernel_name(ed, ek), "kernel_ms": ekms, "achieved_gbs": ebytes / (ekms * 1e-3) / 1e9,
                                "frac": ebytes / (ekms * 1e-3) / 1e9 / measured_peak_gbs()[0], "clocks": eclk,
                                "table": "datagen.hospital_matrix_device (generated in HBM, seed 20250331 + rank)"}
+                if epeer:
+                    extra[name]["peer_exchange"] = epeer
             except Exception as ex:      # noqa: BLE001  (e.g. out of memory on a smaller GPU): report, do not lose the headline
                 extra[name] = {"error": f"{type(ex).__name__}: {str(ex)[:200]}"}
                 torch.cuda.empty_cache()
@@ -476,6 +486,8 @@ def main():
         line["extra"] = extra
     if parity:
         line["parity_check"] = parity
+    if peer_t:
+        line["peer_exchange"] = peer_t
     if not args.no_cpu_baseline and world == 1 and on_host:
         ns = min(n, 10_000_000)
         threads = host_threads()

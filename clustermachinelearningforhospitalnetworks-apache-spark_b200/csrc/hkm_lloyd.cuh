@@ -112,6 +112,10 @@ template <class Sync>
 __device__ __forceinline__ bool peer_allreduce(const LloydParams& p, double* vec, int len, int tid, int nthreads, Sync sync) {
   __shared__ int s_peer_ok;
   if (tid == 0) s_peer_ok = 1;
+  // timing of the exchange (nanoseconds, %globaltimer), accumulated per rank in hkm_lloyd_state.reserved: low word = time to
+  // store this rank's vector into every peer, high word = time spent waiting for the peers' flags (arrival skew + flight)
+  unsigned long long t_begin = 0, t_stored = 0;
+  if (tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_begin));
   const int world = p.xworld, rank = p.xrank, set = (int)(p.xepoch & 1ull);
   const size_t slot_off = ((size_t)set * world + rank) * kXchgSlot;
   for (int q = 0; q < world; ++q) {
@@ -120,6 +124,7 @@ __device__ __forceinline__ bool peer_allreduce(const LloydParams& p, double* vec
   }
   __threadfence_system();
   sync();
+  if (tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_stored));
   if (tid < world) {
     unsigned long long* f = reinterpret_cast<unsigned long long*>(reinterpret_cast<unsigned char*>(p.peer_bufs[tid]) + xchg_flags_offset(world)) + set * world + rank;
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(f), "l"(p.xepoch) : "memory");
@@ -132,6 +137,13 @@ __device__ __forceinline__ bool peer_allreduce(const LloydParams& p, double* vec
     } while (v != p.xepoch);
   }
   sync();
+  if (tid == 0 && p.state_rw != nullptr) {
+    unsigned long long t_end;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_end));
+    const unsigned long long prev = (unsigned long long)p.state_rw->reserved;
+    const unsigned long long lo = (prev & 0xffffffffull) + (t_stored - t_begin), hi = (prev >> 32) + (t_end - t_stored);
+    p.state_rw->reserved = (long long)((hi << 32) | (lo & 0xffffffffull));
+  }
   if (!s_peer_ok) {
     // incomplete exchange: stop this rank's loop (later passes become no-ops) instead of updating from partial sums;
     // the host sees err_flag and raises on every rank

@@ -81,7 +81,7 @@ static int launch_ws_n(LloydParams p, int grid, cudaStream_t st) {
 }
 template <int KS_T, int NT>
 static int launch_ws(const LloydParams& p, int grid, cudaStream_t st) {
-  constexpr int SW = NT >= 7 ? 12 : 8;
+  constexpr int SW = 8;   // see ws_score_warps
 #ifdef HKM_DEV_FAST
   if (const char* e = getenv("HKM_WS_SW")) {     // developer sweep of the score/reduce split
     const int sw = atoi(e), ns = getenv("HKM_WS_NSET") ? atoi(getenv("HKM_WS_NSET")) : 2;

@@ -53,8 +53,10 @@ __host__ __device__ inline int ws_stages(int d, int k_pad, int rw, int nset) {
 }
 // accumulator blocks per reduce warp: two when four stages still fit next to them, else one
 __host__ __device__ inline int ws_nset(int d, int k_pad, int rw) { return ws_stages(d, k_pad, rw, 2) >= 4 ? 2 : 1; }
-// score warps: 8 (+ 8 reduce warps) up to k = 48, 12 (+ 4) above -- measured, see profiles/r01_kernels.jsonl
-__host__ __device__ inline int ws_score_warps(int nt) { return nt >= 7 ? 12 : 8; }
+// score warps: always 8 (+ 8 reduce warps).  A 12 + 4 split was faster for k > 48, but a score warp then skips tiles and can
+// come back to a ring stage two wraps later, which a parity wait cannot tell from the current wrap; with 8 score warps every
+// warp visits every tile, so every wait sees consecutive phases.  (The pipelined tcgen05 variant serves these shapes now.)
+__host__ __device__ inline int ws_score_warps(int nt) { (void)nt; return 8; }
 
 // KS_T > 0: centre B-fragments in registers (d_pad = 4*KS_T); KS_T == 0: re-read from shared memory, p.ks k-steps.
 template <int KS_T, int NT, int SW, int NSET, int MAXREG>

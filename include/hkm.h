@@ -51,7 +51,8 @@ typedef struct hkm_lloyd_state {
   int32_t iter;       /* iterations executed so far */
   int32_t converged;  /* 1 once every updated centre moved by <= tol^2 */
   double max_shift2;  /* largest squared centre movement of the last executed iteration */
-  int64_t reserved;
+  int64_t reserved;   /* hkm_lloyd_step_peer: accumulated exchange timing of this rank in ns -- low 32 bits: storing the vector into the peers,
+                         high 32 bits: waiting for the peers' flags (both wrap after ~4 s of accumulated time) */
 } hkm_lloyd_state;
 
 HKM_API const char* hkm_last_error(void);
