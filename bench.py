@@ -305,6 +305,8 @@ def main():
         step(1)                                  # STORE pass: sum |x|^2 (outside the timed region, like the first Lloyd iteration)
         for _ in range(warmup):
             step(2)
+        torch.cuda.synchronize()
+        st_warm = N.read_state(state)             # exchange timing so far (start-up skew of the first exchange included): subtracted below
         # N == 1: a step IS one launch of the kernel, so the region's own events time it; N > 1: bracket each launch
         kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)] if world > 1 else None
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -328,8 +330,10 @@ def main():
         peer_t = None
         if xchg is not None:
             xchg.check()
-            # per-rank exchange timing the kernel tail accumulated (all steps incl. warm-up): store into the peers / wait for their flags
-            mine = torch.tensor([(st.reserved & 0xffffffff) / st.iter / 1e3, ((st.reserved >> 32) & 0xffffffff) / st.iter / 1e3], dtype=torch.float64, device=dev)
+            # per-rank exchange timing the kernel tail accumulated over the timed steps: store into the peers / wait for their flags
+            lo = ((st.reserved & 0xffffffff) - (st_warm.reserved & 0xffffffff)) & 0xffffffff
+            hi = (((st.reserved >> 32) & 0xffffffff) - ((st_warm.reserved >> 32) & 0xffffffff)) & 0xffffffff
+            mine = torch.tensor([lo / steps / 1e3, hi / steps / 1e3], dtype=torch.float64, device=dev)
             allr = [torch.empty_like(mine) for _ in range(world)]
             dist.all_gather(allr, mine)
             peer_t = {"store_us_per_step_by_rank": [round(float(a[0]), 2) for a in allr], "wait_us_per_step_by_rank": [round(float(a[1]), 2) for a in allr],
