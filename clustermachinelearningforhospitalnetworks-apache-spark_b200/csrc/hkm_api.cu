@@ -150,6 +150,8 @@ int assign_pass(const AssignArgs& a, const char* who) {
   p.stages = pl.stages; p.ks = (d + 3) / 4;
   const int grid = sm_count() * pl.ctas_per_sm;
   const int mode = (a.mode == 0 && a.weights != nullptr) ? 3 : a.mode;   // weights are a compile-time property of the Lloyd kernels
+  if (lloyd_wg_eligible(p, mode))                                        // 8 < k <= 32, d <= 32 plain passes: warp-group tcgen05 screening
+    return launch_lloyd_wg(p, reinterpret_cast<cudaStream_t>(a.stream));
   if (lloyd_tp_eligible(p, mode))                                        // k > 8 plain passes: pipelined tcgen05 screening + fp64 refinement
     return launch_lloyd_tp(p, reinterpret_cast<cudaStream_t>(a.stream));
   const int variant = lloyd_variant_override();
@@ -247,7 +249,7 @@ int hkm_max_k_single_pass(void) { return 64; }
 int hkm_max_d(void) { return 4096; }
 int hkm_needs_workspace(int d, int k) { return (k > kMaxFastK || !fits_fast(d, k)) ? 1 : 0; }
 int hkm_set_lloyd_variant(int variant) {
-  if (!((variant >= 0 && variant <= 5) || (variant == 40 || variant == 42 || variant == 43) || (variant >= 50 && variant <= 54))) { set_error("hkm_set_lloyd_variant: 0..5 (40..43 / 50..54: variant 4 with a pinned reduce scheme / warp budget)"); return HKM_ERR_INVALID; }
+  if (!((variant >= 0 && variant <= 6) || (variant == 40 || variant == 42 || variant == 43) || (variant >= 50 && variant <= 54))) { set_error("hkm_set_lloyd_variant: 0..6 (40..43 / 50..54: variant 4 with a pinned reduce scheme / warp budget)"); return HKM_ERR_INVALID; }
   g_lloyd_variant = variant;
   return HKM_OK;
 }

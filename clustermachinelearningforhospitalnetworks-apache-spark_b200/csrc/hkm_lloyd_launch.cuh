@@ -53,9 +53,12 @@ int launch_lloyd_tc(const LloydParams& p, cudaStream_t st);
 // pipelined tcgen05 variant (hkm_lloyd_tp.cuh): 8 < k <= 64, d <= 64, plain passes without per-row distances
 bool lloyd_tp_eligible(const LloydParams& p, int mode);
 int launch_lloyd_tp(const LloydParams& p, cudaStream_t st);
+// warp-group tcgen05 variant (hkm_lloyd_wg.cuh): 8 < k <= 32, d <= 32, plain passes without per-row distances
+bool lloyd_wg_eligible(const LloydParams& p, int mode);
+int launch_lloyd_wg(const LloydParams& p, cudaStream_t st);
 // 0: pick per shape (default); 1: always the gather variant; 2: the tensor-pipe variant wherever it is built;
 // 3: the warp-specialised variant wherever it is built; 4: the pipelined tcgen05 variant wherever it is built;
-// 5: the round-1 choice (no pipelined tcgen05 variant).  Set through hkm_set_lloyd_variant (tuning and tests).
+// 5: the round-1 choice (no pipelined tcgen05 variant); 6: the warp-group tcgen05 variant wherever it is built.  Set through hkm_set_lloyd_variant (tuning and tests).
 int lloyd_variant_override();
 
 // Validated, dispatched Lloyd data pass shared by the C entry points (hkm_api.cu).

@@ -136,7 +136,7 @@ __device__ __forceinline__ void tp_tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) 
                : "r"(taddr));
 }
 // mbarrier wait: the thread sleeps in hardware until the phase flips (suspend-time hint 1 ms per try, so a waiting warp
-// costs no issue slots); a protocol bug ends the kernel with a message after ~3 s instead of hanging the GPU
+// costs no issue slots); a protocol bug ends the kernel with a message after ~10 s instead of hanging the GPU
 __device__ __forceinline__ bool tp_try_wait(uint32_t bar, uint32_t parity) {
   uint32_t ok;
   asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\nselp.u32 %0, 1, 0, p;\n}\n"
@@ -145,11 +145,17 @@ __device__ __forceinline__ bool tp_try_wait(uint32_t bar, uint32_t parity) {
 }
 static __device__ __noinline__ void tp_wait_slow(uint32_t bar, uint32_t parity, int tag) {
   // the sleep ends at every barrier event of the CTA, so a wait wakes a few dozen times per tile: keep the wake-up path short
-  // (eight tries per watchdog count)
+  // (eight tries per loop trip; the watchdog reads the wall clock every 64 trips and gives up after 10 s)
+  unsigned long long t0 = 0;
 #pragma unroll 1
-  for (int it = 0; it < 400; ++it) {
+  for (unsigned it = 0;; ++it) {
 #pragma unroll
     for (int u = 0; u < 8; ++u) if (tp_try_wait(bar, parity)) return;
+    if ((it & 63u) == 63u) {
+      unsigned long long now;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+      if (t0 == 0) t0 = now; else if (now - t0 > 10000000000ull) break;
+    }
   }
   printf("lloyd_tp: block %d warp %d stuck on barrier tag %d (smem 0x%x, parity %u)\n", (int)blockIdx.x, (int)(threadIdx.x >> 5), tag, bar, parity);
   __trap();

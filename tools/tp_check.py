@@ -28,6 +28,9 @@ def _mods():
 
 def one(n, d, k, seed=0, tpv=4):
     np, torch, N, O = _mods()
+    if os.environ.get("HKM_WG_GROUPS"):
+        import ctypes
+        N.load().hkm_debug_wg_groups(ctypes.c_int(int(os.environ["HKM_WG_GROUPS"])))
     rng = np.random.default_rng(seed + n + 31 * d + 977 * k)
     prof = rng.normal(size=(k, d)) * 1.5
     Xh = prof[rng.integers(0, k, size=n)] + rng.normal(size=(n, d))
@@ -101,11 +104,11 @@ def bench(shapes, iters=10, extra=()):
 ROLE = ["screen"] * 8 + ["reduce"] * 4 + ["convert"] * 4 + ["producer", "mma"]
 
 
-def prof(shapes, iters=3, hospital=False):
+def prof(shapes, iters=3, hospital=False, variant=4, hook="hkm_debug_tp_profile", nw=18):
     """Per-warp cycle breakdown of CTA 0: where each role waits (site 0/1), refine cycles, listed rows."""
     import ctypes
     np, torch, N, O = _mods()
-    N.set_lloyd_variant(4)
+    N.set_lloyd_variant(variant)
     for n, d, k in shapes:
         g = torch.Generator(device="cuda"); g.manual_seed(1)
         if hospital:        # bench.py's table and centres: first k rows, then 10 Lloyd steps
@@ -122,18 +125,18 @@ def prof(shapes, iters=3, hospital=False):
             C = prof_c + 0.1
         partial = torch.empty(k * d + k + 1, dtype=torch.float64, device="cuda"); scratch = N.new_scratch(d, k, "cuda")
         xs = torch.zeros(1, dtype=torch.float64, device="cuda")
-        buf = torch.zeros(18 * 8, dtype=torch.int64, device="cuda")
+        buf = torch.zeros(nw * 8, dtype=torch.int64, device="cuda")
         N.assign_reduce(X, C, partial, scratch=scratch, xnorm2_sum=xs, xnorm2_mode=1)
-        fn = N.load().hkm_debug_tp_profile; fn.argtypes = [ctypes.c_void_p]; fn.restype = None
+        fn = getattr(N.load(), hook); fn.argtypes = [ctypes.c_void_p]; fn.restype = None
         fn(ctypes.c_void_p(buf.data_ptr()))
         for _ in range(iters):
             N.assign_reduce(X, C, partial, scratch=scratch, xnorm2_sum=xs, xnorm2_mode=2)
         torch.cuda.synchronize()
         fn(None)
-        b = buf.cpu().numpy().reshape(18, 8)
-        tiles = max(int(b[16, 6]), 1)
-        print(json.dumps(dict(n=n, d=d, k=k, tiles_cta0=tiles, clk_per_tile=round(float(b[16, 0]) / tiles, 1))))
-        for w in range(18):
+        b = buf.cpu().numpy().reshape(nw, 8)
+        tiles = max(int(b[0, 6]), 1)
+        print(json.dumps(dict(n=n, d=d, k=k, tiles_cta0=tiles, clk_per_tile=round(float(b[0, 0]) / tiles, 1))))
+        for w in range(nw):
             if b[w, 0] == 0:
                 continue
             print(f"  warp {w:2d} total/tile {b[w, 0] / tiles:8.1f}  wait0 {b[w, 1] / tiles:8.1f}  wait1 {b[w, 2] / tiles:8.1f}  refine {b[w, 3] / tiles:7.1f}  refined rows/tile {b[w, 5] / tiles:6.2f}")
@@ -148,6 +151,9 @@ if __name__ == "__main__":
         np, torch, N, O = _mods()
         n, d, k = int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4])
         N.set_lloyd_variant(int(sys.argv[5]) if len(sys.argv) > 5 else 4)
+        if os.environ.get("HKM_WG_GROUPS"):
+            import ctypes
+            N.load().hkm_debug_wg_groups(ctypes.c_int(int(os.environ["HKM_WG_GROUPS"])))
         g = torch.Generator(device="cuda"); g.manual_seed(1)
         pc = torch.randn(k, d, dtype=torch.float64, device="cuda", generator=g) * 2
         X = pc[torch.randint(0, k, (n,), device="cuda", generator=g)] + torch.randn(n, d, dtype=torch.float64, device="cuda", generator=g)
@@ -184,6 +190,40 @@ if __name__ == "__main__":
                 print(json.dumps(dict(n=n, d=d, k=k, v=v, timeout=True)), flush=True)
         print("ALL OK" if bad == 0 else f"FAILED {bad}")
         sys.exit(0 if bad == 0 else 1)
+    if cmd == "wgcheck":    # the warp-group variant (6) on every shape it takes
+        bad = 0
+        shapes = [(n, d, k) for n, d, k in CHECK_SHAPES if k <= 32 and d <= 32 and k > 8] + [(1, 16, 16), (129, 13, 9), (4097, 8, 31), (555, 32, 32), (100001, 17, 16), (3000000, 16, 16)]
+        for n, d, k in shapes:
+            for g in ([0] if n != 50000 else [0, 2, 3, 5]):
+                env = dict(os.environ, HKM_WG_GROUPS=str(g))
+                r = subprocess.run([sys.executable, __file__, "one", str(n), str(d), str(k), "6"], capture_output=True, text=True, timeout=180, env=env)
+                out = (r.stdout.strip().splitlines() or ["(no output)"])[-1]
+                if r.returncode != 0:
+                    bad += 1
+                    out += "  rc=%d %s" % (r.returncode, r.stderr.strip()[-400:].replace("\n", " | "))
+                print(("g=%d " % g) + out, flush=True)
+        print("ALL OK" if bad == 0 else f"FAILED {bad}")
+        sys.exit(0 if bad == 0 else 1)
+    if cmd == "wgprof":
+        import ctypes
+        np, torch, N, O = _mods()
+        for g in [int(a) for a in sys.argv[2:] if a.isdigit()] or [0]:
+            N.load().hkm_debug_wg_groups(ctypes.c_int(g))
+            print("groups", g, flush=True)
+            prof([(20_000_000, 16, 16), (10_000_000, 32, 16), (5_000_000, 24, 32)], hospital="hospital" in sys.argv, variant=6, hook="hkm_debug_wg_profile", nw=24)
+        sys.exit(0)
+    if cmd == "wgbench":
+        shapes = [(20_000_000, 16, 16), (5_000_000, 24, 16), (10_000_000, 32, 16), (10_000_000, 8, 16), (5_000_000, 24, 32), (5_000_000, 32, 32), (5_000_000, 16, 24),
+                  (5_000_000, 24, 12), (5_000_000, 16, 9), (5_000_000, 32, 20)]
+        import ctypes
+        np, torch, N, O = _mods()
+        if "short" in sys.argv:
+            shapes = shapes[:3]
+        for g in [int(a) for a in sys.argv[2:] if a.isdigit()] or [0]:
+            N.load().hkm_debug_wg_groups(ctypes.c_int(g))
+            print("groups", g, flush=True)
+            bench(shapes, extra=[(6, "wg")])
+        sys.exit(0)
     if cmd == "bench":
         extra = []
         if "modes" in sys.argv:
