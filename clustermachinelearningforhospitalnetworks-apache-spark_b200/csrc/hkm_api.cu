@@ -108,6 +108,8 @@ int generic_assign(const double* X, int64_t n, int d, const double* C, int k, in
 int generic_reduce(const double* X, int64_t n, int d, int kc, const int32_t* labels, int label_base, const double* w, const double* mind2,
                    const int32_t* skip, void* scratch, double* stats, cudaStream_t st);
 
+size_t assign_reduce_scratch_core(int d, int k);
+size_t wl_tail_offset(int d, int k);
 // the tiled (TMA ring) kernels take (d, k) when the row fits and at least two ring stages do
 static bool fits_fast(int d, int k) {
   if (d > kMaxFastD || k > kMaxFastK) return false;
@@ -131,7 +133,7 @@ int assign_pass(const AssignArgs& a, const char* who) {
   }
   if ((reinterpret_cast<uintptr_t>(a.X) & 15) != 0) { set_error("%s: X must be 16-byte aligned", who); return HKM_ERR_INVALID; }
   if (a.do_reduce && (a.partial_out == nullptr || a.scratch == nullptr)) { set_error("%s: reduce needs partial_out and scratch", who); return HKM_ERR_INVALID; }
-  if (a.do_reduce && a.scratch_bytes < hkm_assign_reduce_scratch_bytes(d, k)) { set_error("%s: scratch too small (%zu < %zu)", who, a.scratch_bytes, hkm_assign_reduce_scratch_bytes(d, k)); return HKM_ERR_INVALID; }
+  if (a.do_reduce && a.scratch_bytes < assign_reduce_scratch_core(d, k)) { set_error("%s: scratch too small (%zu < %zu)", who, a.scratch_bytes, assign_reduce_scratch_core(d, k)); return HKM_ERR_INVALID; }
   if (a.xnorm2_mode < 0 || a.xnorm2_mode > 2 || (a.xnorm2_mode != 0 && a.xnorm2_sum == nullptr)) { set_error("%s: bad xnorm2_mode/xnorm2_sum", who); return HKM_ERR_INVALID; }
   if (a.xnorm2_mode == 2 && a.mind2_out != nullptr) { set_error("%s: mind2_out needs per-row norms (xnorm2_mode 0 or 1)", who); return HKM_ERR_INVALID; }
   if (a.out_mode != 0 && a.mind2_out == nullptr) { set_error("%s: min-merge needs mind2", who); return HKM_ERR_INVALID; }
@@ -150,6 +152,17 @@ int assign_pass(const AssignArgs& a, const char* who) {
   p.stages = pl.stages; p.ks = (d + 3) / 4;
   const int grid = sm_count() * pl.ctas_per_sm;
   const int mode = (a.mode == 0 && a.weights != nullptr) ? 3 : a.mode;   // weights are a compile-time property of the Lloyd kernels
+  if (lloyd_wl_shape(p, mode) && a.scratch != nullptr && a.scratch_bytes >= wl_tail_offset(d, k) + wl_tail_bytes() && a.n > 0) {
+    // limb-reduction variant: the STORE pass also measures the column ranges (one more read of the table, once per fit); REUSE
+    // passes run the variant, which declines on its own when the record does not admit the table -- the launch below then works
+    void* tail = reinterpret_cast<unsigned char*>(a.scratch) + wl_tail_offset(d, k);
+    if (p.xx_mode == 1) { const int rc = launch_column_range(a.X, a.n, d, tail, reinterpret_cast<cudaStream_t>(a.stream)); if (rc != HKM_OK) return rc; }
+    if (p.xx_mode == 2) {
+      const int rc = launch_lloyd_wl(p, tail, reinterpret_cast<cudaStream_t>(a.stream));
+      if (rc != HKM_OK) return rc;
+      p.skip2 = reinterpret_cast<const int32_t*>(reinterpret_cast<unsigned char*>(tail) + wl_done_offset());
+    }
+  }
   if (lloyd_wg_eligible(p, mode))                                        // 8 < k <= 32, d <= 32 plain passes: warp-group tcgen05 screening
     return launch_lloyd_wg(p, reinterpret_cast<cudaStream_t>(a.stream));
   if (lloyd_tp_eligible(p, mode))                                        // k > 8 plain passes: pipelined tcgen05 screening + fp64 refinement
@@ -203,7 +216,7 @@ static int assign_pass_large(const AssignArgs& a, const char* who) {
   const int chunk = general ? generic_chunk_k(d) : kChunkK;
   if (a.labels_out == nullptr || a.mind2_out == nullptr) { set_error("%s: d=%d k=%d runs in centre chunks (k > %d, or a shape outside the tiled kernels) and needs labels_out and mind2_out (n entries each) as workspace", who, d, k, kChunkK); return HKM_ERR_INVALID; }
   if (a.mode != 0 || a.out_mode != 0 || a.C_update != nullptr || a.peer_bufs != nullptr) { set_error("%s: k=%d > %d supports plain passes only", who, k, kChunkK); return HKM_ERR_UNSUPPORTED; }
-  if (a.do_reduce && (a.partial_out == nullptr || a.scratch == nullptr || a.scratch_bytes < hkm_assign_reduce_scratch_bytes(d, k))) { set_error("%s: reduce needs partial_out and scratch of hkm_assign_reduce_scratch_bytes(d, k)", who); return HKM_ERR_INVALID; }
+  if (a.do_reduce && (a.partial_out == nullptr || a.scratch == nullptr || a.scratch_bytes < assign_reduce_scratch_core(d, k))) { set_error("%s: reduce needs partial_out and scratch of hkm_assign_reduce_scratch_bytes(d, k)", who); return HKM_ERR_INVALID; }
   cudaStream_t st = reinterpret_cast<cudaStream_t>(a.stream);
   if (a.n > 0) { fill_inf_kernel<<<sm_count() * 4, 256, 0, st>>>(a.mind2_out, a.n); HKM_CUDA_TRY(cudaGetLastError()); }
   for (int c0 = 0; c0 < k; c0 += chunk) {
@@ -216,7 +229,7 @@ static int assign_pass_large(const AssignArgs& a, const char* who) {
   if (!a.do_reduce) return HKM_OK;
   const int32_t* skip = a.state ? &a.state->converged : nullptr;
   // chunk statistics land behind the per-CTA partials of one chunk pass
-  const size_t chunk_scratch = general ? generic_scratch_bytes(d) : hkm_assign_reduce_scratch_bytes(d, kChunkK);
+  const size_t chunk_scratch = general ? generic_scratch_bytes(d) : assign_reduce_scratch_core(d, kChunkK);
   double* stats = reinterpret_cast<double*>(reinterpret_cast<unsigned char*>(a.scratch) + chunk_scratch);
   for (int c0 = 0; c0 < k; c0 += chunk) {
     const int kc = (k - c0 < chunk) ? (k - c0) : chunk;
@@ -236,6 +249,17 @@ static int assign_pass_large(const AssignArgs& a, const char* who) {
   return HKM_OK;
 }
 
+size_t assign_reduce_scratch_core(int d, int k) {
+  if (d < 1 || k < 1) return 0;
+  if (!fits_fast(d, k < 64 ? k : 64)) return generic_scratch_bytes(d) + ((size_t)64 * d + 2 * 64 + 2) * sizeof(double);   // general kernels: CTA partials + chunk statistics
+  if (k > 64) return assign_reduce_scratch_core(d, 64) + ((size_t)64 * d + 2 * 64 + 2) * sizeof(double);   // chunk pass + chunk statistics
+  const int k_pad = ((k + 7) / 8) * 8;
+  LaunchPlan pl = plan_lloyd(d, k_pad);
+  size_t grid = (size_t)sm_count() * (pl.ctas_per_sm > 2 ? pl.ctas_per_sm : 2);   // every variant launches at most this many CTAs
+  return 256 + grid * ((size_t)k * d + 2 * (size_t)k + 2) * sizeof(double);
+}
+size_t wl_tail_offset(int d, int k) { return (assign_reduce_scratch_core(d, k) + 255) & ~(size_t)255; }
+
 }  // namespace hkm
 
 using namespace hkm;
@@ -249,21 +273,17 @@ int hkm_max_k_single_pass(void) { return 64; }
 int hkm_max_d(void) { return 4096; }
 int hkm_needs_workspace(int d, int k) { return (k > kMaxFastK || !fits_fast(d, k)) ? 1 : 0; }
 int hkm_set_lloyd_variant(int variant) {
-  if (!((variant >= 0 && variant <= 6) || (variant == 40 || variant == 42 || variant == 43) || (variant >= 50 && variant <= 54))) { set_error("hkm_set_lloyd_variant: 0..6 (40..43 / 50..54: variant 4 with a pinned reduce scheme / warp budget)"); return HKM_ERR_INVALID; }
+  if (!((variant >= 0 && variant <= 7) || (variant == 40 || variant == 42 || variant == 43) || (variant >= 50 && variant <= 54))) { set_error("hkm_set_lloyd_variant: 0..7 (40..43 / 50..54: variant 4 with a pinned reduce scheme / warp budget)"); return HKM_ERR_INVALID; }
   g_lloyd_variant = variant;
   return HKM_OK;
 }
 
+// what the kernels' per-CTA partials need; hkm_assign_reduce_scratch_bytes adds the column range record of the limb-reduction
+// variant behind it (a scratch of only the core size still works: that variant is then not used)
 size_t hkm_assign_reduce_scratch_bytes(int d, int k) {
   if (d < 1 || k < 1) return 0;
-  if (!fits_fast(d, k < 64 ? k : 64)) return generic_scratch_bytes(d) + ((size_t)64 * d + 2 * 64 + 2) * sizeof(double);   // general kernels: CTA partials + chunk statistics
-  if (k > 64) return hkm_assign_reduce_scratch_bytes(d, 64) + ((size_t)64 * d + 2 * 64 + 2) * sizeof(double);   // chunk pass + chunk statistics
-  const int k_pad = ((k + 7) / 8) * 8;
-  LaunchPlan pl = plan_lloyd(d, k_pad);
-  size_t grid = (size_t)sm_count() * (pl.ctas_per_sm > 2 ? pl.ctas_per_sm : 2);   // every variant launches at most this many CTAs
-  return 256 + grid * ((size_t)k * d + 2 * (size_t)k + 2) * sizeof(double);
+  return wl_tail_offset(d, k) + wl_tail_bytes();
 }
-
 int hkm_assign_reduce(const double* X, int64_t n, int d, const double* C, int k, const double* weights, double* partial_out,
                       int32_t* labels_out, double* mind2_out, double* xnorm2_sum, int xnorm2_mode, const hkm_lloyd_state* state,
                       int do_reduce, void* scratch, size_t scratch_bytes, void* stream) {

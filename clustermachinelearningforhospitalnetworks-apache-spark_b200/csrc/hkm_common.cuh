@@ -100,6 +100,28 @@ __device__ __forceinline__ void dmma1684(double& c0, double& c1, double& c2, dou
   asm("mma.sync.aligned.m16n8k4.row.col.f64.f64.f64.f64 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
       : "+d"(c0), "+d"(c1), "+d"(c2), "+d"(c3) : "d"(a_lo), "d"(a_hi), "d"(b));
 }
+// Sum of n doubles base[0], base[stride], base[2 stride], ... in index order (the last-CTA fold of per-CTA partials).  The loads
+// of a batch are issued together and then added in order: same result as the plain loop, without a memory round trip per term.
+__device__ __forceinline__ double ordered_sum_ldcg(const double* base, size_t stride, unsigned n) {
+  double s = 0;
+  unsigned b = 0;
+#pragma unroll 1
+  for (; b + 16 <= n; b += 16) {
+    double v[16];
+#pragma unroll
+    for (int u = 0; u < 16; ++u) v[u] = __ldcg(base + (size_t)(b + u) * stride);
+#pragma unroll
+    for (int u = 0; u < 16; ++u) s += v[u];
+  }
+  if (b < n) {
+    double v[16];
+#pragma unroll
+    for (int u = 0; u < 16; ++u) v[u] = (b + u < n) ? __ldcg(base + (size_t)(b + u) * stride) : 0.0;
+#pragma unroll
+    for (int u = 0; u < 16; ++u) if (b + u < n) s += v[u];
+  }
+  return s;
+}
 __device__ __forceinline__ double shfl_xor_d(double v, int m) { return __shfl_xor_sync(0xffffffffu, v, m); }
 
 }  // namespace hkm

@@ -78,7 +78,7 @@ __global__ void __launch_bounds__(256) generic_assign_kernel(const double* __res
       if (s_ticket == gridDim.x - 1) {
         __threadfence();
         double tot = 0;
-        for (unsigned b = 0; b < gridDim.x; ++b) tot += __ldcg(cost_parts + b);
+        tot = ordered_sum_ldcg(cost_parts, 1, gridDim.x);
         *cost_out = tot; *counter = 0u;
       }
     }
@@ -121,7 +121,7 @@ __global__ void __launch_bounds__(256) generic_reduce_kernel(const double* __res
     __threadfence();
     for (int i = tid; i < S; i += 256) {
       double s = 0;
-      for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(partials + (size_t)b * S + i);
+      s = ordered_sum_ldcg(partials + i, (size_t)S, gridDim.x);
       stats[i] = s;
     }
     if (tid == 0) *counter = 0u;

@@ -42,6 +42,7 @@ struct LloydParams {
   int32_t* labels_out;     // nullable
   double* mind2_out;       // nullable
   const int32_t* skip;     // nullable: device flag, nonzero => no-op
+  const int32_t* skip2;    // nullable: second flag of the same kind (set by a variant launched ahead that already produced the pass)
   int do_reduce;           // 0: labels/mind2 only; 1: sums + counts + cost; 2: cost only (partial_out[0])
   const int32_t* labels_in;  // MODE 1/2 (silhouette): given cluster ids; ids outside [0, k) are ignored
   const double* aux;         // MODE 2: [k] cluster weight sums N, then [k] Psi/N
@@ -197,6 +198,7 @@ __host__ __device__ inline SmemLayout smem_layout(int d, int k_pad, int stages) 
 template <int KS_T, int NT, int LPR, int FPL, int MAXREG, int MODE = 0>
 __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kernel(const LloydParams p) {
   if (p.skip != nullptr && *p.skip != 0) return;
+  if (p.skip2 != nullptr && *p.skip2 != 0) return;
 
   extern __shared__ __align__(128) unsigned char smem[];
   const int d = p.d, k = p.k;
@@ -634,7 +636,7 @@ __global__ void __launch_bounds__(kThreads) __maxnreg__(MAXREG) lloyd_pass_kerne
     const int i_hi = MODE == 2 ? P + 1 : (p.do_reduce == 2 ? P : (MODE == 1 ? S : P + 1));
     for (int i = i_lo + tid; i < i_hi; i += kComputeThreads) {
       double s = 0;
-      for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(p.cta_partials + (size_t)b * S + i);
+      s = ordered_sum_ldcg(p.cta_partials + i, (size_t)S, gridDim.x);
       if (i == P - 1 && xx_mode == 2) s = fmax(fma(-2.0, s, *p.xnorm2_sum), 0.0);  // cost = sum w|x|^2 - 2 sum w*score
       if (MODE == 2) p.partial_out[i - (P - 1)] = s;           // [sum s*w, sum w]
       else if (p.do_reduce == 2) p.partial_out[0] = s;

@@ -56,9 +56,17 @@ int launch_lloyd_tp(const LloydParams& p, cudaStream_t st);
 // warp-group tcgen05 variant (hkm_lloyd_wg.cuh): 8 < k <= 32, d <= 32, plain passes without per-row distances
 bool lloyd_wg_eligible(const LloydParams& p, int mode);
 int launch_lloyd_wg(const LloydParams& p, cudaStream_t st);
+// limb-reduction variant (hkm_lloyd_wl.cuh): REUSE passes with 8 < k <= 64, d in {16, 32}, given the column range record that
+// launch_column_range leaves in the tail of the scratch during the STORE pass
+bool lloyd_wl_shape(const LloydParams& p, int mode);
+size_t wl_tail_bytes();
+size_t wl_done_offset();      // offset of the "pass produced" flag inside the record
+size_t assign_reduce_scratch_core(int d, int k);
+int launch_column_range(const double* X, int64_t n, int d, void* tail, cudaStream_t st);
+int launch_lloyd_wl(const LloydParams& p, void* tail, cudaStream_t st);
 // 0: pick per shape (default); 1: always the gather variant; 2: the tensor-pipe variant wherever it is built;
 // 3: the warp-specialised variant wherever it is built; 4: the pipelined tcgen05 variant wherever it is built;
-// 5: the round-1 choice (no pipelined tcgen05 variant); 6: the warp-group tcgen05 variant wherever it is built.  Set through hkm_set_lloyd_variant (tuning and tests).
+// 5: the round-1 choice (no pipelined tcgen05 variant); 6: the warp-group tcgen05 variant wherever it is built; 7: as 0 (the limb-reduction variant is a REUSE-pass refinement of 0).  Set through hkm_set_lloyd_variant (tuning and tests).
 int lloyd_variant_override();
 
 // Validated, dispatched Lloyd data pass shared by the C entry points (hkm_api.cu).

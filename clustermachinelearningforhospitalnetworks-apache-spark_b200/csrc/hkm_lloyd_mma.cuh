@@ -37,6 +37,7 @@ __host__ __device__ inline MmaSmemLayout mma_smem_layout(int d, int k_pad, int s
 template <int KS_T, int NT, int MAXREG, int MODE = 0>
 __global__ void __launch_bounds__(kMmaThreads) __maxnreg__(MAXREG) lloyd_mma_kernel(const LloydParams p) {
   if (p.skip != nullptr && *p.skip != 0) return;
+  if (p.skip2 != nullptr && *p.skip2 != 0) return;
   constexpr int ND = (KS_T + 1) / 2;
   constexpr int NDX = MODE == 1 ? ND + 1 : ND;   // accumulator feature tiles (one more for Psi)
   constexpr int k_pad = NT * 8;
@@ -359,7 +360,7 @@ __global__ void __launch_bounds__(kMmaThreads) __maxnreg__(MAXREG) lloyd_mma_ker
       const int i_lo = MODE == 2 ? P - 1 : 0, i_hi = MODE == 1 ? S : P + 1;
       for (int i = i_lo + tid; i < i_hi; i += kComputeThreads) {
         double s = 0;
-        for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(p.cta_partials + (size_t)b * S + i);
+        s = ordered_sum_ldcg(p.cta_partials + i, (size_t)S, gridDim.x);
         if (i == P - 1 && xx_mode == 2) s = fmax(fma(-2.0, s, *p.xnorm2_sum), 0.0);  // cost = sum |x|^2 - 2 sum score
         if (MODE == 2) p.partial_out[i - (P - 1)] = s;           // [sum s*w, sum w]
         else if (i < P) p.partial_out[i] = s;

@@ -55,6 +55,7 @@ __device__ __forceinline__ uint64_t umma_desc_kmajor(uint32_t saddr, uint32_t lb
 template <int NT, int FPL>
 __global__ void __launch_bounds__(kTcThreads, 1) lloyd_tc_kernel(const LloydParams p) {
   if (p.skip != nullptr && *p.skip != 0) return;
+  if (p.skip2 != nullptr && *p.skip2 != 0) return;
   constexpr int k_pad = NT * 8;
   constexpr int HALF = k_pad / 2;               // centres scanned per thread in the epilogue
 
@@ -441,7 +442,7 @@ __global__ void __launch_bounds__(kTcThreads, 1) lloyd_tc_kernel(const LloydPara
         const int i_lo = p.do_reduce == 2 ? P - 1 : 0, i_hi = p.do_reduce == 2 ? P : P + 1;
         for (int i = i_lo + tid; i < i_hi; i += kComputeThreads) {
           double sum = 0;
-          for (unsigned b = 0; b < gridDim.x; ++b) sum += __ldcg(p.cta_partials + (size_t)b * S + i);
+          sum = ordered_sum_ldcg(p.cta_partials + i, (size_t)S, gridDim.x);
           if (i == P - 1 && xx_mode == 2) sum = fmax(fma(-2.0, sum, *p.xnorm2_sum), 0.0);
           if (p.do_reduce == 2) p.partial_out[0] = sum;
           else if (i < P) p.partial_out[i] = sum;

@@ -180,6 +180,7 @@ __device__ __forceinline__ void sts_v2f64(uint32_t a, double x, double y) { asm 
 template <int KP, int CVEC, int RMODE, int WCFG, int ND>
 __global__ void __launch_bounds__(tp_warps(WCFG) * 32, tp_ctas_per_sm(WCFG)) lloyd_tp_kernel(const LloydParams p, const TpPlan L) {
   if (p.skip != nullptr && *p.skip != 0) return;
+  if (p.skip2 != nullptr && *p.skip2 != 0) return;
   constexpr int SG = tp_sg(WCFG), R = tp_reduce_warps(WCFG), CW = tp_conv_warps(WCFG);
   constexpr int kTpWarps = tp_warps(WCFG), kTpThreads = kTpWarps * 32;
   constexpr int kTpConvWarp0 = 4 * SG + R, kTpProdWarp = kTpConvWarp0 + CW, kTpMmaWarp = kTpProdWarp + 1;
@@ -726,13 +727,13 @@ __global__ void __launch_bounds__(tp_warps(WCFG) * 32, tp_ctas_per_sm(WCFG)) llo
     for (int i = tid; i < P + 1; i += kTpThreads) {
       if (i == P - 1) continue;
       double sum = 0;
-      for (unsigned bq = 0; bq < gridDim.x; ++bq) sum += __ldcg(p.cta_partials + (size_t)bq * SL + i);
+      sum = ordered_sum_ldcg(p.cta_partials + i, (size_t)SL, gridDim.x);
       if (i < P) p.partial_out[i] = sum; else red_s[0] = sum;    // i == P: sum |x|^2 over the whole pass
     }
     __syncthreads();
     if (tid == 0) {
       double ssc = 0;
-      for (unsigned bq = 0; bq < gridDim.x; ++bq) ssc += __ldcg(p.cta_partials + (size_t)bq * SL + (P - 1));
+      ssc = ordered_sum_ldcg(p.cta_partials + (P - 1), (size_t)SL, gridDim.x);
       const double xx = xx_mode == 2 ? *p.xnorm2_sum : red_s[0];
       if (xx_mode == 1) *p.xnorm2_sum = xx;
       p.partial_out[P - 1] = fmax(fma(-2.0, ssc, xx), 0.0);      // cost = sum |x|^2 - 2 sum score

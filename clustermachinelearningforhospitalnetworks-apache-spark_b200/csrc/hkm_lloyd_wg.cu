@@ -11,11 +11,13 @@ static int g_wg_groups = -1;    // developer override of the group count
 // Plain passes (unit weights, labels and/or sums, no per-row distances) with 8 < k <= 32 and d <= 32.
 bool lloyd_wg_eligible(const LloydParams& p, int mode) {
   const int variant = lloyd_variant_override();
-  if (variant != 6) return false;   // TODO default
+  if (variant != 0 && variant != 6) return false;
   if (mode != 0 || p.w != nullptr || p.out_mode != 0 || p.mind2_out != nullptr || p.do_reduce > 1) return false;
   if (p.k > 32 || p.d > 32) return false;
   if (p.k <= 8 && variant == 0) return false;
   const int kp = ((p.k + 15) / 16) * 16;
+  // measured against the pipelined variant on the same box (tools/tp_check.py wgbench): ahead for k <= 16 with 8 < d <= 24
+  if (variant == 0 && !(kp == 16 && p.d > 8 && p.d <= 24)) return false;
   return wg_choose(p.d, kp, g_wg_groups).stages > 0;
 }
 

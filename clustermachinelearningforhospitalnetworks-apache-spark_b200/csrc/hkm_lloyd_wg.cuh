@@ -107,6 +107,7 @@ __host__ inline WgPlan wg_choose(int d, int kp, int force_groups = -1) {
 template <int KP, int CVEC, int ND, int MAXT, int DFIX = 0, int GFIX = 0>
 __global__ void __launch_bounds__(MAXT, 1) lloyd_wg_kernel(const LloydParams p, const WgPlan Lrt) {
   if (p.skip != nullptr && *p.skip != 0) return;
+  if (p.skip2 != nullptr && *p.skip2 != 0) return;
   constexpr int NW = (KP + 31) / 32;              // candidate mask words
   constexpr int MT = KP / 16;                     // 16-cluster row tiles of the one-hot product
   constexpr int TSTRIDE = 32;
@@ -584,13 +585,13 @@ __global__ void __launch_bounds__(MAXT, 1) lloyd_wg_kernel(const LloydParams p, 
     for (int i = tid; i < P + 1; i += nthreads) {
       if (i == P - 1) continue;
       double sum = 0;
-      for (unsigned bq = 0; bq < gridDim.x; ++bq) sum += __ldcg(p.cta_partials + (size_t)bq * SL + i);
+      sum = ordered_sum_ldcg(p.cta_partials + i, (size_t)SL, gridDim.x);
       if (i < P) p.partial_out[i] = sum; else red_s[0] = sum;    // i == P: sum |x|^2 over the whole pass
     }
     __syncthreads();
     if (tid == 0) {
       double ssc = 0;
-      for (unsigned bq = 0; bq < gridDim.x; ++bq) ssc += __ldcg(p.cta_partials + (size_t)bq * SL + (P - 1));
+      ssc = ordered_sum_ldcg(p.cta_partials + (P - 1), (size_t)SL, gridDim.x);
       const double xx = xx_mode == 2 ? *p.xnorm2_sum : red_s[0];
       if (xx_mode == 1) *p.xnorm2_sum = xx;
       p.partial_out[P - 1] = fmax(fma(-2.0, ssc, xx), 0.0);      // cost = sum |x|^2 - 2 sum score

@@ -1,0 +1,160 @@
+// Host side of the limb-reduction Lloyd pass (hkm_lloyd_wl.cuh): the column range pass, tensor-map construction, dispatch.
+#include "../../include/hkm.h"
+#include "hkm_lloyd_launch.cuh"
+#include "hkm_lloyd_wl.cuh"
+
+namespace hkm {
+
+static unsigned long long* g_wl_prof = nullptr;
+static int g_wl_off = 0;       // developer switch: 1 = never use this variant
+static int g_wl_flags = -1;    // developer switch: bit 0 = close the previous tile at the top of the iteration when its product is done
+static int g_wl_groups = 0;    // developer switch: group count for d = 16, k <= 16 (4, 5 or 6)
+
+// ---- column range pass: per column the largest magnitude (its exponent) and the mean exponent of the nonzero values; one read of
+// the table, run in the STORE pass of a fit.  Thread = (row of a group, feature pair); integer statistics only, so the result does
+// not depend on the order in which CTAs finish.
+__global__ void __launch_bounds__(256) column_range_kernel(const double* __restrict__ X, int64_t n, int d, RangeRec* rec) {
+  __shared__ unsigned int s_ticket;
+  __shared__ int s_ok;
+  const int tid = threadIdx.x, hp = d / 2, rpb = blockDim.x / hp;          // blockDim.x is a multiple of d / 2
+  const int pf = tid % hp, r = tid / hp;
+  unsigned int mx0 = 0, mx1 = 0, es0 = 0, es1 = 0, nz0 = 0, nz1 = 0;
+  unsigned long long ES0 = 0, ES1 = 0, NZ0 = 0, NZ1 = 0;
+  const int64_t step = (int64_t)gridDim.x * rpb;
+  int flush = 0;
+  for (int64_t row = (int64_t)blockIdx.x * rpb + r; row < n; row += 4 * step) {
+    double2 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int64_t rr = row + u * step;
+      v[u] = rr < n ? __ldcs(reinterpret_cast<const double2*>(X + (size_t)rr * d) + pf) : make_double2(0.0, 0.0);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const unsigned int h0 = (unsigned int)__double2hiint(v[u].x) & 0x7fffffffu, h1 = (unsigned int)__double2hiint(v[u].y) & 0x7fffffffu;
+      mx0 = max(mx0, h0); mx1 = max(mx1, h1);
+      const unsigned int e0 = h0 >> 20, e1 = h1 >> 20;
+      es0 += e0; es1 += e1; nz0 += e0 != 0u; nz1 += e1 != 0u;
+    }
+    if (++flush == 256) { ES0 += es0; ES1 += es1; NZ0 += nz0; NZ1 += nz1; es0 = es1 = nz0 = nz1 = 0u; flush = 0; }   // 32-bit partials: 4 * 256 * 2047 fits
+  }
+  ES0 += es0; ES1 += es1; NZ0 += nz0; NZ1 += nz1;
+  // combine the CTA's rows per feature pair in shared memory, then one set of integer atomics per CTA and feature
+  __shared__ unsigned int s_mx[2][256];
+  __shared__ unsigned long long s_es[2][256], s_nz[2][256];
+  s_mx[0][tid] = mx0; s_mx[1][tid] = mx1; s_es[0][tid] = ES0; s_es[1][tid] = ES1; s_nz[0][tid] = NZ0; s_nz[1][tid] = NZ1;
+  __syncthreads();
+  if (tid < d) {
+    const int pp = tid >> 1, e = tid & 1;
+    unsigned int m = 0; unsigned long long es = 0, nz = 0;
+    for (int q = 0; q < rpb; ++q) { m = max(m, s_mx[e][q * hp + pp]); es += s_es[e][q * hp + pp]; nz += s_nz[e][q * hp + pp]; }
+    atomicMax(&rec->emax_hi[tid], m); atomicAdd(&rec->esum[tid], es); atomicAdd(&rec->nnz[tid], nz);
+  }
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) s_ticket = atomicAdd(&rec->ticket, 1u);
+  __syncthreads();
+  if (s_ticket != gridDim.x - 1) return;
+  __threadfence();
+  if (tid == 0) s_ok = 1;
+  __syncthreads();
+  if (tid < d) {
+    const unsigned int e = __ldcg(&rec->emax_hi[tid]) >> 20;                 // biased exponent of the largest magnitude
+    const unsigned long long es = __ldcg(&rec->esum[tid]), nz = __ldcg(&rec->nnz[tid]);
+    bool ok = e + 2u < 0x7ffu;                                               // finite, and room for M_f
+    if (ok && nz > 0) ok = (unsigned long long)e * nz <= es + 20ull * nz;    // e - mean exponent <= 20
+    if (!ok) s_ok = 0;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    rec->tag_x = (unsigned long long)(uintptr_t)X; rec->n = (long long)n; rec->d = d; rec->done = 0; rec->ticket = 0u;
+    __threadfence();
+    rec->ok = s_ok;
+  }
+}
+
+size_t wl_done_offset() { return offsetof(RangeRec, done); }
+size_t wl_tail_bytes() { return 2048; }
+
+// Shapes and passes this variant takes (given a valid record): plain Lloyd passes with sums, 8 < k <= 64, d in {16, 32}
+bool lloyd_wl_shape(const LloydParams& p, int mode) {
+  const int variant = lloyd_variant_override();
+  if (g_wl_off || (variant != 0 && variant != 7)) return false;
+  if (mode != 0 || p.w != nullptr || p.out_mode != 0 || p.mind2_out != nullptr || p.do_reduce != 1) return false;
+  if (p.k <= 8 || p.k > 64 || (p.d != 16 && p.d != 32)) return false;
+  if (p.n >= (int64_t)1 << 31) return false;                                   // tensor-map row coordinates are 32-bit
+  if (p.n / kTileRows / sm_count() > 60000) return false;                      // s32 limb columns: 65 000 tiles per group
+  const int kp = ((p.k + 15) / 16) * 16;
+  return wl_groups(p.d, kp) > 0;
+}
+
+int launch_column_range(const double* X, int64_t n, int d, void* tail, cudaStream_t st) {
+  static_assert(sizeof(RangeRec) <= 2048, "range record");
+  RangeRec* rec = reinterpret_cast<RangeRec*>(tail);
+  HKM_CUDA_TRY(cudaMemsetAsync(rec, 0, sizeof(RangeRec), st));
+  const int tpb = (256 / (d / 2)) * (d / 2);
+  column_range_kernel<<<4 * sm_count(), tpb, 0, st>>>(X, n, d, rec);
+  HKM_CUDA_TRY(cudaGetLastError());
+  return HKM_OK;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) == cudaSuccess && qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  }
+  return fn;
+}
+
+template <int KP, int NS, int GO = 0>
+static int launch_wl(const LloydParams& p, const CUtensorMap& tmap, RangeRec* rec, cudaStream_t st) {
+  constexpr int G = GO > 0 ? GO : wl_groups(16 * NS, KP);
+  if constexpr (G == 0) { set_error("lloyd_wl: d=%d k=%d does not fit", p.d, p.k); return HKM_ERR_UNSUPPORTED; }
+  else {
+    constexpr WlPlan L = wl_plan(16 * NS, KP, G, wl_stages(16 * NS, KP, G));
+    auto kern = lloyd_wl_kernel<KP, NS, G>;
+    static bool attr_done[64];
+    int dev = 0; HKM_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev >= 64 || !attr_done[dev]) {
+      HKM_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total + 1024));
+      if (dev < 64) attr_done[dev] = true;
+    }
+    kern<<<sm_count(), G * 128, L.total + 1024, st>>>(p, tmap, rec, g_wl_prof, g_wl_flags >= 0 ? g_wl_flags : (((NS == 2 && KP == 16) || (NS == 1 && KP == 32)) ? 1 : 0));
+    HKM_CUDA_TRY(cudaGetLastError());
+    return HKM_OK;
+  }
+}
+
+int launch_lloyd_wl(const LloydParams& p, void* tail, cudaStream_t st) {
+  EncodeTiledFn enc = encode_tiled();
+  if (enc == nullptr) { set_error("lloyd_wl: cuTensorMapEncodeTiled is not available"); return HKM_ERR_UNSUPPORTED; }
+  CUtensorMap tmap;
+  const cuuint64_t gdim[2] = {(cuuint64_t)p.d, (cuuint64_t)p.n};
+  const cuuint64_t gstride[1] = {(cuuint64_t)p.d * 8};
+  const cuuint32_t box[2] = {16, 32}, estr[2] = {1, 1};
+  const CUresult cr = enc(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<double*>(p.X), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (cr != CUDA_SUCCESS) { set_error("lloyd_wl: cuTensorMapEncodeTiled failed (%d)", (int)cr); return HKM_ERR_CUDA; }
+  RangeRec* rec = reinterpret_cast<RangeRec*>(tail);
+  const int kp = ((p.k + 15) / 16) * 16, ns = p.d / 16;
+#define HKM_WL_CASE(KPV, NSV) if (kp == KPV && ns == NSV) return launch_wl<KPV, NSV>(p, tmap, rec, st);
+  if (kp == 16 && ns == 1 && g_wl_groups == 4) return launch_wl<16, 1, 4>(p, tmap, rec, st);
+  if (kp == 16 && ns == 1 && g_wl_groups == 5) return launch_wl<16, 1, 5>(p, tmap, rec, st);
+  HKM_WL_CASE(16, 1) HKM_WL_CASE(32, 1) HKM_WL_CASE(48, 1) HKM_WL_CASE(64, 1)
+  HKM_WL_CASE(16, 2) HKM_WL_CASE(32, 2) HKM_WL_CASE(48, 2) HKM_WL_CASE(64, 2)
+#undef HKM_WL_CASE
+  set_error("lloyd_wl: no instantiation for d=%d k=%d", p.d, p.k);
+  return HKM_ERR_UNSUPPORTED;
+}
+
+}  // namespace hkm
+
+extern "C" __attribute__((visibility("default"))) void hkm_debug_wl_profile(void* buf) { hkm::g_wl_prof = reinterpret_cast<unsigned long long*>(buf); }
+extern "C" __attribute__((visibility("default"))) void hkm_debug_wl_off(int off) { hkm::g_wl_off = off; }
+extern "C" __attribute__((visibility("default"))) void hkm_debug_wl_groups(int g) { hkm::g_wl_groups = g; }
+extern "C" __attribute__((visibility("default"))) void hkm_debug_wl_flags(int f) { hkm::g_wl_flags = f; }

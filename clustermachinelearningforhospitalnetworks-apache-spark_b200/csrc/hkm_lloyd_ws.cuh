@@ -62,6 +62,7 @@ __host__ __device__ inline int ws_score_warps(int nt) { (void)nt; return 8; }
 template <int KS_T, int NT, int SW, int NSET, int MAXREG>
 __global__ void __launch_bounds__(kWsThreads) __maxnreg__(MAXREG) lloyd_ws_kernel(const LloydParams p) {
   if (p.skip != nullptr && *p.skip != 0) return;
+  if (p.skip2 != nullptr && *p.skip2 != 0) return;
   constexpr int k_pad = NT * 8;
   constexpr int RW = kWsWarps - SW;
   constexpr int RROWS = 16;                 // reduce item: one 16-row chunk ("slice") of a tile, 8 per tile
@@ -391,7 +392,7 @@ __global__ void __launch_bounds__(kWsThreads) __maxnreg__(MAXREG) lloyd_ws_kerne
     __threadfence();
     for (int i = tid; i < P + 1; i += kWsThreads) {
       double s = 0;
-      for (unsigned b = 0; b < gridDim.x; ++b) s += __ldcg(p.cta_partials + (size_t)b * S + i);
+      s = ordered_sum_ldcg(p.cta_partials + i, (size_t)S, gridDim.x);
       if (i == P - 1 && xx_mode == 2) s = fmax(fma(-2.0, s, *p.xnorm2_sum), 0.0);  // cost = sum |x|^2 - 2 sum score
       if (i < P) p.partial_out[i] = s;
       else if (xx_mode == 1) *p.xnorm2_sum = s;

@@ -47,7 +47,7 @@ extern "C" int hkm_assign_reduce_noalloc(const double* X, int64_t n, int d, cons
     hkm::set_error("hkm_assign_reduce_noalloc: k=%d, d=%d runs in centre chunks with per-row workspace; use hkm_assign_reduce for this shape", k, d);
     return HKM_ERR_UNSUPPORTED;
   }
-  const size_t need = hkm_assign_reduce_scratch_bytes(d, k);
+  const size_t need = hkm::assign_reduce_scratch_core(d, k);   // without the optional column range record
   if (need > (size_t)HKM_NOALLOC_SCRATCH_BYTES) {
     hkm::set_error("hkm_assign_reduce_noalloc: k=%d, d=%d needs %zu bytes of scratch but the built-in array holds %zu; "
                    "use hkm_assign_reduce with caller-allocated scratch for this shape",
