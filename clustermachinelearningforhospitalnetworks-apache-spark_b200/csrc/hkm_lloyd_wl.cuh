@@ -49,7 +49,7 @@ struct WlPlan {
 };
 
 // Tensor memory, per group: [tf32 operand: d data columns + 8 constant columns][scores: k_pad], then behind all groups the s32 limb
-// sums [group][slab][k_pad].  Shared memory: ring stages (1024-byte aligned), the centres' tf32 operand, the one-hot operands.
+// sums [slab][k_pad], one set for the whole CTA (every warp adds its products into it).  Shared memory: ring stages (1024-byte aligned), the centres' tf32 operand, the one-hot operands.
 __host__ __device__ constexpr inline WlPlan wl_plan(int d, int kp, int groups, int stages) {
   WlPlan L{};
   L.groups = groups; L.stages = stages;
@@ -63,7 +63,7 @@ __host__ __device__ constexpr inline WlPlan wl_plan(int d, int kp, int groups, i
   L.tstride = kp <= 32 ? 32 : 64;
   L.gstride = L.acols + L.tstride;
   L.rcol0 = groups * L.gstride;
-  int tc = 32; while (tc < L.rcol0 + groups * ns * kp) tc *= 2;
+  int tc = 32; while (tc < L.rcol0 + ns * kp) tc *= 2;
   L.tcols = tc;
   int o = 0;
   L.x_off = o; o += stages * L.tile_bytes;         // 1024-byte aligned (swizzle atoms)
@@ -88,13 +88,13 @@ __host__ __device__ constexpr inline int wl_stages(int d, int kp, int g) {
   if (z.tcols > 512) return 0;
   int st = (227 * 1024 - 4096 - z.total) / z.tile_bytes;     // 1 KB alignment slack, static shared memory of the tail
   if (st > kWlMaxStages) st = kWlMaxStages;
-  const int comb = g * (d / 16) * kp * 128 * 4;     // s32 accumulators parked in the idle ring for the final combine
+  const int comb = (d / 16) * kp * 128 * 4;         // s32 accumulators parked in the idle ring for the final combine
   if (st < g + 2 || (st - g) * z.tile_bytes < 40 * 1024 || st * z.tile_bytes < comb) return 0;
   return st;
 }
 // group count per shape (0: shape not taken)
 __host__ __device__ constexpr inline int wl_groups(int d, int kp) {
-  for (int g = (d == 16 ? 6 : 4); g >= 2; --g) if (wl_stages(d, kp, g) > 0) return g;
+  for (int g = 6; g >= 2; --g) if (wl_stages(d, kp, g) > 0) return g;
   return 0;
 }
 
@@ -117,7 +117,7 @@ __device__ __forceinline__ void wl_tmem_st8(uint32_t taddr, const uint32_t (&v)[
 }
 __device__ __forceinline__ void wl_tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
-// KP = padded cluster count (16..64); NS = d / 16 (slabs of 128 bytes per row); GFIX = groups of four warps.
+// KP = padded cluster count (16..64); NS = ceil(d / 16) (slabs of 128 bytes per row; d even); GFIX = groups of four warps.
 // Thread = row throughout: a thread reads its row through the swizzle (eight consecutive rows hit eight different 16-byte columns),
 // writes the tf32 values into its lane of the group's tensor-memory operand (the tensor core takes A from TMEM: no shared-memory
 // copy of the operand at all), keeps |x - mu|^2 in a register, and overwrites the row in place with its fixed-point form.
@@ -125,8 +125,9 @@ template <int KP, int NS, int GFIX>
 __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydParams p, const __grid_constant__ CUtensorMap tmap, RangeRec* rec,
                                                                  unsigned long long* prof_buf, int flags) {
   if (p.skip != nullptr && *p.skip != 0) return;
-  constexpr int d = 16 * NS, ND = 2 * NS, G = GFIX, S = wl_stages(d, KP, GFIX);
-  constexpr WlPlan L = wl_plan(d, KP, GFIX, S);
+  constexpr int DP = 16 * NS, ND = 2 * NS, G = GFIX, S = wl_stages(DP, KP, GFIX);   // DP: features padded to whole slabs
+  constexpr WlPlan L = wl_plan(DP, KP, GFIX, S);
+  const int d = p.d;                                  // even, DP - 16 < d <= DP; the padding columns arrive as zeros (tensor-map bounds)
   static_assert(S >= GFIX + 2, "shape does not fit");
   constexpr int NW = (KP + 31) / 32;
   constexpr int IDXBITS = 6;
@@ -135,7 +136,7 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
   constexpr uint32_t LBO_B = L.lbo_b, LBO_H = L.lbo_h, tile_bytes = L.tile_bytes;
   constexpr uint32_t SLAB = kTileRows * 128;          // bytes of one 16-feature slab of a tile
   // the record must describe this table and admit it; otherwise the launch behind this one does the pass
-  if (rec->ok != 1 || rec->tag_x != (unsigned long long)(uintptr_t)p.X || rec->n != (long long)p.n || rec->d != d) {
+  if (rec->ok != 1 || rec->tag_x != (unsigned long long)(uintptr_t)p.X || rec->n != (long long)p.n || rec->d != p.d) {
     if (blockIdx.x == 0 && threadIdx.x == 0) rec->done = 0;
     return;
   }
@@ -181,10 +182,10 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
   for (int i = tid; i < KP; i += nthreads) cnt_s[i] = 0u;
   for (int i = tid; i < 4 * S; i += nthreads) reinterpret_cast<uint32_t*>(smem + L.seq_off)[i] = (uint32_t)(i >> 2);
   if (L.cs_off != 0) for (int i = tid; i < k * d; i += nthreads) reinterpret_cast<double*>(smem + L.cs_off)[i] = p.C[i];
-  if (tid < d + 8) { double s = 0; if (tid < d) for (int j = 0; j < k; ++j) s += p.C[(size_t)j * d + tid]; mu_s[tid] = tid < d ? s / k : 0.0; }
-  if (tid < d) {
-    // M_f = 1.5 * 2^(E_f + 2): exponent field of the column's largest magnitude + 2, top mantissa bit set
-    const unsigned eb = (rec->emax_hi[tid] >> 20) & 0x7ffu;
+  if (tid < DP + 8) { double s = 0; if (tid < d) for (int j = 0; j < k; ++j) s += p.C[(size_t)j * d + tid]; mu_s[tid] = tid < d ? s / k : 0.0; }
+  if (tid < DP) {
+    // M_f = 1.5 * 2^(E_f + 2): exponent field of the column's largest magnitude + 2, top mantissa bit set (padding columns: 1.5)
+    const unsigned eb = tid < d ? (rec->emax_hi[tid] >> 20) & 0x7ffu : 1021u;
     mg_s[tid] = __longlong_as_double(((long long)(eb + 2u) << 52) | (1ll << 51));
   }
   __syncthreads();
@@ -195,11 +196,11 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
     cn_s[tid] = tid < k ? -0.5 * s : -__longlong_as_double(0x7ff0000000000000LL);
     h_s[tid] = tid < k ? sc : 0.0;
   }
-  for (int i = tid; i < KP * (d / 4); i += nthreads) {
+  for (int i = tid; i < KP * (DP / 4); i += nthreads) {
     const int j = i % KP, c = i / KP;
     uint32_t vv[4];
 #pragma unroll
-    for (int e = 0; e < 4; ++e) { const int f = 4 * c + e; vv[e] = j < k ? f32_to_tf32_rn((float)(p.C[(size_t)j * d + f] - mu_s[f])) : 0u; }
+    for (int e = 0; e < 4; ++e) { const int f = 4 * c + e; vv[e] = (j < k && f < d) ? f32_to_tf32_rn((float)(p.C[(size_t)j * d + f] - mu_s[f])) : 0u; }
     *reinterpret_cast<uint4*>(smem + L.b_off + c * LBO_B + (j >> 3) * 128 + (j & 7) * 16) = make_uint4(vv[0], vv[1], vv[2], vv[3]);
   }
   __syncthreads();
@@ -210,7 +211,7 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
     const float mid = __uint_as_float(f32_to_tf32_rn((float)r1));
     const double r2 = r1 - (double)mid;
     const float lo = __uint_as_float(f32_to_tf32_rn((float)r2));
-    *reinterpret_cast<uint4*>(smem + L.b_off + (d / 4) * LBO_B + (tid >> 3) * 128 + (tid & 7) * 16) =
+    *reinterpret_cast<uint4*>(smem + L.b_off + (DP / 4) * LBO_B + (tid >> 3) * 128 + (tid & 7) * 16) =
         make_uint4(__float_as_uint(hi), __float_as_uint(mid), __float_as_uint(lo), 0u);
   }
   float vmax2 = 0.f;
@@ -231,11 +232,11 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
     // the eight constant columns behind the data columns: (1, 1, 1, 0, ...) against the hi/mid/lo split of -0.5|c - mu|^2
     const uint32_t one = __float_as_uint(1.0f);
     const uint32_t cv[8] = {one, one, one, 0u, 0u, 0u, 0u, 0u};
-    wl_tmem_st8(t_A + (uint32_t)d, cv);
+    wl_tmem_st8(t_A + (uint32_t)DP, cv);
     // the limb sums start at zero (every product below accumulates; the four warps of a group issue theirs independently)
     const uint32_t zv[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
 #pragma unroll 1
-    for (int c0 = 0; c0 < NS * KP; c0 += 8) wl_tmem_st8(tmem + tlane + (uint32_t)L.rcol0 + (uint32_t)(grp * NS * KP + c0), zv);
+    if (grp == 0) for (int c0 = 0; c0 < NS * KP; c0 += 8) wl_tmem_st8(tmem + tlane + (uint32_t)L.rcol0 + (uint32_t)c0, zv);
     wl_tmem_wait_st();
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   }
@@ -299,7 +300,7 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
   const uint64_t db0 = tp_desc_kmajor(a_B, LBO_B, 128u);
   const uint32_t db_step = (2u * LBO_B) >> 4;
   const uint32_t acol = tmem + (uint32_t)grp * (uint32_t)L.gstride, dcol = acol + (uint32_t)L.acols;
-  const uint32_t rcol = tmem + (uint32_t)L.rcol0 + (uint32_t)(grp * NS) * (uint32_t)KP;
+  const uint32_t rcol = tmem + (uint32_t)L.rcol0;
   const uint64_t dh0 = wl_desc(a_H, LBO_H, 128u, 0u);
   const uint32_t dh_step = (2u * LBO_H) >> 4;
   // mu as packed float pairs: in registers for one slab, re-read (broadcast) from shared memory for wider rows
@@ -314,9 +315,9 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
       for (int c = 0; c < 8; ++c) asm("mov.b64 %0, {%1,%2};" : "=l"(mu_r[c]) : "f"(t[c].x), "f"(t[c].y));
     } else {
       float2 mine = make_float2(0.f, 0.f);
-      if (tid < d / 2) mine = make_float2((float)mu_s[2 * tid], (float)mu_s[2 * tid + 1]);
+      if (tid < DP / 2) mine = make_float2((float)mu_s[2 * tid], (float)mu_s[2 * tid + 1]);
       __syncthreads();
-      if (tid < d / 2) mu2_s[tid] = mine;
+      if (tid < DP / 2) mu2_s[tid] = mine;
       __syncthreads();
       mu_r[0] = 0;
     }
@@ -537,21 +538,21 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
     o[4] = 0ull; o[5] = (unsigned long long)pcnt; o[6] = (unsigned long long)T; o[7] = 0ull;
   }
   // ===================================================================== CTA-level combine (all warps)
-  // every tile is reduced and no copy is in flight: the s32 limb sums go from TMEM to the idle ring, acc[(g NS + sl) KP + c][byte]
+  // every tile is reduced and no copy is in flight: the s32 limb sums go from TMEM to the idle ring, acc[sl KP + c][byte]
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   int32_t* acc_s = reinterpret_cast<int32_t*>(smem + L.x_off);
-  {
+  if (grp == 0) {
 #pragma unroll 1
     for (int sl = 0; sl < NS; ++sl)
 #pragma unroll 1
       for (int c0 = 0; c0 < KP; c0 += 16) {
         uint32_t v[16];
-        tp_tmem_ld16(tmem + tlane + (uint32_t)L.rcol0 + (uint32_t)((grp * NS + sl) * KP + c0), v);
+        tp_tmem_ld16(tmem + tlane + (uint32_t)L.rcol0 + (uint32_t)(sl * KP + c0), v);
         tp_tmem_wait_ld();
 #pragma unroll
-        for (int c = 0; c < 16; ++c) acc_s[(size_t)((grp * NS + sl) * KP + c0 + c) * 128 + row] = (int32_t)v[c];
+        for (int c = 0; c < 16; ++c) acc_s[(size_t)(sl * KP + c0 + c) * 128 + row] = (int32_t)v[c];
       }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -560,11 +561,9 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
   for (int idx = tid; idx < k * d; idx += nthreads) {
     const int j = idx / d, f = idx - j * d, sl = f >> 4, b0 = 8 * (f & 15);
     __int128 tot = 0;
-    for (int g = 0; g < G; ++g) {
-      const int32_t* a = acc_s + (size_t)((g * NS + sl) * KP + j) * 128 + b0;
+    const int32_t* a = acc_s + (size_t)(sl * KP + j) * 128 + b0;
 #pragma unroll
-      for (int l = 0; l < 8; ++l) tot += (__int128)(long long)a[l] << (8 * l);
-    }
+    for (int l = 0; l < 8; ++l) tot += (__int128)(long long)a[l] << (8 * l);
     const unsigned long long mbits = (unsigned long long)__double_as_longlong(mg_s[f]);
     tot -= (__int128)(unsigned long long)cnt_s[j] * (__int128)mbits;            // every row of the cluster carried the bits of M_f
     // tot = sum of round(x / 2^(E_f - 50)); |tot| < 2^83: two halves, one rounding each

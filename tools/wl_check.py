@@ -93,6 +93,7 @@ if __name__ == "__main__":
     if cmd == "check":
         cases = [(5000, 16, 16, "blobs"), (128, 16, 16, "blobs"), (100, 16, 9, "blobs"), (1, 16, 12, "blobs"), (200000, 16, 16, "blobs"), (30011, 16, 33, "blobs"),
                  (40000, 16, 40, "blobs"), (45000, 16, 64, "blobs"), (50000, 32, 20, "blobs"), (60000, 32, 64, "blobs"), (129, 32, 17, "blobs"),
+                 (30000, 24, 17, "blobs"), (30011, 24, 32, "blobs"), (9000, 12, 20, "blobs"), (33333, 2, 10, "blobs"), (70003, 8, 12, "blobs"), (3000, 30, 33, "blobs"), (4097, 22, 64, "blobs"),
                  (70000, 16, 16, "offset"), (70000, 16, 24, "scales"), (50000, 16, 16, "outlier"), (3000000, 16, 16, "blobs")]
         bad = 0
         for n, d, k, kind in cases:
@@ -157,4 +158,5 @@ if __name__ == "__main__":
             bench([(20_000_000, 16, 16), (5_000_000, 16, 12)])
         sys.exit(0)
     if cmd == "bench":
-        bench([(20_000_000, 16, 16), (20_000_000, 16, 32), (20_000_000, 16, 64), (10_000_000, 32, 16), (10_000_000, 32, 32), (10_000_000, 32, 64), (5_000_000, 16, 9), (5_000_000, 16, 48)])
+        bench([(20_000_000, 16, 16), (20_000_000, 16, 32), (20_000_000, 16, 64), (10_000_000, 32, 16), (10_000_000, 32, 32), (10_000_000, 32, 64), (5_000_000, 16, 9), (5_000_000, 16, 48),
+               (5_000_000, 24, 12), (5_000_000, 24, 16), (5_000_000, 24, 32), (5_000_000, 24, 64), (10_000_000, 8, 16), (5_000_000, 12, 64), (5_000_000, 20, 24)])
