@@ -76,18 +76,19 @@ __global__ void __launch_bounds__(256) column_range_kernel(const double* __restr
 size_t wl_done_offset() { return offsetof(RangeRec, done); }
 size_t wl_tail_bytes() { return 2048; }
 
-// Shapes and passes this variant takes (given a valid record): plain Lloyd passes with sums, 8 < k <= 64, even d <= 32
+// Shapes and passes this variant takes (given a valid record): plain Lloyd passes with sums, 8 < k <= 64, even d <= 64
 bool lloyd_wl_shape(const LloydParams& p, int mode) {
   const int variant = lloyd_variant_override();
   if (g_wl_off || (variant != 0 && variant != 7)) return false;
   if (mode != 0 || p.w != nullptr || p.out_mode != 0 || p.mind2_out != nullptr || p.do_reduce != 1) return false;
-  if (p.k <= 8 || p.k > 64 || p.d > 32 || p.d < 2 || (p.d & 1)) return false;          // even d: rows stay 16-byte aligned (tensor map, fixed point in place)
+  if (p.k <= 8 || p.k > 64 || p.d > 64 || p.d < 2 || (p.d & 1)) return false;          // even d: rows stay 16-byte aligned (tensor map, fixed point in place)
   if (p.n >= (int64_t)1 << 31) return false;                                   // tensor-map row coordinates are 32-bit
   if (p.n / kTileRows / sm_count() > 60000) return false;                      // s32 limb columns: 65 000 tiles per group
   const int kp = ((p.k + 15) / 16) * 16;
   // measured against the warp-group variant on the same box (tools/wl_check.py bench): with k <= 16 and rows of 18..24 features
   // the padding to two slabs costs more than the cheaper reduction saves
   if (variant == 0 && kp == 16 && p.d > 16 && p.d <= 24) return false;
+  if (variant == 0 && kp == 16 && p.d > 32) return false;                     // one group of four warps: the fp64 tensor-pipe kernel is ahead there
   return wl_groups(16 * ((p.d + 15) / 16), kp) > 0;
 }
 
@@ -150,6 +151,8 @@ int launch_lloyd_wl(const LloydParams& p, void* tail, cudaStream_t st) {
   if (kp == 16 && ns == 1 && g_wl_groups == 5) return launch_wl<16, 1, 5>(p, tmap, rec, st);
   HKM_WL_CASE(16, 1) HKM_WL_CASE(32, 1) HKM_WL_CASE(48, 1) HKM_WL_CASE(64, 1)
   HKM_WL_CASE(16, 2) HKM_WL_CASE(32, 2) HKM_WL_CASE(48, 2) HKM_WL_CASE(64, 2)
+  HKM_WL_CASE(16, 3) HKM_WL_CASE(32, 3) HKM_WL_CASE(48, 3) HKM_WL_CASE(64, 3)
+  HKM_WL_CASE(16, 4) HKM_WL_CASE(32, 4) HKM_WL_CASE(48, 4) HKM_WL_CASE(64, 4)
 #undef HKM_WL_CASE
   set_error("lloyd_wl: no instantiation for d=%d k=%d", p.d, p.k);
   return HKM_ERR_UNSUPPORTED;

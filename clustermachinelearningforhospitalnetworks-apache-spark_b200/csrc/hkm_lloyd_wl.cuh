@@ -59,7 +59,7 @@ __host__ __device__ constexpr inline WlPlan wl_plan(int d, int kp, int groups, i
   L.lbo_h = (kp / 8) * 128 + 16;                   // one-hot operand: chunk of 16 rows, then cluster * 16, then row % 16
   L.h_bytes = (8 * L.lbo_h + 127) & ~127;
   L.tile_bytes = ns * kTileRows * 128;
-  L.acols = d + 8 <= 32 ? 32 : (d + 8 <= 64 ? 64 : 128);
+  L.acols = (d + 8 + 15) & ~15;
   L.tstride = kp <= 32 ? 32 : 64;
   L.gstride = L.acols + L.tstride;
   L.rcol0 = groups * L.gstride;
@@ -90,11 +90,12 @@ __host__ __device__ constexpr inline int wl_stages(int d, int kp, int g) {
   if (st > kWlMaxStages) st = kWlMaxStages;
   const int comb = (d / 16) * kp * 128 * 4;         // s32 accumulators parked in the idle ring for the final combine
   if (st < g + 2 || (st - g) * z.tile_bytes < 40 * 1024 || st * z.tile_bytes < comb) return 0;
+  if (g == 1 && d <= 32) return 0;                  // a single group only where nothing else fits
   return st;
 }
 // group count per shape (0: shape not taken)
 __host__ __device__ constexpr inline int wl_groups(int d, int kp) {
-  for (int g = 6; g >= 2; --g) if (wl_stages(d, kp, g) > 0) return g;
+  for (int g = 6; g >= 1; --g) if (wl_stages(d, kp, g) > 0) return g;
   return 0;
 }
 

@@ -94,6 +94,7 @@ if __name__ == "__main__":
         cases = [(5000, 16, 16, "blobs"), (128, 16, 16, "blobs"), (100, 16, 9, "blobs"), (1, 16, 12, "blobs"), (200000, 16, 16, "blobs"), (30011, 16, 33, "blobs"),
                  (40000, 16, 40, "blobs"), (45000, 16, 64, "blobs"), (50000, 32, 20, "blobs"), (60000, 32, 64, "blobs"), (129, 32, 17, "blobs"),
                  (30000, 24, 17, "blobs"), (30011, 24, 32, "blobs"), (9000, 12, 20, "blobs"), (33333, 2, 10, "blobs"), (70003, 8, 12, "blobs"), (3000, 30, 33, "blobs"), (4097, 22, 64, "blobs"),
+                 (20000, 64, 64, "blobs"), (20000, 64, 16, "blobs"), (6000, 48, 24, "blobs"), (5000, 40, 40, "blobs"), (4000, 62, 64, "blobs"), (65, 64, 64, "blobs"),
                  (70000, 16, 16, "offset"), (70000, 16, 24, "scales"), (50000, 16, 16, "outlier"), (3000000, 16, 16, "blobs")]
         bad = 0
         for n, d, k, kind in cases:
@@ -150,6 +151,9 @@ if __name__ == "__main__":
         for f in (0, 1):
             N.load().hkm_debug_wl_flags(ctypes.c_int(f)); print("flags", f, flush=True)
             bench([(20_000_000, 16, 16), (20_000_000, 16, 32), (10_000_000, 32, 16), (10_000_000, 32, 32), (5_000_000, 16, 12)])
+        sys.exit(0)
+    if cmd == "bench64":
+        bench([(20_000_000, 64, 64), (5_000_000, 64, 64), (5_000_000, 64, 16), (5_000_000, 64, 32), (5_000_000, 48, 24), (5_000_000, 48, 48), (5_000_000, 40, 40)])
         sys.exit(0)
     if cmd == "gbench":
         np, torch, N, O = _mods()
