@@ -117,18 +117,19 @@ static EncodeTiledFn encode_tiled() {
 
 template <int KP, int NS, int GO = 0>
 static int launch_wl(const LloydParams& p, const CUtensorMap& tmap, RangeRec* rec, cudaStream_t st) {
+  constexpr int H = GO > 0 ? 1 : wl_halves(16 * NS, KP);
   constexpr int G = GO > 0 ? GO : wl_groups(16 * NS, KP);
   if constexpr (G == 0) { set_error("lloyd_wl: d=%d k=%d does not fit", p.d, p.k); return HKM_ERR_UNSUPPORTED; }
   else {
-    constexpr WlPlan L = wl_plan(16 * NS, KP, G, wl_stages(16 * NS, KP, G));
-    auto kern = lloyd_wl_kernel<KP, NS, G>;
+    constexpr WlPlan L = wl_plan(16 * NS, KP, G, wl_stages(16 * NS, KP, G, H), H);
+    auto kern = lloyd_wl_kernel<KP, NS, G, H>;
     static bool attr_done[64];
     int dev = 0; HKM_CUDA_TRY(cudaGetDevice(&dev));
     if (dev >= 64 || !attr_done[dev]) {
-      HKM_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total + 1024));
+      HKM_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
       if (dev < 64) attr_done[dev] = true;
     }
-    kern<<<sm_count(), G * 128, L.total + 1024, st>>>(p, tmap, rec, g_wl_prof, g_wl_flags >= 0 ? g_wl_flags : (((NS == 2 && KP == 16) || (NS == 1 && KP == 32)) ? 1 : 0));
+    kern<<<sm_count(), G * 128 * H, L.total, st>>>(p, tmap, rec, g_wl_prof, g_wl_flags >= 0 ? g_wl_flags : (((NS == 2 && KP == 16) || (NS == 1 && KP == 32)) ? 1 : 0));
     HKM_CUDA_TRY(cudaGetLastError());
     return HKM_OK;
   }

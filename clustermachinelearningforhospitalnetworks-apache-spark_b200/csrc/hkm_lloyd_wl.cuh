@@ -45,12 +45,13 @@ struct RangeRec {
 
 struct WlPlan {
   int groups, stages, kchunks, lbo_b, lbo_h, h_bytes, tile_bytes, tcols, acols, tstride, gstride, rcol0;
-  int x_off, b_off, h_off, cn_off, mu_off, mg_off, cnt_off, red_off, bar_off, seq_off, tmem_off, cs_off, total;
+  int x_off, b_off, h_off, ex_off, cn_off, mu_off, mg_off, cnt_off, red_off, bar_off, seq_off, tmem_off, cs_off, total;
 };
 
 // Tensor memory, per group: [tf32 operand: d data columns + 8 constant columns][scores: k_pad], then behind all groups the s32 limb
 // sums [slab][k_pad], one set for the whole CTA (every warp adds its products into it).  Shared memory: ring stages (1024-byte aligned), the centres' tf32 operand, the one-hot operands.
-__host__ __device__ constexpr inline WlPlan wl_plan(int d, int kp, int groups, int stages) {
+// halves = warps per 32 rows (1, or 2: the features and the score columns of a row split over two threads)
+__host__ __device__ constexpr inline WlPlan wl_plan(int d, int kp, int groups, int stages, int halves = 1) {
   WlPlan L{};
   L.groups = groups; L.stages = stages;
   const int ns = d / 16;
@@ -69,35 +70,41 @@ __host__ __device__ constexpr inline WlPlan wl_plan(int d, int kp, int groups, i
   L.x_off = o; o += stages * L.tile_bytes;         // 1024-byte aligned (swizzle atoms)
   L.b_off = o; o += (L.kchunks * L.lbo_b + 127) & ~127;
   L.h_off = o; o += groups * L.h_bytes;
+  L.ex_off = o; o += halves > 1 ? groups * kTileRows * 2 * 16 : 0;     // exchange slots of the two threads of a row
   L.cn_off = o; o += kp * 8;
   L.mu_off = o; o += (d + 8) * 8;
   L.mg_off = o; o += d * 8;                        // M_f per feature
   L.cnt_off = o; o += kp * 4;
-  L.red_off = o; o += (2 * kWlMaxWarps + 64) * 8;
-  L.bar_off = o; o += (4 * kWlMaxStages + kWlMaxGroups + kWlMaxWarps) * 8;     // full[stage][quarter], scores[group], sums[warp]
-  L.seq_off = o; o += 4 * kWlMaxStages * 4;
+  L.red_off = o; o += (2 * 4 * groups * halves + 64) * 8;
+  const int nst = stages > 0 ? stages : 1;
+  L.bar_off = o; o += (4 * halves * nst + kWlMaxGroups + kWlMaxWarps) * 8;     // full[stage][quarter][half], scores[group], sums[group][quarter]
+  L.seq_off = o; o += 4 * halves * nst * 4; o = (o + 15) & ~15;
   L.tmem_off = o; o += 16;
   if (kp * d * 8 <= 8 * 1024) { L.cs_off = o; o += kp * d * 8; }
   L.total = o;
   return L;
 }
 
-__host__ __device__ constexpr inline int wl_stages(int d, int kp, int g) {
-  if (g < 1 || g > kWlMaxGroups) return 0;
-  const WlPlan z = wl_plan(d, kp, g, 0);
+__host__ __device__ constexpr inline int wl_stages(int d, int kp, int g, int halves = 1) {
+  if (g < 1 || g * halves > kWlMaxGroups) return 0;
+  const WlPlan z = wl_plan(d, kp, g, 0, halves);
   if (z.tcols > 512) return 0;
-  int st = (227 * 1024 - 4096 - z.total) / z.tile_bytes;     // 1 KB alignment slack, static shared memory of the tail
-  if (st > kWlMaxStages) st = kWlMaxStages;
+  const int budget = 227 * 1024 - 1024;             // the static words are padded to 1 KB (alignment of the dynamic part)
+  int st = kWlMaxStages;
+  while (st > 0 && wl_plan(d, kp, g, st, halves).total > budget) --st;
   const int comb = (d / 16) * kp * 128 * 4;         // s32 accumulators parked in the idle ring for the final combine
   if (st < g + 2 || (st - g) * z.tile_bytes < 40 * 1024 || st * z.tile_bytes < comb) return 0;
-  if (g == 1 && d <= 32) return 0;                  // a single group only where nothing else fits
+  if (g == 1 && halves == 1 && d <= 32) return 0;   // a single group only where nothing else fits
   return st;
 }
-// group count per shape (0: shape not taken)
-__host__ __device__ constexpr inline int wl_groups(int d, int kp) {
-  for (int g = 6; g >= 1; --g) if (wl_stages(d, kp, g) > 0) return g;
+// group count per shape (0: shape not taken), and threads per row: where only one group of four warps fits (64 KB tiles), the
+// same tile is worked by eight warps instead, two threads per row
+__host__ __device__ constexpr inline int wl_groups1(int d, int kp) {
+  for (int g = 6; g >= 1; --g) if (wl_stages(d, kp, g, 1) > 0) return g;
   return 0;
 }
+__host__ __device__ constexpr inline int wl_halves(int d, int kp) { return (wl_groups1(d, kp) == 1 && wl_stages(d, kp, 1, 2) > 0) ? 2 : 1; }
+__host__ __device__ constexpr inline int wl_groups(int d, int kp) { return wl_halves(d, kp) == 2 ? 1 : wl_groups1(d, kp); }
 
 __device__ __forceinline__ void sts_u8(uint32_t a, uint32_t v) { asm volatile("st.shared.u8 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
 __device__ __forceinline__ uint64_t wl_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout_type) {
@@ -122,18 +129,20 @@ __device__ __forceinline__ void wl_tmem_wait_st() { asm volatile("tcgen05.wait::
 // Thread = row throughout: a thread reads its row through the swizzle (eight consecutive rows hit eight different 16-byte columns),
 // writes the tf32 values into its lane of the group's tensor-memory operand (the tensor core takes A from TMEM: no shared-memory
 // copy of the operand at all), keeps |x - mu|^2 in a register, and overwrites the row in place with its fixed-point form.
-template <int KP, int NS, int GFIX>
-__global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydParams p, const __grid_constant__ CUtensorMap tmap, RangeRec* rec,
+template <int KP, int NS, int GFIX, int H = 1>
+__global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const LloydParams p, const __grid_constant__ CUtensorMap tmap, RangeRec* rec,
                                                                  unsigned long long* prof_buf, int flags) {
   if (p.skip != nullptr && *p.skip != 0) return;
-  constexpr int DP = 16 * NS, ND = 2 * NS, G = GFIX, S = wl_stages(DP, KP, GFIX);   // DP: features padded to whole slabs
-  constexpr WlPlan L = wl_plan(DP, KP, GFIX, S);
+  constexpr int DP = 16 * NS, ND = 2 * NS, G = GFIX, S = wl_stages(DP, KP, GFIX, H);   // DP: features padded to whole slabs
+  constexpr WlPlan L = wl_plan(DP, KP, GFIX, S, H);
+  static_assert(H == 1 || H == 2, "one or two threads per row");
   const int d = p.d;                                  // even, DP - 16 < d <= DP; the padding columns arrive as zeros (tensor-map bounds)
   static_assert(S >= GFIX + 2, "shape does not fit");
   constexpr int NW = (KP + 31) / 32;
   constexpr int IDXBITS = 6;
   constexpr uint32_t IDXMASK = (1u << IDXBITS) - 1u;
-  constexpr int nthreads = G * 128, nwarps = G * 4;
+  constexpr int nthreads = G * 128 * H, nwarps = G * 4 * H;
+  constexpr int NCH = KP / 16;                          // score columns in chunks of 16
   constexpr uint32_t LBO_B = L.lbo_b, LBO_H = L.lbo_h, tile_bytes = L.tile_bytes;
   constexpr uint32_t SLAB = kTileRows * 128;          // bytes of one 16-feature slab of a tile
   // the record must describe this table and admit it; otherwise the launch behind this one does the pass
@@ -143,13 +152,14 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
   }
 
   extern __shared__ __align__(1024) unsigned char smem_raw[];
-  // the swizzle is a function of the shared address: stages must start on 1024-byte boundaries whatever precedes the dynamic part
-  unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  // the swizzle is a function of the shared address: stages must start on 1024-byte boundaries (the declared alignment gives that)
+  unsigned char* smem = smem_raw;
+  if ((smem_u32(smem_raw) & 1023u) != 0u) __trap();
   const int k = p.k;
   const uint32_t sb = smem_u32(smem);
   const uint32_t a_x = sb + L.x_off, a_B = sb + L.b_off, a_cnt = sb + L.cnt_off;
   const uint32_t a_bar = sb + L.bar_off, a_seq = sb + L.seq_off;
-  const uint32_t b_full = a_bar, b_tfull = a_bar + 8u * 4u * kWlMaxStages, b_rfull = b_tfull + 8u * kWlMaxGroups;
+  const uint32_t b_full = a_bar, b_tfull = a_bar + 8u * 4u * H * S, b_rfull = b_tfull + 8u * kWlMaxGroups;
   double* cn_s = reinterpret_cast<double*>(smem + L.cn_off);
   double* mu_s = reinterpret_cast<double*>(smem + L.mu_off);
   double* mg_s = reinterpret_cast<double*>(smem + L.mg_off);
@@ -157,7 +167,10 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
   unsigned int* cnt_s = reinterpret_cast<unsigned int*>(smem + L.cnt_off);
 
   const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
-  const int grp = warp >> 2, q = warp & 3;
+  const int grp = warp / (4 * H), q = warp & 3, hh = H == 1 ? 0 : (warp >> 2) & 1;   // group, lane quarter of the tile, half of the row
+  // this thread's share of its row: slabs [sl_lo, sl_hi) and score chunks [ch_lo, ch_hi)
+  const int sl_lo = hh ? (NS + 1) / 2 : 0, sl_hi = (H == 1 || hh) ? NS : (NS + 1) / 2;
+  const int ch_lo = hh ? (NCH + 1) / 2 : 0, ch_hi = (H == 1 || hh) ? NCH : (NCH + 1) / 2;
   const int64_t full_tiles = p.n / kTileRows;
   const int tail_rows = (int)(p.n - full_tiles * kTileRows);
   const int my_tiles = full_tiles > (int64_t)blockIdx.x ? (int)((full_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
@@ -169,8 +182,8 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
   // ------------------------------------------------------------------ one-time set-up
   if (tid == 0) {
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L.bar_off);
-    for (int s = 0; s < 4 * S; ++s) mbar_init(bars + s, 1);
-    for (int g = 0; g < kWlMaxGroups + kWlMaxWarps; ++g) mbar_init(bars + 4 * kWlMaxStages + g, 1);
+    for (int s = 0; s < 4 * H * S; ++s) mbar_init(bars + s, 1);
+    for (int g = 0; g < kWlMaxGroups + kWlMaxWarps; ++g) mbar_init(bars + 4 * H * S + g, 1);
     mbar_fence_init();
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap) : "memory");
   }
@@ -181,7 +194,7 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
   // zero: B and the one-hot operands (one contiguous range), counters
   for (int i = tid; i < (L.cn_off - L.b_off) / 16; i += nthreads) reinterpret_cast<uint4*>(smem + L.b_off)[i] = make_uint4(0, 0, 0, 0);
   for (int i = tid; i < KP; i += nthreads) cnt_s[i] = 0u;
-  for (int i = tid; i < 4 * S; i += nthreads) reinterpret_cast<uint32_t*>(smem + L.seq_off)[i] = (uint32_t)(i >> 2);
+  for (int i = tid; i < 4 * H * S; i += nthreads) reinterpret_cast<uint32_t*>(smem + L.seq_off)[i] = (uint32_t)(i / (4 * H));
   if (L.cs_off != 0) for (int i = tid; i < k * d; i += nthreads) reinterpret_cast<double*>(smem + L.cs_off)[i] = p.C[i];
   if (tid < DP + 8) { double s = 0; if (tid < d) for (int j = 0; j < k; ++j) s += p.C[(size_t)j * d + tid]; mu_s[tid] = tid < d ? s / k : 0.0; }
   if (tid < DP) {
@@ -190,7 +203,7 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
     mg_s[tid] = __longlong_as_double(((long long)(eb + 2u) << 52) | (1ll << 51));
   }
   __syncthreads();
-  double* h_s = red_s + 2 * kWlMaxWarps;
+  double* h_s = red_s + 2 * nwarps;
   if (tid < KP) {
     double s = 0, sc = 0;
     if (tid < k) for (int f = 0; f < d; ++f) { const double c = p.C[(size_t)tid * d + f], cc = c - mu_s[f]; s = fma(c, c, s); sc = fma(cc, cc, sc); }
@@ -237,7 +250,7 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
     // the limb sums start at zero (every product below accumulates; the four warps of a group issue theirs independently)
     const uint32_t zv[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
 #pragma unroll 1
-    if (grp == 0) for (int c0 = 0; c0 < NS * KP; c0 += 8) wl_tmem_st8(tmem + tlane + (uint32_t)L.rcol0 + (uint32_t)c0, zv);
+    if (grp == 0 && hh == 0) for (int c0 = 0; c0 < NS * KP; c0 += 8) wl_tmem_st8(tmem + tlane + (uint32_t)L.rcol0 + (uint32_t)c0, zv);
     wl_tmem_wait_st();
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   }
@@ -269,10 +282,11 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
           "{\n.reg .pred pe;\nelect.sync _|pe, 0xffffffff;\n"
           "@pe st.shared.u32 [%0], %1;\n"
           "@pe mbarrier.arrive.expect_tx.shared::cta.b64 _, [%2], %3;\n}\n"
-          ::"r"(seqa), "r"((uint32_t)i), "r"(bar), "r"((uint32_t)NS * 4096u)
+          ::"r"(seqa), "r"((uint32_t)i), "r"(bar), "r"((uint32_t)(sl_hi - sl_lo) * 4096u)
           : "memory");
 #pragma unroll
       for (int sl = 0; sl < NS; ++sl)
+        if (sl >= sl_lo && sl < sl_hi)
         asm volatile(
             "{\n.reg .pred pe;\nelect.sync _|pe, 0xffffffff;\n"
             "@pe cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];\n}\n"
@@ -281,7 +295,7 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
     }
   };
   for (int i = grp; i < S && i < T; i += G)
-    tma_load(i, a_x + (uint32_t)i * tile_bytes + (uint32_t)q * 4096u, b_full + 8u * (uint32_t)(4 * i + q), a_seq + 4u * (uint32_t)(4 * i + q));
+    tma_load(i, a_x + (uint32_t)i * tile_bytes + (uint32_t)q * 4096u, b_full + 8u * (uint32_t)((4 * i + q) * H + hh), a_seq + 4u * (uint32_t)((4 * i + q) * H + hh));
 
   const int row = 32 * q + lane;                                                  // tile row of this thread = TMEM lane
   const uint32_t xrow = (uint32_t)lane * 128u, xsw = (uint32_t)(lane & 7) << 4;   // row offset inside the quarter, swizzle term
@@ -294,7 +308,9 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
   constexpr int RLANES = tp_dclass(ND) / 2 > 32 ? 32 : tp_dclass(ND) / 2;
   const double* Cr = L.cs_off != 0 ? reinterpret_cast<const double*>(smem + L.cs_off) : p.C;
   const uint32_t a_H = sb + L.h_off + (uint32_t)grp * (uint32_t)L.h_bytes;
-  const uint32_t bar_t = b_tfull + 8u * (uint32_t)grp, bar_r = b_rfull + 8u * (uint32_t)warp;
+  const uint32_t bar_t = b_tfull + 8u * (uint32_t)grp, bar_r = b_rfull + 8u * (uint32_t)(4 * grp + q);
+  const uint32_t a_ex = sb + L.ex_off + (uint32_t)grp * (kTileRows * 32u) + (uint32_t)row * 32u;   // this row's two exchange slots
+  const int pair_id = 1 + G + 4 * grp + q;                          // named barrier of the two warps that share 32 rows
   const uint32_t hrow = a_H + (uint32_t)(row >> 4) * LBO_H + (uint32_t)(row & 15);       // + 16 * label: this row's one-hot byte
   const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(KP >> 3) << 17) | ((uint32_t)(kTileRows >> 4) << 24);
   const uint32_t idesc2 = (2u << 4) | (1u << 15) | ((uint32_t)(KP >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);   // u8 x u8 -> s32, A MN-major
@@ -333,7 +349,7 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
   for (int i = grp; i < T; i += G) {
     const int rows_valid = i < my_tiles ? kTileRows : tail_rows;
     const uint32_t xs = a_x + (uint32_t)s * tile_bytes + (uint32_t)q * 4096u;       // this warp's 32 rows of slab 0
-    const uint32_t bar_f = b_full + 8u * (uint32_t)(4 * s + q), seqa = a_seq + 4u * (uint32_t)(4 * s + q);
+    const uint32_t bar_f = b_full + 8u * (uint32_t)((4 * s + q) * H + hh), seqa = a_seq + 4u * (uint32_t)((4 * s + q) * H + hh);
     if (pend && early && mbar_probe_a(bar_r, tph ^ 1u)) {
       // the previous tile's limb product is already complete: close it now, so its quarter of the ring refills at once
       // (otherwise after the next product has been issued, which hides the wait)
@@ -356,6 +372,7 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
     float xa = 0.f, xb = 0.f;
 #pragma unroll
     for (int sl = 0; sl < NS; ++sl) {
+      if (H == 2 && (sl < sl_lo || sl >= sl_hi)) continue;       // the other thread of the row converts these
       const uint32_t xr = xs + (uint32_t)sl * SLAB + xrow;
       double v[16];
 #pragma unroll
@@ -379,12 +396,12 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
         sts_v2f64(xr + (((uint32_t)c << 4) ^ xsw), v[2 * c] + m0, v[2 * c + 1] + m1);
       }
     }
-    const float xn2 = xa + xb;
+    float xn2 = xa + xb;
     wl_tmem_wait_st();
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");       // fixed-point rows -> visible to the tensor core (second product)
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    named_bar_sync(1 + grp, 128);
-    if (q == 0 && lane == 0) {
+    named_bar_sync(1 + grp, 128 * H);
+    if (q == 0 && hh == 0 && lane == 0) {
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
       for (int ks = 0; ks < ND + 1; ++ks) {                          // K = 8: eight operand columns, two 16-byte chunks of B
@@ -411,7 +428,8 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
     // ---- sweep 1: top two of the packed scores (tournament per 16 columns)
     float m1 = 0.f, m2 = 0.f;
 #pragma unroll
-    for (int ch = 0; ch < KP / 16; ++ch) {
+    for (int ch = 0; ch < NCH; ++ch) {
+      if (H == 2 && (ch < ch_lo || ch >= ch_hi)) continue;       // the other thread of the row sweeps these columns
       uint32_t v[16];
       tp_tmem_ld16(t_D + (uint32_t)(ch * 16), v);
       tp_tmem_wait_ld();
@@ -431,12 +449,23 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
           asm("max.f32 %0, %1, %2, %3;" : "=f"(lo[c]) : "f"(t), "f"(lo[c]), "f"(lo[c + w2]));
           hi[c] = fmaxf(hi[c], hi[c + w2]);
         }
-      if (ch == 0) { m1 = hi[0]; m2 = lo[0]; }
+      if (ch == ch_lo) { m1 = hi[0]; m2 = lo[0]; }
       else {
         const float t = fminf(m1, hi[0]);
         asm("max.f32 %0, %1, %2, %3;" : "=f"(m2) : "f"(t), "f"(m2), "f"(lo[0]));
         m1 = fmaxf(m1, hi[0]);
       }
+    }
+    if constexpr (H == 2) {
+      // the two threads of the row swap their top two and their share of |x - mu|^2, and both form the same decision
+      asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(a_ex + 16u * (uint32_t)hh), "f"(m1), "f"(m2), "f"(xn2), "f"(0.f) : "memory");
+      named_bar_sync(pair_id, 64);
+      float o1, o2, o3, o4;
+      asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(o1), "=f"(o2), "=f"(o3), "=f"(o4) : "r"(a_ex + 16u * (uint32_t)(hh ^ 1)) : "memory");
+      const float t = fminf(m1, o1);
+      asm("max.f32 %0, %1, %2, %3;" : "=f"(m2) : "f"(t), "f"(m2), "f"(o2));
+      m1 = fmaxf(m1, o1);
+      xn2 += o3;
     }
     const bool valid = row < rows_valid;
     const float eps = fmaf(kapv, sqrtf(xn2) * 1.001f, etab) + 6e-5f * fabsf(m1);
@@ -448,11 +477,13 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
       // sweep 2 + exact re-scoring of the undecided rows (hkm_lloyd_wg.cuh).  The stage holds the fixed-point form by now, so the
       // row's fp64 values come from global memory again (the table was just streamed: an L2 hit more often than not)
       const long long tr0 = prof ? clock64() : 0;
+      if constexpr (H == 2) named_bar_sync(pair_id, 64);         // the other thread has read this row's sweep slot: the slots are reused below
       uint32_t w[NW];
 #pragma unroll
       for (int qq = 0; qq < NW; ++qq) w[qq] = 0u;
 #pragma unroll
-      for (int ch = 0; ch < KP / 16; ++ch) {
+      for (int ch = 0; ch < NCH; ++ch) {
+        if (H == 2 && (ch < ch_lo || ch >= ch_hi)) continue;
         uint32_t v[16];
         tp_tmem_ld16(t_D + (uint32_t)(ch * 16), v);
         tp_tmem_wait_ld();
@@ -492,14 +523,28 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
           }
         }
         bj = __shfl_sync(0xffffffffu, bj, 0);
-        if (lane == src) lab = bj;
+        if constexpr (H == 1) { if (lane == src) lab = bj; }
+        else if (lane == 0) {
+          // best of this thread's columns; the row's two halves meet below
+          asm volatile("st.shared.v2.u32 [%0], {%1,%2};" ::"r"(a_ex + (uint32_t)(src - lane) * 32u + 16u * (uint32_t)hh),
+                       "r"((uint32_t)__double2loint(best)), "r"((uint32_t)__double2hiint(best)) : "memory");
+          sts_u32(a_ex + (uint32_t)(src - lane) * 32u + 16u * (uint32_t)hh + 8u, (uint32_t)bj);
+        }
         ++pcnt;
+      }
+      if constexpr (H == 2) {
+        named_bar_sync(pair_id, 64);
+        if (amb) {
+          double b0 = lds_f64(a_ex), b1 = lds_f64(a_ex + 16u);
+          const int j0 = (int)lds_u32(a_ex + 8u), j1 = (int)lds_u32(a_ex + 24u);
+          lab = (j1 >= 0 && (j0 < 0 || b1 > b0)) ? j1 : j0;    // equal scores: the lower index (first half) wins
+        }
       }
       if (prof) pw2 += clock64() - tr0;
     }
     // ---- this row's one-hot byte, label, count (rows past the end take no part)
     const uint32_t hb = hrow + 16u * (uint32_t)lab;
-    if (valid) {
+    if (valid && hh == 0) {
       sts_u8(hb, 1u);
       asm volatile("red.shared.add.u32 [%0], 1;" ::"r"(a_cnt + 4u * (uint32_t)lab) : "memory");
       if (p.labels_out != nullptr) {
@@ -513,7 +558,7 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncwarp();
-    if (lane == 0) {
+    if (lane == 0 && hh == 0) {
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
       const uint64_t dh = dh0 + (uint64_t)((uint32_t)q * dh_step);
 #pragma unroll
@@ -526,7 +571,7 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
       asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar_r) : "memory");
     }
     __syncwarp();
-    hb_prev = valid ? hb : 0u; xs_prev = xs; bar_f_prev = bar_f; seqa_prev = seqa; pend = true;
+    hb_prev = (valid && hh == 0) ? hb : 0u; xs_prev = xs; bar_f_prev = bar_f; seqa_prev = seqa; pend = true;
     s += G; if (s >= S) { s -= S; ph ^= 1u; }
     tph ^= 1u;
   }
@@ -544,7 +589,7 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
   __syncthreads();
   asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
   int32_t* acc_s = reinterpret_cast<int32_t*>(smem + L.x_off);
-  if (grp == 0) {
+  if (grp == 0 && hh == 0) {
 #pragma unroll 1
     for (int sl = 0; sl < NS; ++sl)
 #pragma unroll 1
@@ -612,7 +657,7 @@ __global__ void __launch_bounds__(GFIX * 128, 1) lloyd_wl_kernel(const LloydPara
     if (p.C_update != nullptr && peer_ok) {
       __threadfence_block();
       __syncthreads();
-      update_centers_body(p.partial_out, k, d, p.C_update, p.tol2, p.state_rw, red_s + 2 * kWlMaxWarps, tid);
+      update_centers_body(p.partial_out, k, d, p.C_update, p.tol2, p.state_rw, red_s + 2 * nwarps, tid);
     }
   }
 }

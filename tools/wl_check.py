@@ -125,7 +125,7 @@ if __name__ == "__main__":
         sys.exit(0)
     if cmd == "prof":
         np, torch, N, O = _mods()
-        for n, d, k in [(20_000_000, 16, 16), (10_000_000, 32, 16), (20_000_000, 16, 32)]:
+        for n, d, k in ([(20_000_000, 64, 64)] if "64" in sys.argv else [(20_000_000, 16, 16), (10_000_000, 32, 16), (20_000_000, 16, 32)]):
             g = torch.Generator(device="cuda"); g.manual_seed(1)
             prof = torch.randn(k, d, dtype=torch.float64, device="cuda", generator=g) * 2
             X = prof[torch.randint(0, k, (n,), device="cuda", generator=g)] + torch.randn(n, d, dtype=torch.float64, device="cuda", generator=g)
