@@ -143,6 +143,7 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
   constexpr uint32_t IDXMASK = (1u << IDXBITS) - 1u;
   constexpr int nthreads = G * 128 * H, nwarps = G * 4 * H;
   constexpr int NCH = KP / 16;                          // score columns in chunks of 16
+  constexpr bool HOIST = nwarps <= 8;
   constexpr uint32_t LBO_B = L.lbo_b, LBO_H = L.lbo_h, tile_bytes = L.tile_bytes;
   constexpr uint32_t SLAB = kTileRows * 128;          // bytes of one 16-feature slab of a tile
   // the record must describe this table and admit it; otherwise the launch behind this one does the pass
@@ -377,11 +378,22 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
       double v[16];
 #pragma unroll
       for (int c = 0; c < 8; ++c) lds_v2f64(xr + (((uint32_t)c << 4) ^ xsw), v[2 * c], v[2 * c + 1]);
+      // with registers to spare (at most 16 warps) the per-feature constants of the slab are fetched up front, so the arithmetic
+      // below does not wait for one broadcast load after the other
+      uint64_t mu8[HOIST ? 8 : 1];
+      double mg8[HOIST ? 16 : 1];
+      if constexpr (HOIST) {
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          if (NS > 1) asm volatile("ld.shared.b64 %0, [%1];" : "=l"(mu8[c]) : "r"(a_mu2 + (uint32_t)(8 * sl + c) * 8u)); else mu8[c] = mu_r[c];
+          lds_v2f64(a_mg + (uint32_t)(16 * sl + 2 * c) * 8u, mg8[2 * c], mg8[2 * c + 1]);
+        }
+      }
       uint32_t tv[16];
 #pragma unroll
       for (int c = 0; c < 8; ++c) {
-        uint64_t mu01 = mu_r[NS == 1 ? c : 0], vv, rr;
-        if (NS > 1) asm volatile("ld.shared.b64 %0, [%1];" : "=l"(mu01) : "r"(a_mu2 + (uint32_t)(8 * sl + c) * 8u));
+        uint64_t mu01 = HOIST ? mu8[HOIST ? c : 0] : mu_r[NS == 1 ? c : 0], vv, rr;
+        if (!HOIST && NS > 1) asm volatile("ld.shared.b64 %0, [%1];" : "=l"(mu01) : "r"(a_mu2 + (uint32_t)(8 * sl + c) * 8u));
         asm("mov.b64 %0, {%1,%2};" : "=l"(vv) : "f"((float)v[2 * c]), "f"((float)v[2 * c + 1]));
         asm("sub.f32x2 %0, %1, %2;" : "=l"(rr) : "l"(vv), "l"(mu01));
         tv[2 * c] = (uint32_t)rr + 0x1000u; tv[2 * c + 1] = (uint32_t)(rr >> 32) + 0x1000u;
@@ -392,7 +404,8 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
 #pragma unroll
       for (int c = 0; c < 8; ++c) {
         double m0, m1;
-        lds_v2f64(a_mg + (uint32_t)(16 * sl + 2 * c) * 8u, m0, m1);
+        if constexpr (HOIST) { m0 = mg8[HOIST ? 2 * c : 0]; m1 = mg8[HOIST ? 2 * c + 1 : 0]; }
+        else lds_v2f64(a_mg + (uint32_t)(16 * sl + 2 * c) * 8u, m0, m1);
         sts_v2f64(xr + (((uint32_t)c << 4) ^ xsw), v[2 * c] + m0, v[2 * c + 1] + m1);
       }
     }
