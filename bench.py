@@ -268,9 +268,18 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    def limb_shape(d_, k_):
+        """REUSE passes of this shape run the limb-reduction variant (the dispatch rule of hkm_lloyd_wl.cu)."""
+        kp = ((k_ + 15) // 16) * 16
+        return 8 < k_ <= 64 and d_ % 2 == 0 and d_ <= 64 and not (kp == 16 and (16 < d_ <= 24 or d_ > 32))
+
     def kernel_name(d_, k_):
-        if k_ <= 8 or (k_ <= 16 and (d_ <= 8 or d_ > 32)):
+        if limb_shape(d_, k_):
+            return "lloyd_wl_kernel (hkm_lloyd_wl.cuh)"
+        if k_ <= 8 or (k_ <= 16 and d_ > 32):
             return "lloyd_mma_kernel (hkm_lloyd_mma.cuh)"
+        if k_ <= 16 and 8 < d_ <= 24:
+            return "lloyd_wg_kernel (hkm_lloyd_wg.cuh)"
         return "lloyd_tp_kernel (hkm_lloyd_tp.cuh)"
 
     def timed_loop(X, C0, steps, warmup, sample_clocks):
@@ -479,7 +488,9 @@ def main():
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})", "kernel": kernel_name(d, k),
                      "kernel_ms": kernel_ms, "algorithmic_bytes_per_launch": alg_bytes, "traffic": ncu_traffic(args.workload)},
-        "gpu_launches": (1 if (world == 1 or xchg is not None) else 2) * args.steps,
+        # per step: the fused Lloyd kernel (+ the update kernel on the NCCL path); shapes on the limb-reduction variant launch the
+        # variant behind it as well, which returns at once when the limb pass has run
+        "gpu_launches": ((1 if (world == 1 or xchg is not None) else 2) + (1 if limb_shape(d, k) else 0)) * args.steps,
         "clocks": clocks,
     }
     if e2e:
