@@ -73,11 +73,15 @@ HKM_API int hkm_needs_workspace(int d, int k);
 
 /* Tuning / test hook, process wide: pins the kernel family the Lloyd data passes use wherever that family is built for the
  * shape.  0 = pick per shape (default), 1 = gather, 2 = fp64 tensor pipe, 3 = warp-specialised fp64, 4 = pipelined tcgen05
- * screening, 5 = the selection without the pipelined tcgen05 variant.  Every family gives the same labels, sums and cost
- * (tests/test_gpu_lloyd.py compares them), so this never changes results.  No counterpart in Spark. */
+ * screening, 5 = the selection without the tcgen05 variants of round 2, 6 = warp-group tcgen05 screening, 7 = as 0.  Every family
+ * gives the same labels and counts, and sums / cost equal to fp64 rounding (tests/test_gpu_lloyd.py, tests/test_gpu_limb.py compare
+ * them), so this never changes results beyond the last bits.  No counterpart in Spark. */
 HKM_API int hkm_set_lloyd_variant(int variant);
 
-/* Bytes of scratch hkm_assign_reduce needs for (d, k) on the current device. */
+/* Bytes of scratch hkm_assign_reduce needs for (d, k) on the current device: the per-CTA partials, 256 + CTAs * (k*d + 2k + 2) * 8,
+ * and behind them a 2 KB record of the table's column ranges.  The record is written by a HKM_XNORM_STORE pass and lets the
+ * HKM_XNORM_REUSE passes of a fit on the same scratch form the per-cluster sums on the integer tensor cores (8 < k <= 64, even
+ * d <= 64).  A scratch of only the per-CTA size is accepted too; those passes then run the other kernels. */
 HKM_API size_t hkm_assign_reduce_scratch_bytes(int d, int k);
 
 /*
@@ -92,8 +96,9 @@ HKM_API size_t hkm_assign_reduce_scratch_bytes(int d, int k);
  *               correct; required for mind2_out).  HKM_XNORM_STORE (1): same, and the pass
  *               also stores sum_i w_i |x_i|^2 to *xnorm2_sum.  HKM_XNORM_REUSE (2): the pass
  *               skips the per-row norms and forms cost = *xnorm2_sum - 2 sum_i w_i score_i
- *               (X and weights must be those of the STORE pass).  The sum is exact to fp64
- *               rounding of ~1e-16 * sum|x|^2, so REUSE is meant for cost / sum|x|^2 > 1e-9.
+ *               (X and weights must be those of the STORE pass; pass the same scratch as well, see
+ *               hkm_assign_reduce_scratch_bytes).  The sum is exact to fp64 rounding of ~1e-16 * sum|x|^2,
+ *               so REUSE is meant for cost / sum|x|^2 > 1e-9.
  *   state       NULL, or a device hkm_lloyd_state: when state->converged != 0 the pass is a
  *               no-op (lets a host enqueue maxIter passes without reading back in between).
  *   do_reduce   0 = only labels/mind2 are produced (partial_out may be NULL).
@@ -146,7 +151,8 @@ HKM_API int hkm_lloyd_step_peer(const double* X, int64_t n, int d, double* C_ino
  * HKM_NOALLOC_SCRATCH_BYTES array that lives inside libhkm.so on every GPU that loads it, until
  * the process exits.  Arguments and results are those of hkm_assign_reduce, minus scratch.
  *
- *  - Limit: hkm_assign_reduce_scratch_bytes(d, k) = 256 + CTAs * (k*d + 2k + 2) * 8 must fit in
+ *  - Limit: the per-CTA partials, 256 + CTAs * (k*d + 2k + 2) * 8 (hkm_assign_reduce_scratch_bytes(d, k) without the
+ *    column range record, which this entry point does not use), must fit in
  *    HKM_NOALLOC_SCRATCH_BYTES (4 MiB).  On a 148-SM B200 the pass launches 296 CTAs, so k*d + 2k + 2 <= 1771
  *    (e.g. k = 32, d = 32 is the largest square shape), and 444 CTAs for thin rows (d <= 8 and k <= 8), so
  *    k*d + 2k + 2 <= 1180 there (always met).  Larger shapes -- and every shape hkm_needs_workspace() reports --
