@@ -90,3 +90,43 @@ def test_short_fit_property(hkm, oracle, prob):
     if (lab_g == lab_o).all():
         assert np.allclose(G, Co, rtol=1e-6, atol=1e-9 * max(1.0, np.abs(Co).max()))
         assert model.summary.trainingCost == pytest.approx(cost, rel=1e-6, abs=1e-9 * scale)
+
+
+@st.composite
+def limb_problems(draw):
+    """Shapes the limb-reduction variant takes (even d <= 64, 8 < k <= 64), same pathologies."""
+    d = 2 * draw(st.one_of(st.integers(1, 32), st.sampled_from([1, 4, 8, 12, 15, 16, 17, 24, 31, 32])))
+    k = draw(st.one_of(st.integers(9, 64), st.sampled_from([9, 16, 17, 32, 33, 48, 49, 64])))
+    n = draw(st.one_of(st.integers(1, 2000), st.integers(1, 100_000), st.sampled_from([1, 127, 128, 129, 4096])))
+    seed = draw(st.integers(0, 2**31 - 1))
+    flags = draw(st.fixed_dictionaries({"dups": st.booleans(), "const_col": st.booleans(), "far_centre": st.booleans(), "dup_centre": st.booleans(),
+                                        "integers": st.booleans(), "offset": st.sampled_from([0.0, 0.0, 5.0, 300.0])}))
+    return n, d, k, seed, flags
+
+
+@settings(max_examples=60, deadline=None, derandomize=True, suppress_health_check=[HealthCheck.too_slow, HealthCheck.data_too_large, HealthCheck.function_scoped_fixture])
+@given(limb_problems())
+def test_reuse_pass_property(hkm, oracle, prob):
+    """STORE pass, then a REUSE pass on the same scratch (the limb-reduction variant wherever the column ranges admit the table)."""
+    n, d, k, seed, flags = prob
+    X, C = build(n, d, k, seed, flags)
+    N = hkm._native
+    Xd = torch.from_numpy(X).cuda(); Cd = torch.from_numpy(C).cuda()
+    partial = torch.empty(k * d + k + 1, dtype=torch.float64, device="cuda")
+    labels = torch.empty(n, dtype=torch.int32, device="cuda")
+    scratch = N.new_scratch(d, k, "cuda"); xs = torch.zeros(1, dtype=torch.float64, device="cuda")
+    N.assign_reduce(Xd, Cd, partial, scratch=scratch, xnorm2_sum=xs, xnorm2_mode=1)
+    N.assign_reduce(Xd, Cd, partial, labels, scratch=scratch, xnorm2_sum=xs, xnorm2_mode=2)
+    p = partial.cpu().numpy(); lab = labels.cpu().numpy()
+    sums, wsum, cost, olab = oracle.lloyd_pass(X, C, P=1, want_labels=True)
+    agree = (lab == olab).mean()
+    assert agree >= 0.9999 or (lab != olab).sum() <= 1, (prob, agree)
+    assert p[k * d:k * d + k].sum() == n
+    if (lab == olab).all():
+        assert np.array_equal(p[k * d:k * d + k], wsum)
+        assert np.abs(p[:k * d].reshape(k, d) - sums).max() <= 1e-6 * max(1.0, np.abs(sums).max())
+        if flags["dup_centre"] and k > 2:
+            assert wsum[k - 2] == 0
+    scale = float((X * X).sum()) + 1.0
+    # REUSE forms the cost as sum|x|^2 - 2 sum score: absolute accuracy ~1e-16 sum|x|^2 (include/hkm.h)
+    assert p[-1] == pytest.approx(cost, rel=1e-6, abs=1e-9 * scale)
