@@ -13,7 +13,7 @@ namespace hkm {
 
 constexpr int kMaxCols = 64;
 constexpr int kRowsPerBlockSmall = 128, kRowsPerBlockBig = 256;
-inline int assemble_rows_per_block(int d) { (void)d; return kRowsPerBlockSmall; }   // measured: 256-row blocks are slower (fewer resident blocks, longer per-thread column loop)
+inline int assemble_rows_per_block(int d) { (void)d; return kRowsPerBlockSmall; }   // measured (also with the warp-per-column loop): 256-row blocks are slower, three resident blocks per SM
 
 struct ColDesc { const void* data; const void* valid; int dtype; int vkind; };
 struct AssembleParams {
@@ -61,11 +61,9 @@ __global__ void __launch_bounds__(256) assemble_kernel(const AssembleParams p) {
   __shared__ int s_bad[ROWS];
   __shared__ int s_wsum[ROWS / 32];
   constexpr int kRowsPerBlock = ROWS;
-  constexpr int STEP = 256 / ROWS;            // columns in flight per step
   const int d = p.d, ld = d | 1;
   const int64_t row0 = (int64_t)blockIdx.x * kRowsPerBlock;
   const int rows = (int)min((int64_t)kRowsPerBlock, p.n - row0);
-  const int t = threadIdx.x & (kRowsPerBlock - 1), half = threadIdx.x / ROWS;
   if (threadIdx.x < kRowsPerBlock) {
     // bit 0: null / NaN somewhere in the row; bit 1: outside the time window
     int b0 = 0;
@@ -80,18 +78,43 @@ __global__ void __launch_bounds__(256) assemble_kernel(const AssembleParams p) {
     s_bad[threadIdx.x] = b0;
   }
   __syncthreads();
-  int bad = 0;
-  for (int c = half; c < d; c += STEP) {
-    if (t < rows) {
-      bool ok;
-      double v = load_col(p.cols[c], row0 + t, ok);
-      if (!ok) bad = 1;
-      if (p.shift != nullptr) v -= p.shift[c];
-      if (p.scale != nullptr) v *= p.scale[c];
-      if (p.mode != 2) tile[t * ld + c] = v;
+  // a warp takes a column at a time: the element type is decided once per warp and column (not per value), every lane reads
+  // ROWS / 32 rows of it back to back, and the values go transposed into the tile (row stride ld is odd: conflict free)
+  {
+    constexpr int RPL = ROWS / 32;
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const double qnan = __longlong_as_double(0x7ff8000000000000LL);
+    for (int c = w; c < d; c += 8) {
+      const ColDesc col = p.cols[c];
+      const double sh = p.shift != nullptr ? p.shift[c] : 0.0, sc = p.scale != nullptr ? p.scale[c] : 1.0;
+      double v[RPL];
+      const int64_t i0 = row0 + lane;
+      auto fetch = [&](auto* ptr) {
+#pragma unroll
+        for (int j = 0; j < RPL; ++j) v[j] = (lane + 32 * j < rows) ? (double)ptr[i0 + 32 * j] : 0.0;
+      };
+      switch (col.dtype) {
+        case HKM_DTYPE_F64: fetch(reinterpret_cast<const double*>(col.data)); break;
+        case HKM_DTYPE_F32: fetch(reinterpret_cast<const float*>(col.data)); break;
+        case HKM_DTYPE_I32: fetch(reinterpret_cast<const int32_t*>(col.data)); break;
+        case HKM_DTYPE_I64: fetch(reinterpret_cast<const int64_t*>(col.data)); break;
+        case HKM_DTYPE_I16: fetch(reinterpret_cast<const int16_t*>(col.data)); break;
+        case HKM_DTYPE_I8: fetch(reinterpret_cast<const int8_t*>(col.data)); break;
+        default: fetch(reinterpret_cast<const uint8_t*>(col.data)); break;
+      }
+#pragma unroll
+      for (int j = 0; j < RPL; ++j) {
+        const int r = lane + 32 * j;
+        if (r < rows) {
+          bool ok = v[j] == v[j];                      // VectorAssembler treats NaN like null
+          if (col.vkind == 1) ok = ok && reinterpret_cast<const uint8_t*>(col.valid)[i0 + 32 * j] != 0;
+          else if (col.vkind == 2) ok = ok && ((reinterpret_cast<const uint8_t*>(col.valid)[(i0 + 32 * j) >> 3] >> ((i0 + 32 * j) & 7)) & 1);
+          if (!ok) atomicOr(&s_bad[r], 1);
+          if (p.mode != 2) tile[r * ld + c] = ok ? (v[j] - sh) * sc : qnan;
+        }
+      }
     }
   }
-  if (bad) atomicOr(&s_bad[t], 1);
   __syncthreads();
   // rank of every valid row inside the block (exclusive), and the block's valid count
   int valid = 0, rank = 0;
@@ -124,15 +147,10 @@ __global__ void __launch_bounds__(256) assemble_kernel(const AssembleParams p) {
   if (p.mode == 2) return;
   __syncthreads();
   if (p.mode == 0) {
-    // contiguous, coalesced write of rows*d doubles; (row, column) advance incrementally -- no division per element
+    // a warp writes a row at a time: rows * d doubles, contiguous and coalesced
     double* out = p.X + row0 * d;
-    int rr = threadIdx.x / d, c = threadIdx.x - rr * d;
-    const int dr = blockDim.x / d, dc = blockDim.x - dr * d;
-    for (int i = threadIdx.x; i < rows * d; i += blockDim.x) {
-      out[i] = tile[rr * ld + c];
-      rr += dr; c += dc;
-      if (c >= d) { c -= d; ++rr; }
-    }
+    for (int rr = threadIdx.x >> 5; rr < rows; rr += 8)
+      for (int c = threadIdx.x & 31; c < d; c += 32) out[(int64_t)rr * d + c] = tile[rr * ld + c];
   } else {
     // compaction: scatter inside shared memory is avoided by reading through the rank table
     double* out = p.X + p.block_base[blockIdx.x] * d;
