@@ -645,18 +645,38 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
     for (int wv = 0; wv < nwarps; ++wv) c += red_s[wv];
     out[P - 1] = c; out[P] = 0.0;
   }
-  // ===================================================================== last CTA folds all partials
+  // ===================================================================== two-level fold of the per-CTA partials
+  // The CTAs form groups of 16; the last CTA of a group to finish folds the group's partials into a group slot (behind the
+  // per-CTA slots: this kernel launches one CTA per SM, the scratch is sized for two), and the last group folds the group slots.
+  // Fixed shape, so the result is the same whatever the order of arrival; a single CTA summing gridDim.x values per entry would
+  // pull CTAs x P doubles through one SM.
   __threadfence();
   __syncthreads();
   __shared__ unsigned int s_ticket;
+  constexpr unsigned GS = 16u;
+  const unsigned ngroups = (gridDim.x + GS - 1u) / GS, mygroup = blockIdx.x / GS;
+  const unsigned gsize = min(GS, gridDim.x - mygroup * GS);
+  if (tid == 0) s_ticket = atomicAdd(p.counter + 2 + mygroup, 1u);
+  __syncthreads();
+  if (s_ticket != gsize - 1u) return;
+  __threadfence();
+  {
+    double* gslot = p.cta_partials + (size_t)(gridDim.x + mygroup) * SL;
+    const double* src = p.cta_partials + (size_t)(mygroup * GS) * SL;
+    for (int i = tid; i < P; i += nthreads) gslot[i] = ordered_sum_ldcg(src + i, (size_t)SL, gsize);
+    if (tid == 0) p.counter[2 + mygroup] = 0u;
+  }
+  __threadfence();
+  __syncthreads();
   if (tid == 0) s_ticket = atomicAdd(p.counter, 1u);
   __syncthreads();
-  if (s_ticket == gridDim.x - 1) {
+  if (s_ticket == ngroups - 1u) {
     __threadfence();
-    for (int i = tid; i < P - 1; i += nthreads) p.partial_out[i] = ordered_sum_ldcg(p.cta_partials + i, (size_t)SL, gridDim.x);
+    const double* gs = p.cta_partials + (size_t)gridDim.x * SL;
+    for (int i = tid; i < P - 1; i += nthreads) p.partial_out[i] = ordered_sum_ldcg(gs + i, (size_t)SL, ngroups);
     __syncthreads();
     if (tid == 0) {
-      const double ssc = ordered_sum_ldcg(p.cta_partials + (P - 1), (size_t)SL, gridDim.x);
+      const double ssc = ordered_sum_ldcg(gs + (P - 1), (size_t)SL, ngroups);
       p.partial_out[P - 1] = fmax(fma(-2.0, ssc, *p.xnorm2_sum), 0.0);      // cost = sum |x|^2 - 2 sum score (REUSE pass)
       *p.counter = 0u;
       rec->done = 1;                                                         // the launch behind this one has nothing to do

@@ -8,7 +8,7 @@ for n, d, k in [(1000, 16, 16), (1000, 32, 8), (1000, 24, 32), (1000, 64, 64), (
     partial = torch.empty(k * d + k + 1, dtype=torch.float64, device="cuda"); scratch = N.new_scratch(d, k, "cuda")
     xs = torch.zeros(1, dtype=torch.float64, device="cuda")
     row = dict(n=n, d=d, k=k)
-    for v, name in ((5, "round1"), (4, "tp"), (6, "wg")):
+    for v, name in ((5, "round1"), (4, "tp"), (6, "wg"), (0, "default")):
         N.set_lloyd_variant(v)
         for _ in range(3):
             N.assign_reduce(X, C, partial, scratch=scratch, xnorm2_sum=xs, xnorm2_mode=1)
