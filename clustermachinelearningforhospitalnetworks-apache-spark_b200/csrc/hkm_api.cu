@@ -152,6 +152,8 @@ int assign_pass(const AssignArgs& a, const char* who) {
   p.stages = pl.stages; p.ks = (d + 3) / 4;
   const int grid = sm_count() * pl.ctas_per_sm;
   const int mode = (a.mode == 0 && a.weights != nullptr) ? 3 : a.mode;   // weights are a compile-time property of the Lloyd kernels
+  if (a.n > 0 && lloyd_wd_shape(p, mode) && (p.do_reduce == 0 || a.scratch != nullptr))   // distance-returning passes with 8 < k <= 64, even d <= 48
+    return launch_lloyd_wd(p, reinterpret_cast<cudaStream_t>(a.stream));
   if (lloyd_wl_shape(p, mode) && a.scratch != nullptr && a.scratch_bytes >= wl_tail_offset(d, k) + wl_tail_bytes() && a.n > 0) {
     // limb-reduction variant: the STORE pass also measures the column ranges (one more read of the table, once per fit); REUSE
     // passes run the variant, which declines on its own when the record does not admit the table -- the launch below then works

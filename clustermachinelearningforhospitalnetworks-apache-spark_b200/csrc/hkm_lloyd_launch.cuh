@@ -64,6 +64,9 @@ size_t wl_done_offset();      // offset of the "pass produced" flag inside the r
 size_t assign_reduce_scratch_core(int d, int k);
 int launch_column_range(const double* X, int64_t n, int d, void* tail, cudaStream_t st);
 int launch_lloyd_wl(const LloydParams& p, void* tail, cudaStream_t st);
+// the same kernel as a distance-returning pass (k-means|| cost update, candidate weights): no record needed
+bool lloyd_wd_shape(const LloydParams& p, int mode);
+int launch_lloyd_wd(const LloydParams& p, cudaStream_t st);
 // 0: pick per shape (default); 1: always the gather variant; 2: the tensor-pipe variant wherever it is built;
 // 3: the warp-specialised variant wherever it is built; 4: the pipelined tcgen05 variant wherever it is built;
 // 5: the round-1 choice (no pipelined tcgen05 variant); 6: the warp-group tcgen05 variant wherever it is built; 7: as 0 (the limb-reduction variant is a REUSE-pass refinement of 0).  Set through hkm_set_lloyd_variant (tuning and tests).

@@ -92,6 +92,18 @@ bool lloyd_wl_shape(const LloydParams& p, int mode) {
   return wl_groups(16 * ((p.d + 15) / 16), kp) > 0;
 }
 
+// Distance-returning passes the same kernel takes without the limb sums (k-means|| cost update and candidate weights: running
+// minimum of the squared distance, labels, cost sum): 8 < k <= 64 centres per launch, even d <= 48
+bool lloyd_wd_shape(const LloydParams& p, int mode) {
+  const int variant = lloyd_variant_override();
+  if (g_wl_off || (variant != 0 && variant != 7)) return false;
+  if (mode != 0 || p.w != nullptr || p.mind2_out == nullptr || (p.do_reduce != 0 && p.do_reduce != 2)) return false;
+  if (p.k <= 8 || p.k > 64 || p.d > 48 || p.d < 2 || (p.d & 1)) return false;
+  if (p.n >= (int64_t)1 << 31) return false;
+  const int kp = ((p.k + 15) / 16) * 16;
+  return wl_groups_dist(16 * ((p.d + 15) / 16), kp) > 0;
+}
+
 int launch_column_range(const double* X, int64_t n, int d, void* tail, cudaStream_t st) {
   static_assert(sizeof(RangeRec) <= 2048, "range record");
   RangeRec* rec = reinterpret_cast<RangeRec*>(tail);
@@ -135,16 +147,54 @@ static int launch_wl(const LloydParams& p, const CUtensorMap& tmap, RangeRec* re
   }
 }
 
-int launch_lloyd_wl(const LloydParams& p, void* tail, cudaStream_t st) {
+static int make_tmap(const LloydParams& p, CUtensorMap& tmap) {
   EncodeTiledFn enc = encode_tiled();
   if (enc == nullptr) { set_error("lloyd_wl: cuTensorMapEncodeTiled is not available"); return HKM_ERR_UNSUPPORTED; }
-  CUtensorMap tmap;
   const cuuint64_t gdim[2] = {(cuuint64_t)p.d, (cuuint64_t)p.n};
   const cuuint64_t gstride[1] = {(cuuint64_t)p.d * 8};
   const cuuint32_t box[2] = {16, 32}, estr[2] = {1, 1};
   const CUresult cr = enc(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<double*>(p.X), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (cr != CUDA_SUCCESS) { set_error("lloyd_wl: cuTensorMapEncodeTiled failed (%d)", (int)cr); return HKM_ERR_CUDA; }
+  return HKM_OK;
+}
+
+template <int KP, int NS>
+static int launch_wd(const LloydParams& p, const CUtensorMap& tmap, cudaStream_t st) {
+  constexpr int G = wl_groups_dist(16 * NS, KP);
+  if constexpr (G == 0) { set_error("lloyd_wd: d=%d k=%d does not fit", p.d, p.k); return HKM_ERR_UNSUPPORTED; }
+  else {
+    constexpr WlPlan L = wl_plan(16 * NS, KP, G, wl_stages(16 * NS, KP, G, 1, 1), 1, 1);
+    auto kern = lloyd_wl_kernel<KP, NS, G, 1, 1>;
+    static bool attr_done[64];
+    int dev = 0; HKM_CUDA_TRY(cudaGetDevice(&dev));
+    if (dev >= 64 || !attr_done[dev]) {
+      HKM_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
+      if (dev < 64) attr_done[dev] = true;
+    }
+    kern<<<sm_count(), G * 128, L.total, st>>>(p, tmap, nullptr, g_wl_prof, 0);
+    HKM_CUDA_TRY(cudaGetLastError());
+    return HKM_OK;
+  }
+}
+
+int launch_lloyd_wd(const LloydParams& p, cudaStream_t st) {
+  CUtensorMap tmap;
+  const int rc = make_tmap(p, tmap);
+  if (rc != HKM_OK) return rc;
+  const int kp = ((p.k + 15) / 16) * 16, ns = (p.d + 15) / 16;
+#define HKM_WD_CASE(KPV, NSV) if (kp == KPV && ns == NSV) return launch_wd<KPV, NSV>(p, tmap, st);
+  HKM_WD_CASE(16, 1) HKM_WD_CASE(32, 1) HKM_WD_CASE(48, 1) HKM_WD_CASE(64, 1)
+  HKM_WD_CASE(16, 2) HKM_WD_CASE(32, 2) HKM_WD_CASE(48, 2) HKM_WD_CASE(64, 2)
+  HKM_WD_CASE(16, 3) HKM_WD_CASE(32, 3) HKM_WD_CASE(48, 3) HKM_WD_CASE(64, 3)
+#undef HKM_WD_CASE
+  set_error("lloyd_wd: no instantiation for d=%d k=%d", p.d, p.k);
+  return HKM_ERR_UNSUPPORTED;
+}
+
+int launch_lloyd_wl(const LloydParams& p, void* tail, cudaStream_t st) {
+  CUtensorMap tmap;
+  { const int rc = make_tmap(p, tmap); if (rc != HKM_OK) return rc; }
   RangeRec* rec = reinterpret_cast<RangeRec*>(tail);
   const int kp = ((p.k + 15) / 16) * 16, ns = (p.d + 15) / 16;
 #define HKM_WL_CASE(KPV, NSV) if (kp == KPV && ns == NSV) return launch_wl<KPV, NSV>(p, tmap, rec, st);

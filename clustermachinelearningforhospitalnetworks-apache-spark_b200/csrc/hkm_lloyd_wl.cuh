@@ -45,13 +45,14 @@ struct RangeRec {
 
 struct WlPlan {
   int groups, stages, kchunks, lbo_b, lbo_h, h_bytes, tile_bytes, tcols, acols, tstride, gstride, rcol0;
-  int x_off, b_off, h_off, ex_off, cn_off, mu_off, mg_off, cnt_off, red_off, bar_off, seq_off, tmem_off, cs_off, total;
+  int x_off, b_off, h_off, ex_off, ct_off, ct_pitch, cn_off, mu_off, mg_off, cnt_off, red_off, bar_off, seq_off, tmem_off, cs_off, total;
 };
 
 // Tensor memory, per group: [tf32 operand: d data columns + 8 constant columns][scores: k_pad], then behind all groups the s32 limb
 // sums [slab][k_pad], one set for the whole CTA (every warp adds its products into it).  Shared memory: ring stages (1024-byte aligned), the centres' tf32 operand, the one-hot operands.
 // halves = warps per 32 rows (1, or 2: the features and the score columns of a row split over two threads)
-__host__ __device__ constexpr inline WlPlan wl_plan(int d, int kp, int groups, int stages, int halves = 1) {
+// dist = 1: the distance-returning variant (no limb sums: no one-hot operands, no limb columns; a padded fp64 centre table instead)
+__host__ __device__ constexpr inline WlPlan wl_plan(int d, int kp, int groups, int stages, int halves = 1, int dist = 0) {
   WlPlan L{};
   L.groups = groups; L.stages = stages;
   const int ns = d / 16;
@@ -64,12 +65,14 @@ __host__ __device__ constexpr inline WlPlan wl_plan(int d, int kp, int groups, i
   L.tstride = kp <= 32 ? 32 : 64;
   L.gstride = L.acols + L.tstride;
   L.rcol0 = groups * L.gstride;
-  int tc = 32; while (tc < L.rcol0 + ns * kp) tc *= 2;
+  int tc = 32; while (tc < L.rcol0 + (dist ? 0 : ns * kp)) tc *= 2;
   L.tcols = tc;
   int o = 0;
   L.x_off = o; o += stages * L.tile_bytes;         // 1024-byte aligned (swizzle atoms)
   L.b_off = o; o += (L.kchunks * L.lbo_b + 127) & ~127;
-  L.h_off = o; o += groups * L.h_bytes;
+  L.h_off = o; o += dist ? 0 : groups * L.h_bytes;
+  L.ct_pitch = d * 8 + 16;                         // centre rows 16 bytes apart modulo 128: gathers by label spread over the banks
+  L.ct_off = o; o += dist ? kp * L.ct_pitch : 0;
   L.ex_off = o; o += halves > 1 ? groups * kTileRows * 2 * 16 : 0;     // exchange slots of the two threads of a row
   L.cn_off = o; o += kp * 8;
   L.mu_off = o; o += (d + 8) * 8;
@@ -85,14 +88,14 @@ __host__ __device__ constexpr inline WlPlan wl_plan(int d, int kp, int groups, i
   return L;
 }
 
-__host__ __device__ constexpr inline int wl_stages(int d, int kp, int g, int halves = 1) {
+__host__ __device__ constexpr inline int wl_stages(int d, int kp, int g, int halves = 1, int dist = 0) {
   if (g < 1 || g * halves > kWlMaxGroups) return 0;
-  const WlPlan z = wl_plan(d, kp, g, 0, halves);
+  const WlPlan z = wl_plan(d, kp, g, 0, halves, dist);
   if (z.tcols > 512) return 0;
   const int budget = 227 * 1024 - 1024;             // the static words are padded to 1 KB (alignment of the dynamic part)
   int st = kWlMaxStages;
-  while (st > 0 && wl_plan(d, kp, g, st, halves).total > budget) --st;
-  const int comb = (d / 16) * kp * 128 * 4;         // s32 accumulators parked in the idle ring for the final combine
+  while (st > 0 && wl_plan(d, kp, g, st, halves, dist).total > budget) --st;
+  const int comb = dist ? 0 : (d / 16) * kp * 128 * 4;   // s32 accumulators parked in the idle ring for the final combine
   if (st < g + 2 || (st - g) * z.tile_bytes < 40 * 1024 || st * z.tile_bytes < comb) return 0;
   if (g == 1 && halves == 1 && d <= 32) return 0;   // a single group only where nothing else fits
   return st;
@@ -105,6 +108,11 @@ __host__ __device__ constexpr inline int wl_groups1(int d, int kp) {
 }
 __host__ __device__ constexpr inline int wl_halves(int d, int kp) { return (wl_groups1(d, kp) == 1 && wl_stages(d, kp, 1, 2) > 0) ? 2 : 1; }
 __host__ __device__ constexpr inline int wl_groups(int d, int kp) { return wl_halves(d, kp) == 2 ? 1 : wl_groups1(d, kp); }
+// the distance-returning variant: one thread per row only
+__host__ __device__ constexpr inline int wl_groups_dist(int d, int kp) {
+  for (int g = 6; g >= 2; --g) if (wl_stages(d, kp, g, 1, 1) > 0) return g;
+  return 0;
+}
 
 __device__ __forceinline__ void sts_u8(uint32_t a, uint32_t v) { asm volatile("st.shared.u8 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
 __device__ __forceinline__ uint64_t wl_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout_type) {
@@ -129,13 +137,14 @@ __device__ __forceinline__ void wl_tmem_wait_st() { asm volatile("tcgen05.wait::
 // Thread = row throughout: a thread reads its row through the swizzle (eight consecutive rows hit eight different 16-byte columns),
 // writes the tf32 values into its lane of the group's tensor-memory operand (the tensor core takes A from TMEM: no shared-memory
 // copy of the operand at all), keeps |x - mu|^2 in a register, and overwrites the row in place with its fixed-point form.
-template <int KP, int NS, int GFIX, int H = 1>
+template <int KP, int NS, int GFIX, int H = 1, int DIST = 0>
 __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const LloydParams p, const __grid_constant__ CUtensorMap tmap, RangeRec* rec,
                                                                  unsigned long long* prof_buf, int flags) {
   if (p.skip != nullptr && *p.skip != 0) return;
-  constexpr int DP = 16 * NS, ND = 2 * NS, G = GFIX, S = wl_stages(DP, KP, GFIX, H);   // DP: features padded to whole slabs
-  constexpr WlPlan L = wl_plan(DP, KP, GFIX, S, H);
+  constexpr int DP = 16 * NS, ND = 2 * NS, G = GFIX, S = wl_stages(DP, KP, GFIX, H, DIST);   // DP: features padded to whole slabs
+  constexpr WlPlan L = wl_plan(DP, KP, GFIX, S, H, DIST);
   static_assert(H == 1 || H == 2, "one or two threads per row");
+  static_assert(DIST == 0 || H == 1, "the distance-returning variant keeps a row in one thread");
   const int d = p.d;                                  // even, DP - 16 < d <= DP; the padding columns arrive as zeros (tensor-map bounds)
   static_assert(S >= GFIX + 2, "shape does not fit");
   constexpr int NW = (KP + 31) / 32;
@@ -147,9 +156,11 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
   constexpr uint32_t LBO_B = L.lbo_b, LBO_H = L.lbo_h, tile_bytes = L.tile_bytes;
   constexpr uint32_t SLAB = kTileRows * 128;          // bytes of one 16-feature slab of a tile
   // the record must describe this table and admit it; otherwise the launch behind this one does the pass
-  if (rec->ok != 1 || rec->tag_x != (unsigned long long)(uintptr_t)p.X || rec->n != (long long)p.n || rec->d != p.d) {
-    if (blockIdx.x == 0 && threadIdx.x == 0) rec->done = 0;
-    return;
+  if constexpr (DIST == 0) {
+    if (rec->ok != 1 || rec->tag_x != (unsigned long long)(uintptr_t)p.X || rec->n != (long long)p.n || rec->d != p.d) {
+      if (blockIdx.x == 0 && threadIdx.x == 0) rec->done = 0;
+      return;
+    }
   }
 
   extern __shared__ __align__(1024) unsigned char smem_raw[];
@@ -193,14 +204,21 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
   // zero: B and the one-hot operands (one contiguous range), counters
-  for (int i = tid; i < (L.cn_off - L.b_off) / 16; i += nthreads) reinterpret_cast<uint4*>(smem + L.b_off)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = tid; i < ((DIST ? L.ct_off : L.cn_off) - L.b_off) / 16; i += nthreads) reinterpret_cast<uint4*>(smem + L.b_off)[i] = make_uint4(0, 0, 0, 0);
   for (int i = tid; i < KP; i += nthreads) cnt_s[i] = 0u;
   for (int i = tid; i < 4 * H * S; i += nthreads) reinterpret_cast<uint32_t*>(smem + L.seq_off)[i] = (uint32_t)(i / (4 * H));
   if (L.cs_off != 0) for (int i = tid; i < k * d; i += nthreads) reinterpret_cast<double*>(smem + L.cs_off)[i] = p.C[i];
+  if constexpr (DIST != 0) {
+    // fp64 centres for the exact distance of every row's winner: row j at j * ct_pitch, padding columns zero
+    for (int i = tid; i < KP * DP; i += nthreads) {
+      const int j = i / DP, f = i - j * DP;
+      *reinterpret_cast<double*>(smem + L.ct_off + j * L.ct_pitch + f * 8) = (j < k && f < d) ? p.C[(size_t)j * d + f] : 0.0;
+    }
+  }
   if (tid < DP + 8) { double s = 0; if (tid < d) for (int j = 0; j < k; ++j) s += p.C[(size_t)j * d + tid]; mu_s[tid] = tid < d ? s / k : 0.0; }
   if (tid < DP) {
     // M_f = 1.5 * 2^(E_f + 2): exponent field of the column's largest magnitude + 2, top mantissa bit set (padding columns: 1.5)
-    const unsigned eb = tid < d ? (rec->emax_hi[tid] >> 20) & 0x7ffu : 1021u;
+    const unsigned eb = (DIST == 0 && tid < d) ? (rec->emax_hi[tid] >> 20) & 0x7ffu : 1021u;
     mg_s[tid] = __longlong_as_double(((long long)(eb + 2u) << 52) | (1ll << 51));
   }
   __syncthreads();
@@ -251,7 +269,7 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
     // the limb sums start at zero (every product below accumulates; the four warps of a group issue theirs independently)
     const uint32_t zv[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
 #pragma unroll 1
-    if (grp == 0 && hh == 0) for (int c0 = 0; c0 < NS * KP; c0 += 8) wl_tmem_st8(tmem + tlane + (uint32_t)L.rcol0 + (uint32_t)c0, zv);
+    if (DIST == 0 && grp == 0 && hh == 0) for (int c0 = 0; c0 < NS * KP; c0 += 8) wl_tmem_st8(tmem + tlane + (uint32_t)L.rcol0 + (uint32_t)c0, zv);
     wl_tmem_wait_st();
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   }
@@ -401,6 +419,7 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
         xa = fmaf(a0, a0, xa); xb = fmaf(a1, a1, xb);
       }
       wl_tmem_st16(t_A + (uint32_t)(16 * sl), tv);
+      if constexpr (DIST == 0)
 #pragma unroll
       for (int c = 0; c < 8; ++c) {
         double m0, m1;
@@ -555,6 +574,46 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
       }
       if (prof) pw2 += clock64() - tr0;
     }
+    if constexpr (DIST != 0) {
+      // ---- exact distance to the winner from the row's fp64 values (the stage still holds them) and the padded centre table:
+      // score = x.c - 0.5|c|^2 and |x|^2 in ascending feature order, dist = max(|x|^2 - 2 score, 0), as every other variant
+      double sc = 0.0, xx = 0.0;
+      const uint32_t crow = sb + L.ct_off + (uint32_t)lab * (uint32_t)L.ct_pitch;
+#pragma unroll
+      for (int sl = 0; sl < NS; ++sl) {
+        const uint32_t xr = xs + (uint32_t)sl * SLAB + xrow;
+        double xv[16], cv[16];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+          lds_v2f64(xr + (((uint32_t)c << 4) ^ xsw), xv[2 * c], xv[2 * c + 1]);
+          lds_v2f64(crow + (uint32_t)(16 * sl + 2 * c) * 8u, cv[2 * c], cv[2 * c + 1]);
+        }
+#pragma unroll
+        for (int f = 0; f < 16; ++f) { sc = fma(xv[f], cv[f], sc); xx = fma(xv[f], xv[f], xx); }
+      }
+      const double dist = fmax(fma(-2.0, sc + cn_s[lab], xx), 0.0);
+      if (valid) {
+        const int64_t r = ((int64_t)blockIdx.x + (int64_t)i * gridDim.x) * kTileRows + row;
+        if (p.out_mode == 0) {
+          if (p.labels_out != nullptr) p.labels_out[r] = lab;
+          p.mind2_out[r] = dist;
+          cost += dist;
+        } else {
+          // running minimum over successive centre chunks: strict '<' keeps the earlier (lower-index) centre on ties
+          const double old = p.mind2_out[r];
+          if (dist < old) {
+            p.mind2_out[r] = dist;
+            if (p.labels_out != nullptr) p.labels_out[r] = lab + p.label_base;
+            cost += dist;
+          } else cost += old;
+        }
+      }
+      __syncwarp();
+      if (i + S < T) tma_load(i + S, xs, bar_f, seqa);
+      s += G; if (s >= S) { s -= S; ph ^= 1u; }
+      tph ^= 1u;
+      continue;
+    }
     // ---- this row's one-hot byte, label, count (rows past the end take no part)
     const uint32_t hb = hrow + 16u * (uint32_t)lab;
     if (valid && hh == 0) {
@@ -595,6 +654,31 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
     unsigned long long* o = prof_buf + warp * 8;
     o[0] = (unsigned long long)(clock64() - pt0); o[1] = (unsigned long long)pw0; o[2] = (unsigned long long)pw1; o[3] = (unsigned long long)pw2;
     o[4] = 0ull; o[5] = (unsigned long long)pcnt; o[6] = (unsigned long long)T; o[7] = 0ull;
+  }
+  if constexpr (DIST != 0) {
+    // ===================================================================== distance variant: only the cost is folded
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(L.tcols) : "memory");
+    if (p.do_reduce != 2) return;
+#pragma unroll
+    for (int msk = 16; msk >= 1; msk >>= 1) cost += shfl_xor_d(cost, msk);
+    if (lane == 0) red_s[warp] = cost;
+    __syncthreads();
+    __shared__ unsigned int s_tk;
+    if (tid == 0) {
+      double c = 0;
+      for (int wv = 0; wv < nwarps; ++wv) c += red_s[wv];
+      p.cta_partials[blockIdx.x] = c;
+      __threadfence();
+      s_tk = atomicAdd(p.counter, 1u);
+      if (s_tk == gridDim.x - 1) {
+        __threadfence();
+        p.partial_out[0] = ordered_sum_ldcg(p.cta_partials, 1, gridDim.x);   // CTA order: bit-stable
+        *p.counter = 0u;
+      }
+    }
+    return;
   }
   // ===================================================================== CTA-level combine (all warps)
   // every tile is reduced and no copy is in flight: the s32 limb sums go from TMEM to the idle ring, acc[sl KP + c][byte]

@@ -163,3 +163,44 @@ def test_fit_with_limb_passes_matches_oracle(hkm, oracle):
     assert model.summary.numIter == it
     assert np.allclose(G, Co, rtol=1e-9, atol=1e-11)
     assert model.summary.trainingCost == pytest.approx(cost, rel=1e-9)
+
+
+@pytest.mark.parametrize("n,d,m", [(50000, 16, 12), (30011, 24, 33), (40000, 32, 64), (20000, 48, 20), (129, 16, 16), (70003, 8, 40), (60000, 16, 100),
+                                   (50000, 20, 9)])
+def test_distance_variant_kmpar_passes(hkm, n, d, m):
+    """k-means|| data passes on the distance-returning variant of the same kernel (running minimum of the squared distance to the
+    new centres, its sum, nearest candidate per row and the counts): against NumPy in the oracle's arithmetic, and against the
+    round-1 kernels with the variant switched off."""
+    N = hkm._native
+    X, C = _blobs(n, d, m, 3 * n + d + m)
+    Xd = torch.from_numpy(X).cuda(); Cd = torch.from_numpy(C).cuda()
+    rng = np.random.default_rng(5)
+    start = rng.random(n) * 40.0                                          # costs so far: some rows improve, some do not
+    # reference: dist = max(|x|^2 - 2 (x.c - 0.5|c|^2), 0), nearest = lowest index among equals
+    xx = (X * X).sum(axis=1)
+    sc = X @ C.T - 0.5 * (C * C).sum(axis=1)[None, :]
+    dist = np.maximum(xx[:, None] - 2.0 * sc, 0.0)
+    want = np.minimum(start, dist.min(axis=1))
+    scale = float(xx.max()) + 1.0
+    outs = []
+    for off in (0, 1):
+        N.load().hkm_debug_wl_off(ctypes.c_int(off))
+        try:
+            costs = torch.from_numpy(start.copy()).cuda(); tot = torch.zeros(1, dtype=torch.float64, device="cuda")
+            N.kmpar_cost_update(Xd, Cd, costs, tot, N.new_scratch(d, min(m, 64), "cuda"))
+            labels = torch.empty(n, dtype=torch.int32, device="cuda"); mind2 = torch.empty(n, dtype=torch.float64, device="cuda")
+            counts = torch.zeros(m, dtype=torch.int64, device="cuda")
+            N.closest_counts(Xd, Cd, labels, mind2, counts)
+            torch.cuda.synchronize()
+        finally:
+            N.load().hkm_debug_wl_off(ctypes.c_int(0))
+        outs.append((costs.cpu().numpy(), tot.item(), labels.cpu().numpy(), mind2.cpu().numpy(), counts.cpu().numpy()))
+    for costs, tot, labels, mind2, counts in outs:
+        assert np.abs(costs - want).max() <= 1e-9 * scale
+        assert tot == pytest.approx(want.sum(), rel=1e-12)
+        near = dist.argmin(axis=1)
+        same = labels == near
+        assert same.mean() >= 0.9999
+        assert np.abs(mind2 - dist.min(axis=1)).max() <= 1e-9 * scale
+        assert counts.sum() == n and np.array_equal(counts, np.bincount(labels, minlength=m))
+    assert (outs[0][2] == outs[1][2]).mean() >= 0.9999 and np.abs(outs[0][0] - outs[1][0]).max() <= 1e-9 * scale
