@@ -8,6 +8,7 @@ namespace hkm {
 static unsigned long long* g_wl_prof = nullptr;
 static int g_wl_off = 0;       // developer switch: 1 = never use this variant
 static int g_wl_flags = -1;    // developer switch: bit 0 = close the previous tile at the top of the iteration when its product is done
+static int g_wl_nohalf = 0;    // developer switch: 1 = pad rows to whole 16-feature slabs (no half slab)
 static int g_wl_groups = 0;    // developer switch: group count for d = 16, k <= 16 (4, 5 or 6)
 
 // ---- column range pass: per column the largest magnitude (its exponent) and the mean exponent of the nonzero values; one read of
@@ -87,7 +88,7 @@ bool lloyd_wl_shape(const LloydParams& p, int mode) {
   const int kp = ((p.k + 15) / 16) * 16;
   // measured against the warp-group variant on the same box (tools/wl_check.py bench): with k <= 16 and rows of 18..24 features
   // the padding to two slabs costs more than the cheaper reduction saves
-  if (variant == 0 && kp == 16 && p.d > 16 && p.d <= 24) return false;
+  if (variant == 0 && kp == 16 && p.d > 16 && p.d <= 24 && g_wl_nohalf) return false;
   if (variant == 0 && kp == 16 && p.d > 32) return false;                     // one group of four warps: the fp64 tensor-pipe kernel is ahead there
   return wl_groups(16 * ((p.d + 15) / 16), kp) > 0;
 }
@@ -127,34 +128,36 @@ static EncodeTiledFn encode_tiled() {
   return fn;
 }
 
-template <int KP, int NS, int GO = 0>
-static int launch_wl(const LloydParams& p, const CUtensorMap& tmap, RangeRec* rec, cudaStream_t st) {
-  constexpr int H = GO > 0 ? 1 : wl_halves(16 * NS, KP);
-  constexpr int G = GO > 0 ? GO : wl_groups(16 * NS, KP);
+template <int KP, int NS, int GO = 0, int HS = 0>
+static int launch_wl(const LloydParams& p, const CUtensorMap& tmap, const CUtensorMap& tmap_h, RangeRec* rec, cudaStream_t st) {
+  constexpr int DPAD = 16 * NS + 8 * HS;
+  constexpr int H = (GO > 0 || HS) ? 1 : wl_halves(DPAD, KP);
+  constexpr int G = GO > 0 ? GO : (HS ? wl_groups1(DPAD, KP) : wl_groups(DPAD, KP));
   if constexpr (G == 0) { set_error("lloyd_wl: d=%d k=%d does not fit", p.d, p.k); return HKM_ERR_UNSUPPORTED; }
   else {
-    constexpr WlPlan L = wl_plan(16 * NS, KP, G, wl_stages(16 * NS, KP, G, H), H);
-    auto kern = lloyd_wl_kernel<KP, NS, G, H>;
+    constexpr WlPlan L = wl_plan(DPAD, KP, G, wl_stages(DPAD, KP, G, H), H);
+    auto kern = lloyd_wl_kernel<KP, NS, G, H, 0, HS>;
     static bool attr_done[64];
     int dev = 0; HKM_CUDA_TRY(cudaGetDevice(&dev));
     if (dev >= 64 || !attr_done[dev]) {
       HKM_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
       if (dev < 64) attr_done[dev] = true;
     }
-    kern<<<sm_count(), G * 128 * H, L.total, st>>>(p, tmap, rec, g_wl_prof, g_wl_flags >= 0 ? g_wl_flags : (((NS == 2 && KP == 16) || (NS == 1 && KP == 32)) ? 1 : 0));
+    kern<<<sm_count(), G * 128 * H, L.total, st>>>(p, tmap, tmap_h, rec, g_wl_prof, g_wl_flags >= 0 ? g_wl_flags : (((NS == 2 && KP == 16) || (NS == 1 && KP == 32)) ? 1 : 0));
     HKM_CUDA_TRY(cudaGetLastError());
     return HKM_OK;
   }
 }
 
-static int make_tmap(const LloydParams& p, CUtensorMap& tmap) {
+static int make_tmap(const LloydParams& p, CUtensorMap& tmap, int box_cols = 16) {
   EncodeTiledFn enc = encode_tiled();
   if (enc == nullptr) { set_error("lloyd_wl: cuTensorMapEncodeTiled is not available"); return HKM_ERR_UNSUPPORTED; }
   const cuuint64_t gdim[2] = {(cuuint64_t)p.d, (cuuint64_t)p.n};
   const cuuint64_t gstride[1] = {(cuuint64_t)p.d * 8};
-  const cuuint32_t box[2] = {16, 32}, estr[2] = {1, 1};
+  const cuuint32_t box[2] = {(cuuint32_t)box_cols, 32}, estr[2] = {1, 1};
   const CUresult cr = enc(&tmap, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<double*>(p.X), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                          box_cols == 16 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (cr != CUDA_SUCCESS) { set_error("lloyd_wl: cuTensorMapEncodeTiled failed (%d)", (int)cr); return HKM_ERR_CUDA; }
   return HKM_OK;
 }
@@ -172,7 +175,7 @@ static int launch_wd(const LloydParams& p, const CUtensorMap& tmap, cudaStream_t
       HKM_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
       if (dev < 64) attr_done[dev] = true;
     }
-    kern<<<sm_count(), G * 128, L.total, st>>>(p, tmap, nullptr, g_wl_prof, 0);
+    kern<<<sm_count(), G * 128, L.total, st>>>(p, tmap, tmap, nullptr, g_wl_prof, 0);
     HKM_CUDA_TRY(cudaGetLastError());
     return HKM_OK;
   }
@@ -196,10 +199,23 @@ int launch_lloyd_wl(const LloydParams& p, void* tail, cudaStream_t st) {
   CUtensorMap tmap;
   { const int rc = make_tmap(p, tmap); if (rc != HKM_OK) return rc; }
   RangeRec* rec = reinterpret_cast<RangeRec*>(tail);
-  const int kp = ((p.k + 15) / 16) * 16, ns = (p.d + 15) / 16;
-#define HKM_WL_CASE(KPV, NSV) if (kp == KPV && ns == NSV) return launch_wl<KPV, NSV>(p, tmap, rec, st);
-  if (kp == 16 && ns == 1 && g_wl_groups == 4) return launch_wl<16, 1, 4>(p, tmap, rec, st);
-  if (kp == 16 && ns == 1 && g_wl_groups == 5) return launch_wl<16, 1, 5>(p, tmap, rec, st);
+  const int kp = ((p.k + 15) / 16) * 16;
+  // rows of 16 ns + 1 .. 16 ns + 8 features (ns = 1, 2) take ns slabs of 16 and a half slab of 8 instead of padding to ns + 1 slabs
+  const int r16 = p.d % 16;
+  if (r16 >= 1 && r16 <= 8 && p.d > 16 && p.d <= 40 && !g_wl_nohalf) {
+    CUtensorMap tmap_h;
+    { const int rc = make_tmap(p, tmap_h, 8); if (rc != HKM_OK) return rc; }
+    const int nsf = p.d / 16;
+#define HKM_WLH_CASE(KPV, NSV) if (kp == KPV && nsf == NSV) return launch_wl<KPV, NSV, 0, 1>(p, tmap, tmap_h, rec, st);
+    if (kp == 16 && nsf == 1) return launch_wl<16, 1, 5, 1>(p, tmap, tmap_h, rec, st);     // five groups: 96 registers (six spill at 80)
+    HKM_WLH_CASE(32, 1) HKM_WLH_CASE(48, 1) HKM_WLH_CASE(64, 1)
+    HKM_WLH_CASE(16, 2) HKM_WLH_CASE(32, 2) HKM_WLH_CASE(48, 2) HKM_WLH_CASE(64, 2)
+#undef HKM_WLH_CASE
+  }
+  const int ns = (p.d + 15) / 16;
+#define HKM_WL_CASE(KPV, NSV) if (kp == KPV && ns == NSV) return launch_wl<KPV, NSV>(p, tmap, tmap, rec, st);
+  if (kp == 16 && ns == 1 && g_wl_groups == 4) return launch_wl<16, 1, 4>(p, tmap, tmap, rec, st);
+  if (kp == 16 && ns == 1 && g_wl_groups == 5) return launch_wl<16, 1, 5>(p, tmap, tmap, rec, st);
   HKM_WL_CASE(16, 1) HKM_WL_CASE(32, 1) HKM_WL_CASE(48, 1) HKM_WL_CASE(64, 1)
   HKM_WL_CASE(16, 2) HKM_WL_CASE(32, 2) HKM_WL_CASE(48, 2) HKM_WL_CASE(64, 2)
   HKM_WL_CASE(16, 3) HKM_WL_CASE(32, 3) HKM_WL_CASE(48, 3) HKM_WL_CASE(64, 3)
@@ -215,3 +231,4 @@ extern "C" __attribute__((visibility("default"))) void hkm_debug_wl_profile(void
 extern "C" __attribute__((visibility("default"))) void hkm_debug_wl_off(int off) { hkm::g_wl_off = off; }
 extern "C" __attribute__((visibility("default"))) void hkm_debug_wl_groups(int g) { hkm::g_wl_groups = g; }
 extern "C" __attribute__((visibility("default"))) void hkm_debug_wl_flags(int f) { hkm::g_wl_flags = f; }
+extern "C" __attribute__((visibility("default"))) void hkm_debug_wl_nohalf(int f) { hkm::g_wl_nohalf = f; }

@@ -55,17 +55,17 @@ struct WlPlan {
 __host__ __device__ constexpr inline WlPlan wl_plan(int d, int kp, int groups, int stages, int halves = 1, int dist = 0) {
   WlPlan L{};
   L.groups = groups; L.stages = stages;
-  const int ns = d / 16;
+  const int ns = d / 16, hs = (d % 16) ? 1 : 0;     // full 16-feature slabs, and a trailing 8-feature half slab (d = 16 ns + 8)
   L.kchunks = (d + 8) / 4;
   L.lbo_b = (kp / 8) * 128 + 16;
   L.lbo_h = (kp / 8) * 128 + 16;                   // one-hot operand: chunk of 16 rows, then cluster * 16, then row % 16
   L.h_bytes = (8 * L.lbo_h + 127) & ~127;
-  L.tile_bytes = ns * kTileRows * 128;
+  L.tile_bytes = ns * kTileRows * 128 + hs * kTileRows * 64;
   L.acols = (d + 8 + 15) & ~15;
   L.tstride = kp <= 32 ? 32 : 64;
   L.gstride = L.acols + L.tstride;
   L.rcol0 = groups * L.gstride;
-  int tc = 32; while (tc < L.rcol0 + (dist ? 0 : ns * kp)) tc *= 2;
+  int tc = 32; while (tc < L.rcol0 + (dist ? 0 : (ns + hs) * kp)) tc *= 2;
   L.tcols = tc;
   int o = 0;
   L.x_off = o; o += stages * L.tile_bytes;         // 1024-byte aligned (swizzle atoms)
@@ -95,7 +95,7 @@ __host__ __device__ constexpr inline int wl_stages(int d, int kp, int g, int hal
   const int budget = 227 * 1024 - 1024;             // the static words are padded to 1 KB (alignment of the dynamic part)
   int st = kWlMaxStages;
   while (st > 0 && wl_plan(d, kp, g, st, halves, dist).total > budget) --st;
-  const int comb = dist ? 0 : (d / 16) * kp * 128 * 4;   // s32 accumulators parked in the idle ring for the final combine
+  const int comb = dist ? 0 : ((d + 15) / 16) * kp * 128 * 4;   // s32 accumulators parked in the idle ring for the final combine
   if (st < g + 2 || (st - g) * z.tile_bytes < 40 * 1024 || st * z.tile_bytes < comb) return 0;
   if (g == 1 && halves == 1 && d <= 32) return 0;   // a single group only where nothing else fits
   return st;
@@ -137,11 +137,16 @@ __device__ __forceinline__ void wl_tmem_wait_st() { asm volatile("tcgen05.wait::
 // Thread = row throughout: a thread reads its row through the swizzle (eight consecutive rows hit eight different 16-byte columns),
 // writes the tf32 values into its lane of the group's tensor-memory operand (the tensor core takes A from TMEM: no shared-memory
 // copy of the operand at all), keeps |x - mu|^2 in a register, and overwrites the row in place with its fixed-point form.
-template <int KP, int NS, int GFIX, int H = 1, int DIST = 0>
-__global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const LloydParams p, const __grid_constant__ CUtensorMap tmap, RangeRec* rec,
+template <int KP, int NS, int GFIX, int H = 1, int DIST = 0, int HS = 0>
+__global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const LloydParams p, const __grid_constant__ CUtensorMap tmap,
+                                                                 const __grid_constant__ CUtensorMap tmap_h, RangeRec* rec,
                                                                  unsigned long long* prof_buf, int flags) {
   if (p.skip != nullptr && *p.skip != 0) return;
-  constexpr int DP = 16 * NS, ND = 2 * NS, G = GFIX, S = wl_stages(DP, KP, GFIX, H, DIST);   // DP: features padded to whole slabs
+  // DP: features padded to whole slabs -- NS slabs of 16 and, with HS, a trailing half slab of 8 (64-byte rows, SWIZZLE_64B boxes from
+  // the second tensor map; its limb product is an M = 64 instruction whose result row m sits in TMEM lane m % 16 + 32 (m / 16))
+  constexpr int DP = 16 * NS + 8 * HS, ND = DP / 8, G = GFIX, S = wl_stages(DP, KP, GFIX, H, DIST);
+  static_assert(HS == 0 || (H == 1 && NS <= 2), "half slab: one thread per row, d <= 40");
+  constexpr uint32_t HSLAB_OFF = NS * kTileRows * 128u;   // the half slab sits behind the full slabs of a stage
   constexpr WlPlan L = wl_plan(DP, KP, GFIX, S, H, DIST);
   static_assert(H == 1 || H == 2, "one or two threads per row");
   static_assert(DIST == 0 || H == 1, "the distance-returning variant keeps a row in one thread");
@@ -269,7 +274,7 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
     // the limb sums start at zero (every product below accumulates; the four warps of a group issue theirs independently)
     const uint32_t zv[8] = {0u, 0u, 0u, 0u, 0u, 0u, 0u, 0u};
 #pragma unroll 1
-    if (DIST == 0 && grp == 0 && hh == 0) for (int c0 = 0; c0 < NS * KP; c0 += 8) wl_tmem_st8(tmem + tlane + (uint32_t)L.rcol0 + (uint32_t)c0, zv);
+    if (DIST == 0 && grp == 0 && hh == 0) for (int c0 = 0; c0 < (NS + HS) * KP; c0 += 8) wl_tmem_st8(tmem + tlane + (uint32_t)L.rcol0 + (uint32_t)c0, zv);
     wl_tmem_wait_st();
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
   }
@@ -288,7 +293,7 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
   auto tma_load = [&](int i, uint32_t xs_q, uint32_t bar, uint32_t seqa) {
     const int row0 = (int)(((int64_t)blockIdx.x + (int64_t)i * gridDim.x) * kTileRows) + 32 * q;
     // one elected lane, inside the asm: the C++ control flow stays convergent and the operands stay in uniform registers
-    if constexpr (NS == 1) {
+    if constexpr (NS == 1 && HS == 0) {
       asm volatile(
           "{\n.reg .pred pe;\nelect.sync _|pe, 0xffffffff;\n"
           "@pe st.shared.u32 [%0], %1;\n"
@@ -301,8 +306,14 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
           "{\n.reg .pred pe;\nelect.sync _|pe, 0xffffffff;\n"
           "@pe st.shared.u32 [%0], %1;\n"
           "@pe mbarrier.arrive.expect_tx.shared::cta.b64 _, [%2], %3;\n}\n"
-          ::"r"(seqa), "r"((uint32_t)i), "r"(bar), "r"((uint32_t)(sl_hi - sl_lo) * 4096u)
+          ::"r"(seqa), "r"((uint32_t)i), "r"(bar), "r"((uint32_t)(sl_hi - sl_lo) * 4096u + (uint32_t)HS * 2048u)
           : "memory");
+      if constexpr (HS != 0)
+        asm volatile(
+            "{\n.reg .pred pe;\nelect.sync _|pe, 0xffffffff;\n"
+            "@pe cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];\n}\n"
+            ::"r"(xs_q - (uint32_t)q * 4096u + HSLAB_OFF + (uint32_t)q * 2048u), "l"(&tmap_h), "r"(16 * NS), "r"(row0), "r"(bar)
+            : "memory");
 #pragma unroll
       for (int sl = 0; sl < NS; ++sl)
         if (sl >= sl_lo && sl < sl_hi)
@@ -343,20 +354,18 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
   float2* mu2_s = reinterpret_cast<float2*>(smem + L.mu_off);                     // overlays mu_s once every thread has read it
   uint64_t mu_r[NS == 1 ? 8 : 1];
   {
-    float2 t[8 * NS > 8 ? 1 : 8];
+    float2 t[NS == 1 ? 8 : 1];
     if (NS == 1) {
 #pragma unroll
       for (int c = 0; c < 8; ++c) t[c] = make_float2((float)mu_s[2 * c], (float)mu_s[2 * c + 1]);
 #pragma unroll
       for (int c = 0; c < 8; ++c) asm("mov.b64 %0, {%1,%2};" : "=l"(mu_r[c]) : "f"(t[c].x), "f"(t[c].y));
-    } else {
-      float2 mine = make_float2(0.f, 0.f);
-      if (tid < DP / 2) mine = make_float2((float)mu_s[2 * tid], (float)mu_s[2 * tid + 1]);
-      __syncthreads();
-      if (tid < DP / 2) mu2_s[tid] = mine;
-      __syncthreads();
-      mu_r[0] = 0;
-    }
+    } else mu_r[0] = 0;
+    float2 mine = make_float2(0.f, 0.f);
+    if (tid < DP / 2) mine = make_float2((float)mu_s[2 * tid], (float)mu_s[2 * tid + 1]);
+    __syncthreads();
+    if (tid < DP / 2) mu2_s[tid] = mine;                     // the table (used beyond the first slab) overlays mu_s
+    __syncthreads();
   }
   const uint32_t a_mu2 = sb + L.mu_off, a_mg = sb + L.mg_off;
 
@@ -426,6 +435,33 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
         if constexpr (HOIST) { m0 = mg8[HOIST ? 2 * c : 0]; m1 = mg8[HOIST ? 2 * c + 1 : 0]; }
         else lds_v2f64(a_mg + (uint32_t)(16 * sl + 2 * c) * 8u, m0, m1);
         sts_v2f64(xr + (((uint32_t)c << 4) ^ xsw), v[2 * c] + m0, v[2 * c + 1] + m1);
+      }
+    }
+    if constexpr (HS != 0) {
+      // the trailing 8 features: 64-byte rows, 16-byte column c at c ^ ((row >> 1) & 3)
+      const uint32_t xr = xs - (uint32_t)q * 4096u + HSLAB_OFF + (uint32_t)q * 2048u + (uint32_t)lane * 64u;
+      const uint32_t hsw = (uint32_t)((lane >> 1) & 3) << 4;
+      double v[8];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) lds_v2f64(xr + (((uint32_t)c << 4) ^ hsw), v[2 * c], v[2 * c + 1]);
+      uint32_t tv[8];
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        uint64_t mu01, vv, rr;
+        asm volatile("ld.shared.b64 %0, [%1];" : "=l"(mu01) : "r"(a_mu2 + (uint32_t)(8 * NS + c) * 8u));
+        asm("mov.b64 %0, {%1,%2};" : "=l"(vv) : "f"((float)v[2 * c]), "f"((float)v[2 * c + 1]));
+        asm("sub.f32x2 %0, %1, %2;" : "=l"(rr) : "l"(vv), "l"(mu01));
+        tv[2 * c] = (uint32_t)rr + 0x1000u; tv[2 * c + 1] = (uint32_t)(rr >> 32) + 0x1000u;
+        const float a0 = __uint_as_float(tv[2 * c]), a1 = __uint_as_float(tv[2 * c + 1]);
+        xa = fmaf(a0, a0, xa); xb = fmaf(a1, a1, xb);
+      }
+      wl_tmem_st8(t_A + (uint32_t)(16 * NS), tv);
+      if constexpr (DIST == 0)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        double m0, m1;
+        lds_v2f64(a_mg + (uint32_t)(16 * NS + 2 * c) * 8u, m0, m1);
+        sts_v2f64(xr + (((uint32_t)c << 4) ^ hsw), v[2 * c] + m0, v[2 * c + 1] + m1);
       }
     }
     float xn2 = xa + xb;
@@ -591,6 +627,18 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
 #pragma unroll
         for (int f = 0; f < 16; ++f) { sc = fma(xv[f], cv[f], sc); xx = fma(xv[f], xv[f], xx); }
       }
+      if constexpr (HS != 0) {
+        const uint32_t xr = xs - (uint32_t)q * 4096u + HSLAB_OFF + (uint32_t)q * 2048u + (uint32_t)lane * 64u;
+        const uint32_t hsw = (uint32_t)((lane >> 1) & 3) << 4;
+        double xv[8], cv[8];
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          lds_v2f64(xr + (((uint32_t)c << 4) ^ hsw), xv[2 * c], xv[2 * c + 1]);
+          lds_v2f64(crow + (uint32_t)(16 * NS + 2 * c) * 8u, cv[2 * c], cv[2 * c + 1]);
+        }
+#pragma unroll
+        for (int f = 0; f < 8; ++f) { sc = fma(xv[f], cv[f], sc); xx = fma(xv[f], xv[f], xx); }
+      }
       const double dist = fmax(fma(-2.0, sc + cn_s[lab], xx), 0.0);
       if (valid) {
         const int64_t r = ((int64_t)blockIdx.x + (int64_t)i * gridDim.x) * kTileRows + row;
@@ -638,6 +686,13 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
         const uint64_t da = wl_desc(xs + (uint32_t)sl * SLAB, 16u, 1024u, 2u);
         asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n}\n" ::"r"(rcol + (uint32_t)(sl * KP)),
                      "l"(da), "l"(dh), "r"(idesc2), "r"(1u)
+                     : "memory");
+      }
+      if constexpr (HS != 0) {
+        const uint64_t da = wl_desc(xs - (uint32_t)q * 4096u + HSLAB_OFF + (uint32_t)q * 2048u, 16u, 512u, 4u);   // SWIZZLE_64B, 8 rows x 64 bytes per atom
+        const uint32_t idesc2h = (2u << 4) | (1u << 15) | ((uint32_t)(KP >> 3) << 17) | ((uint32_t)(64 >> 4) << 24);
+        asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n}\n" ::"r"(rcol + (uint32_t)(NS * KP)),
+                     "l"(da), "l"(dh), "r"(idesc2h), "r"(1u)
                      : "memory");
       }
       asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar_r) : "memory");
@@ -688,7 +743,7 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
   int32_t* acc_s = reinterpret_cast<int32_t*>(smem + L.x_off);
   if (grp == 0 && hh == 0) {
 #pragma unroll 1
-    for (int sl = 0; sl < NS; ++sl)
+    for (int sl = 0; sl < NS + HS; ++sl)
 #pragma unroll 1
       for (int c0 = 0; c0 < KP; c0 += 16) {
         uint32_t v[16];
@@ -702,7 +757,9 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
   __syncthreads();
   if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(L.tcols) : "memory");
   for (int idx = tid; idx < k * d; idx += nthreads) {
-    const int j = idx / d, f = idx - j * d, sl = f >> 4, b0 = 8 * (f & 15);
+    const int j = idx / d, f = idx - j * d, sl = f >> 4;
+    int b0 = 8 * (f & 15);
+    if (HS != 0 && sl == NS) b0 = (b0 & 15) + 32 * (b0 >> 4);   // M = 64 product: result row m in lane m % 16 + 32 (m / 16)
     __int128 tot = 0;
     const int32_t* a = acc_s + (size_t)(sl * KP + j) * 128 + b0;
 #pragma unroll

@@ -225,12 +225,99 @@ static int run4(int rounds) {
   return bad != 0;
 }
 
+// M = 64 (one 8-feature slab: 64 bytes per row), SWIZZLE_64B: byte (row k, byte m) at k*64 + ((m/16) ^ ((k>>1)&3))*16 + m%16.
+// Prints where each of the 64 result rows lands in tensor memory (lane of which warp).
+template <int N>
+__global__ void __launch_bounds__(128) k_test64(const uint8_t* __restrict__ A, const uint8_t* __restrict__ B, int32_t* __restrict__ D) {
+  extern __shared__ __align__(1024) unsigned char smem[];
+  __shared__ uint64_t mbar;
+  __shared__ uint32_t tmem_base_s;
+  unsigned char* sA = smem;                       // 128 rows x 64 bytes
+  unsigned char* sB = smem + K * 64;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const uint32_t LBO_B = (N / 8) * 128 + 16, SBO_B = 128;
+  for (int i = tid; i < K * 64; i += 128) { const int k = i / 64, m = i % 64; sA[k * 64 + (((m / 16) ^ ((k >> 1) & 3)) * 16) + (m % 16)] = A[k * 64 + m]; }
+  for (int i = tid; i < N * K; i += 128) { const int n = i / K, k = i % K; sB[(k / 16) * LBO_B + n * 16 + (k % 16)] = B[n * K + k]; }
+  if (tid == 0) { asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&mbar))); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 64;" ::"r"(smem_u32(&tmem_base_s)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem = tmem_base_s;
+  for (int c0 = 0; c0 < N; c0 += 8)
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1};" ::"r"(tmem + ((uint32_t)(32 * warp) << 16) + (uint32_t)c0), "r"(0x7fffffffu) : "memory");
+  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  if (tid == 0) {
+    const uint32_t idesc = (2u << 4) | (1u << 15) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(64 >> 4) << 24);
+    for (int ks = 0; ks < K / 32; ++ks) {
+      const uint64_t da = make_desc(smem_u32(sA) + ks * 2048, 16, 512, 4);
+      const uint64_t db = make_desc(smem_u32(sB) + 2 * ks * LBO_B, LBO_B, SBO_B, 0);
+      asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, p;\n}\n" ::"r"(tmem), "l"(da), "l"(db), "r"(idesc), "r"(ks > 0 ? 1u : 0u) : "memory");
+    }
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&mbar)) : "memory");
+  }
+  { uint32_t ok = 0; while (!ok) asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n" : "=r"(ok) : "r"(smem_u32(&mbar)), "r"(0u) : "memory"); }
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  for (int c0 = 0; c0 < N; c0 += 16) {
+    uint32_t v[16];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]),
+                   "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                 : "r"(tmem + ((uint32_t)(32 * warp) << 16) + (uint32_t)c0));
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+    for (int c = 0; c < 16; ++c) D[tid * N + c0 + c] = (int32_t)v[c];
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 64;" ::"r"(tmem) : "memory");
+}
+
+template <int N>
+static int run64() {
+  std::vector<uint8_t> hA(K * 64), hB(N * K);
+  srand(21);
+  for (auto& v : hA) v = (uint8_t)(rand() & 255);
+  for (int n = 0; n < N; ++n) for (int k = 0; k < K; ++k) hB[n * K + k] = (uint8_t)((rand() % N) == n ? 1 : 0);
+  uint8_t *dA, *dB; int32_t* dD;
+  CK(cudaMalloc(&dA, hA.size())); CK(cudaMalloc(&dB, hB.size())); CK(cudaMalloc(&dD, 128 * N * 4));
+  CK(cudaMemcpy(dA, hA.data(), hA.size(), cudaMemcpyHostToDevice)); CK(cudaMemcpy(dB, hB.data(), hB.size(), cudaMemcpyHostToDevice));
+  const int smem = K * 64 + 8 * ((N / 8) * 128 + 16) + 1024;
+  CK(cudaFuncSetAttribute(k_test64<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  k_test64<N><<<1, 128, smem>>>(dA, dB, dD);
+  cudaError_t e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) { printf("M=64 N=%d: launch error %s\n", N, cudaGetErrorString(e)); return 1; }
+  std::vector<int32_t> hD(128 * N);
+  CK(cudaMemcpy(hD.data(), dD, 128 * N * 4, cudaMemcpyDeviceToHost));
+  std::vector<long> ref(64 * N);
+  for (int m = 0; m < 64; ++m) for (int n = 0; n < N; ++n) { long r = 0; for (int k = 0; k < K; ++k) r += (long)hA[k * 64 + m] * hB[n * K + k]; ref[m * N + n] = r; }
+  // which lane holds result row m?
+  int found = 0; printf("M=64 N=%d: row -> lane:", N);
+  for (int m = 0; m < 64; ++m) {
+    int where = -1;
+    for (int l = 0; l < 128 && where < 0; ++l) { bool eq = true; for (int n = 0; n < N; ++n) if (hD[l * N + n] != ref[m * N + n]) { eq = false; break; } if (eq) where = l; }
+    if (where >= 0) ++found;
+    if (m < 20 || m % 16 == 0) printf(" %d->%d", m, where);
+  }
+  printf("  (%d of 64 rows found)\n", found);
+  cudaFree(dA); cudaFree(dB); cudaFree(dD);
+  return found != 64;
+}
+
 int main() {
   int rc = 0;
   rc |= run<16>(0);        // swizzled A, LBO field 16
   rc |= run<16>(1);        // swizzled A, LBO field 128 (must not matter: one atom along M)
   rc |= run<64>(0);
   rc |= run<32>(0);
+  rc |= run64<16>();
+  rc |= run64<32>();
   rc |= run4<16>(2000);
   rc |= run4<64>(500);
   return rc;

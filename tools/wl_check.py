@@ -127,11 +127,19 @@ if __name__ == "__main__":
         np, torch, N, O = _mods()
         for n, d, k in ([(20_000_000, 64, 64)] if "64" in sys.argv else [(20_000_000, 16, 16), (10_000_000, 32, 16), (20_000_000, 16, 32)]):
             g = torch.Generator(device="cuda"); g.manual_seed(1)
-            prof = torch.randn(k, d, dtype=torch.float64, device="cuda", generator=g) * 2
-            X = prof[torch.randint(0, k, (n,), device="cuda", generator=g)] + torch.randn(n, d, dtype=torch.float64, device="cuda", generator=g)
-            C = prof + 0.1
             partial = torch.empty(k * d + k + 1, dtype=torch.float64, device="cuda"); scratch = N.new_scratch(d, k, "cuda")
             xs = torch.zeros(1, dtype=torch.float64, device="cuda")
+            if "hospital" in sys.argv:      # bench.py's table and centres: first k rows, then 10 Lloyd steps
+                import hkm_b200
+                from hkm_b200 import datagen
+                X = datagen.hospital_matrix_device(n, d, k, 20250331, torch.device("cuda"))
+                C = X[:k].clone(); st = N.new_state("cuda")
+                for it in range(10):
+                    N.lloyd_step(X, C, partial, -1.0, st, scratch, xnorm2_sum=xs, xnorm2_mode=1 if it == 0 else 2)
+            else:
+                prof = torch.randn(k, d, dtype=torch.float64, device="cuda", generator=g) * 2
+                X = prof[torch.randint(0, k, (n,), device="cuda", generator=g)] + torch.randn(n, d, dtype=torch.float64, device="cuda", generator=g)
+                C = prof + 0.1
             N.assign_reduce(X, C, partial, scratch=scratch, xnorm2_sum=xs, xnorm2_mode=1)
             buf = torch.zeros(24 * 8, dtype=torch.int64, device="cuda")
             fn = N.load().hkm_debug_wl_profile; fn.argtypes = [ctypes.c_void_p]; fn.restype = None
@@ -143,7 +151,7 @@ if __name__ == "__main__":
             print(json.dumps(dict(n=n, d=d, k=k, tiles_cta0=tiles, clk_per_tile=round(float(b[0, 0]) / tiles, 1))))
             for w in range(24):
                 if b[w, 0]:
-                    print(f"  warp {w:2d} total/tile {b[w, 0] / tiles:8.1f}  wait_tma {b[w, 1] / tiles:8.1f}  wait_mma {b[w, 2] / tiles:8.1f}  refine {b[w, 3] / tiles:7.1f}")
+                    print(f"  warp {w:2d} total/tile {b[w, 0] / tiles:8.1f}  wait_tma {b[w, 1] / tiles:8.1f}  wait_mma {b[w, 2] / tiles:8.1f}  refine {b[w, 3] / tiles:7.1f}  refined rows/tile {b[w, 5] / tiles:6.3f}")
             del X
         sys.exit(0)
     if cmd == "fbench":
@@ -154,6 +162,12 @@ if __name__ == "__main__":
         sys.exit(0)
     if cmd == "bench64":
         bench([(20_000_000, 64, 64), (5_000_000, 64, 64), (5_000_000, 64, 16), (5_000_000, 64, 32), (5_000_000, 48, 24), (5_000_000, 48, 48), (5_000_000, 40, 40)])
+        sys.exit(0)
+    if cmd == "hbench":      # rows of 16 ns + 8 features: half slab against padding to whole slabs
+        np, torch, N, O = _mods()
+        for f in (0, 1):
+            N.load().hkm_debug_wl_nohalf(ctypes.c_int(f)); print("nohalf", f, flush=True)
+            bench([(5_000_000, 24, 12), (5_000_000, 24, 16), (5_000_000, 24, 32), (5_000_000, 24, 64), (5_000_000, 20, 24), (5_000_000, 40, 40), (20_000_000, 24, 16)])
         sys.exit(0)
     if cmd == "gbench":
         np, torch, N, O = _mods()
