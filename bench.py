@@ -271,7 +271,7 @@ def main():
     def limb_shape(d_, k_):
         """REUSE passes of this shape run the limb-reduction variant (the dispatch rule of hkm_lloyd_wl.cu)."""
         kp = ((k_ + 15) // 16) * 16
-        return 8 < k_ <= 64 and d_ % 2 == 0 and d_ <= 64 and not (kp == 16 and (16 < d_ <= 24 or d_ > 32))
+        return 8 < k_ <= 64 and d_ % 2 == 0 and d_ <= 64 and not (kp == 16 and d_ > 32)
 
     def kernel_name(d_, k_):
         if limb_shape(d_, k_):
