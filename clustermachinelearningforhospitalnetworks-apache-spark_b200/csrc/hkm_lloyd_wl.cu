@@ -9,6 +9,7 @@ static unsigned long long* g_wl_prof = nullptr;
 static int g_wl_off = 0;       // developer switch: 1 = never use this variant
 static int g_wl_flags = -1;    // developer switch: bit 0 = close the previous tile at the top of the iteration when its product is done
 static int g_wl_nohalf = 0;    // developer switch: 1 = pad rows to whole 16-feature slabs (no half slab)
+static int g_wl_pw = 1;        // developer switch: 0 = no loading warp anywhere
 static int g_wl_groups = 0;    // developer switch: group count for d = 16, k <= 16 (4, 5 or 6)
 
 // ---- column range pass: per column the largest magnitude (its exponent) and the mean exponent of the nonzero values; one read of
@@ -128,7 +129,7 @@ static EncodeTiledFn encode_tiled() {
   return fn;
 }
 
-template <int KP, int NS, int GO = 0, int HS = 0>
+template <int KP, int NS, int GO = 0, int HS = 0, int PW = 0>
 static int launch_wl(const LloydParams& p, const CUtensorMap& tmap, const CUtensorMap& tmap_h, RangeRec* rec, cudaStream_t st) {
   constexpr int DPAD = 16 * NS + 8 * HS;
   constexpr int H = (GO > 0 || HS) ? 1 : wl_halves(DPAD, KP);
@@ -136,14 +137,14 @@ static int launch_wl(const LloydParams& p, const CUtensorMap& tmap, const CUtens
   if constexpr (G == 0) { set_error("lloyd_wl: d=%d k=%d does not fit", p.d, p.k); return HKM_ERR_UNSUPPORTED; }
   else {
     constexpr WlPlan L = wl_plan(DPAD, KP, G, wl_stages(DPAD, KP, G, H), H);
-    auto kern = lloyd_wl_kernel<KP, NS, G, H, 0, HS>;
+    auto kern = lloyd_wl_kernel<KP, NS, G, H, 0, HS, PW>;
     static bool attr_done[64];
     int dev = 0; HKM_CUDA_TRY(cudaGetDevice(&dev));
     if (dev >= 64 || !attr_done[dev]) {
       HKM_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
       if (dev < 64) attr_done[dev] = true;
     }
-    kern<<<sm_count(), G * 128 * H, L.total, st>>>(p, tmap, tmap_h, rec, g_wl_prof, g_wl_flags >= 0 ? g_wl_flags : (((NS == 2 && KP == 16) || (NS == 1 && KP == 32)) ? 1 : 0));
+    kern<<<sm_count(), G * 128 * H + 32 * PW, L.total, st>>>(p, tmap, tmap_h, rec, g_wl_prof, g_wl_flags >= 0 ? g_wl_flags : (((NS == 2 && KP == 16) || (NS == 1 && KP == 32)) ? 1 : 0));
     HKM_CUDA_TRY(cudaGetLastError());
     return HKM_OK;
   }
@@ -216,6 +217,11 @@ int launch_lloyd_wl(const LloydParams& p, void* tail, cudaStream_t st) {
 #define HKM_WL_CASE(KPV, NSV) if (kp == KPV && ns == NSV) return launch_wl<KPV, NSV>(p, tmap, tmap, rec, st);
   if (kp == 16 && ns == 1 && g_wl_groups == 4) return launch_wl<16, 1, 4>(p, tmap, tmap, rec, st);
   if (kp == 16 && ns == 1 && g_wl_groups == 5) return launch_wl<16, 1, 5>(p, tmap, tmap, rec, st);
+#define HKM_WLP_CASE(KPV, NSV) if (kp == KPV && ns == NSV) return launch_wl<KPV, NSV, 0, 0, 1>(p, tmap, tmap, rec, st);
+  // the loading warp where it measured faster: 64-feature rows (0.657 -> 0.677 at k = 64, 0.68 -> 0.69 at k = 32) and d = 32 with k <= 16
+  // (0.84 -> 0.91).  With many groups one warp cannot issue the boxes fast enough (d = 16, k <= 16: 0.86 -> 0.61; d = 48: 0.73 -> 0.68).
+  if (g_wl_pw >= 1) { HKM_WLP_CASE(16, 4) HKM_WLP_CASE(32, 4) HKM_WLP_CASE(48, 4) HKM_WLP_CASE(64, 4) HKM_WLP_CASE(16, 2) }
+#undef HKM_WLP_CASE
   HKM_WL_CASE(16, 1) HKM_WL_CASE(32, 1) HKM_WL_CASE(48, 1) HKM_WL_CASE(64, 1)
   HKM_WL_CASE(16, 2) HKM_WL_CASE(32, 2) HKM_WL_CASE(48, 2) HKM_WL_CASE(64, 2)
   HKM_WL_CASE(16, 3) HKM_WL_CASE(32, 3) HKM_WL_CASE(48, 3) HKM_WL_CASE(64, 3)
@@ -229,6 +235,7 @@ int launch_lloyd_wl(const LloydParams& p, void* tail, cudaStream_t st) {
 
 extern "C" __attribute__((visibility("default"))) void hkm_debug_wl_profile(void* buf) { hkm::g_wl_prof = reinterpret_cast<unsigned long long*>(buf); }
 extern "C" __attribute__((visibility("default"))) void hkm_debug_wl_off(int off) { hkm::g_wl_off = off; }
+extern "C" __attribute__((visibility("default"))) void hkm_debug_wl_pw(int f) { hkm::g_wl_pw = f; }
 extern "C" __attribute__((visibility("default"))) void hkm_debug_wl_groups(int g) { hkm::g_wl_groups = g; }
 extern "C" __attribute__((visibility("default"))) void hkm_debug_wl_flags(int f) { hkm::g_wl_flags = f; }
 extern "C" __attribute__((visibility("default"))) void hkm_debug_wl_nohalf(int f) { hkm::g_wl_nohalf = f; }

@@ -45,7 +45,7 @@ struct RangeRec {
 
 struct WlPlan {
   int groups, stages, kchunks, lbo_b, lbo_h, h_bytes, tile_bytes, tcols, acols, tstride, gstride, rcol0;
-  int x_off, b_off, h_off, ex_off, ct_off, ct_pitch, cn_off, mu_off, mg_off, cnt_off, red_off, bar_off, seq_off, tmem_off, cs_off, total;
+  int x_off, b_off, h_off, ex_off, ct_off, ct_pitch, cn_off, mu_off, mg_off, cnt_off, red_off, bar_off, seq_off, rel_off, tmem_off, cs_off, total;
 };
 
 // Tensor memory, per group: [tf32 operand: d data columns + 8 constant columns][scores: k_pad], then behind all groups the s32 limb
@@ -82,6 +82,7 @@ __host__ __device__ constexpr inline WlPlan wl_plan(int d, int kp, int groups, i
   const int nst = stages > 0 ? stages : 1;
   L.bar_off = o; o += (4 * halves * nst + kWlMaxGroups + kWlMaxWarps) * 8;     // full[stage][quarter][half], scores[group], sums[group][quarter]
   L.seq_off = o; o += 4 * halves * nst * 4; o = (o + 15) & ~15;
+  L.rel_off = o; o += kWlMaxWarps * 4;                // tiles closed per warp (read by the loading warp)
   L.tmem_off = o; o += 16;
   if (kp * d * 8 <= 8 * 1024) { L.cs_off = o; o += kp * d * 8; }
   L.total = o;
@@ -137,8 +138,8 @@ __device__ __forceinline__ void wl_tmem_wait_st() { asm volatile("tcgen05.wait::
 // Thread = row throughout: a thread reads its row through the swizzle (eight consecutive rows hit eight different 16-byte columns),
 // writes the tf32 values into its lane of the group's tensor-memory operand (the tensor core takes A from TMEM: no shared-memory
 // copy of the operand at all), keeps |x - mu|^2 in a register, and overwrites the row in place with its fixed-point form.
-template <int KP, int NS, int GFIX, int H = 1, int DIST = 0, int HS = 0>
-__global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const LloydParams p, const __grid_constant__ CUtensorMap tmap,
+template <int KP, int NS, int GFIX, int H = 1, int DIST = 0, int HS = 0, int PW = 0>
+__global__ void __launch_bounds__(GFIX * 128 * H + 32 * PW, 1) lloyd_wl_kernel(const LloydParams p, const __grid_constant__ CUtensorMap tmap,
                                                                  const __grid_constant__ CUtensorMap tmap_h, RangeRec* rec,
                                                                  unsigned long long* prof_buf, int flags) {
   if (p.skip != nullptr && *p.skip != 0) return;
@@ -155,9 +156,14 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
   constexpr int NW = (KP + 31) / 32;
   constexpr int IDXBITS = 6;
   constexpr uint32_t IDXMASK = (1u << IDXBITS) - 1u;
-  constexpr int nthreads = G * 128 * H, nwarps = G * 4 * H;
+  // PW = 1: one more warp that issues every refill of the ring.  A bulk tensor copy holds the issuing thread for 40-70 clocks per
+  // 4 KB box while the copy engine is busy; with the sixteen boxes of a 64-feature tile requested at the same moment, the computing
+  // warps lost 500-1000 clocks per tile there.
+  static_assert(PW == 0 || (DIST == 0 && HS == 0), "the loading warp is for the reducing variant with whole slabs");
+  constexpr int nthreads = G * 128 * H + 32 * PW, nwarps = G * 4 * H;
   constexpr int NCH = KP / 16;                          // score columns in chunks of 16
   constexpr bool HOIST = nwarps <= 8;
+  constexpr bool XPROF = nwarps <= 8;                  // the finer clock counters of the profile hook: only where registers are plentiful
   constexpr uint32_t LBO_B = L.lbo_b, LBO_H = L.lbo_h, tile_bytes = L.tile_bytes;
   constexpr uint32_t SLAB = kTileRows * 128;          // bytes of one 16-feature slab of a tile
   // the record must describe this table and admit it; otherwise the launch behind this one does the pass
@@ -194,7 +200,8 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
   const bool tail_mine = tail_rows > 0 && (int)(full_tiles % gridDim.x) == (int)blockIdx.x;
   const int T = my_tiles + (tail_mine ? 1 : 0);    // the ragged tail is this CTA's last tile (rows past the end arrive as zeros)
   const bool prof = prof_buf != nullptr && blockIdx.x == 0;
-  long long pw0 = 0, pw1 = 0, pw2 = 0, pcnt = 0;
+  const bool compute = warp < nwarps;                 // the loading warp (PW) takes part in the set-up and in the combine only
+  long long pw0 = 0, pw1 = 0, pw2 = 0, pcnt = 0, pw3 = 0, pw4 = 0, pw5 = 0, pw6 = 0, pw7 = 0, pw8 = 0;
 
   // ------------------------------------------------------------------ one-time set-up
   if (tid == 0) {
@@ -211,6 +218,7 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
   // zero: B and the one-hot operands (one contiguous range), counters
   for (int i = tid; i < ((DIST ? L.ct_off : L.cn_off) - L.b_off) / 16; i += nthreads) reinterpret_cast<uint4*>(smem + L.b_off)[i] = make_uint4(0, 0, 0, 0);
   for (int i = tid; i < KP; i += nthreads) cnt_s[i] = 0u;
+  for (int i = tid; i < kWlMaxWarps; i += nthreads) reinterpret_cast<uint32_t*>(smem + L.rel_off)[i] = 0u;
   for (int i = tid; i < 4 * H * S; i += nthreads) reinterpret_cast<uint32_t*>(smem + L.seq_off)[i] = (uint32_t)(i / (4 * H));
   if (L.cs_off != 0) for (int i = tid; i < k * d; i += nthreads) reinterpret_cast<double*>(smem + L.cs_off)[i] = p.C[i];
   if constexpr (DIST != 0) {
@@ -266,7 +274,7 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
   const uint32_t tlane = ((uint32_t)(32 * q)) << 16;
   const uint32_t t_A = tmem + tlane + (uint32_t)grp * (uint32_t)L.gstride;       // this lane's row of the group's tf32 operand
   const uint32_t t_D = t_A + (uint32_t)L.acols;                                  // ... and of its score accumulator
-  {
+  if (compute) {
     // the eight constant columns behind the data columns: (1, 1, 1, 0, ...) against the hi/mid/lo split of -0.5|c - mu|^2
     const uint32_t one = __float_as_uint(1.0f);
     const uint32_t cv[8] = {one, one, one, 0u, 0u, 0u, 0u, 0u};
@@ -324,7 +332,7 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
             : "memory");
     }
   };
-  for (int i = grp; i < S && i < T; i += G)
+  if (compute) for (int i = grp; i < S && i < T; i += G)
     tma_load(i, a_x + (uint32_t)i * tile_bytes + (uint32_t)q * 4096u, b_full + 8u * (uint32_t)((4 * i + q) * H + hh), a_seq + 4u * (uint32_t)((4 * i + q) * H + hh));
 
   const int row = 32 * q + lane;                                                  // tile row of this thread = TMEM lane
@@ -374,8 +382,59 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
   uint32_t hb_prev = 0u, xs_prev = 0u, bar_f_prev = 0u, seqa_prev = 0u;
   bool pend = false;                                  // the previous tile's limb product has not been waited for yet
   const bool early = (flags & 1) != 0;
-  for (int i = grp; i < T; i += G) {
+  // a closed tile's quarter of the ring is refilled with tile `nxt`: by this warp, or (PW) by the loading warp, which is told through
+  // this warp's counter of closed tiles
+  uint32_t nclosed = 0;
+  const uint32_t a_rel = sb + L.rel_off;
+  auto refill = [&](int nxt, uint32_t xs_q, uint32_t bar, uint32_t seqa) {
+    if constexpr (PW != 0) {
+      ++nclosed;
+      if (lane == 0) asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(a_rel + 4u * (uint32_t)warp), "r"(nclosed) : "memory");
+    } else {
+      if (nxt < T) tma_load(nxt, xs_q, bar, seqa);
+    }
+  };
+  if constexpr (PW != 0) {
+    if (!compute) {
+      // ---- the loading warp: lane w serves computing warp w.  That warp's m-th closed tile j = group + m G frees its quarter of
+      // stage j % S, which takes tile j + S.  The counters only grow, so a lane that falls behind misses nothing.
+      const int w = lane;
+      const int g_w = w / (4 * H), q_w = w & 3, hh_w = (w >> 2) & (H - 1);
+      const int lo_w = hh_w ? (NS + 1) / 2 : 0, hi_w = (H == 1 || hh_w) ? NS : (NS + 1) / 2;
+      int m = 0;
+      bool fin = w >= nwarps;
+      while (true) {
+        bool issued = false;
+        if (!fin) {
+          const int j = g_w + m * G;
+          if (j + S >= T) fin = true;
+          else {
+            uint32_t have;
+            asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(have) : "r"(a_rel + 4u * (uint32_t)w) : "memory");
+            if (have > (uint32_t)m) {
+              const int t = j + S, st = j % S;
+              const int row0 = (int)(((int64_t)blockIdx.x + (int64_t)t * gridDim.x) * kTileRows) + 32 * q_w;
+              const uint32_t xs_q = a_x + (uint32_t)st * tile_bytes + (uint32_t)q_w * 4096u;
+              const uint32_t bar = b_full + 8u * (uint32_t)((4 * st + q_w) * H + hh_w), seqa = a_seq + 4u * (uint32_t)((4 * st + q_w) * H + hh_w);
+              asm volatile("st.shared.u32 [%0], %1;\n"
+                           "mbarrier.arrive.expect_tx.shared::cta.b64 _, [%2], %3;\n"
+                           ::"r"(seqa), "r"((uint32_t)t), "r"(bar), "r"((uint32_t)(hi_w - lo_w) * 4096u) : "memory");
+              for (int sl = lo_w; sl < hi_w; ++sl)
+                asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                             ::"r"(xs_q + (uint32_t)sl * SLAB), "l"(&tmap), "r"(16 * sl), "r"(row0), "r"(bar) : "memory");
+              ++m; issued = true;
+            }
+          }
+        }
+        if (__all_sync(0xffffffffu, fin)) break;
+        if (!__any_sync(0xffffffffu, issued)) __nanosleep(32);
+      }
+    }
+  }
+  const int Tc = compute ? T : 0;                      // tiles this warp computes on
+  for (int i = grp; i < Tc; i += G) {
     const int rows_valid = i < my_tiles ? kTileRows : tail_rows;
+    const long long tt0 = (XPROF && prof) ? clock64() : 0;
     const uint32_t xs = a_x + (uint32_t)s * tile_bytes + (uint32_t)q * 4096u;       // this warp's 32 rows of slab 0
     const uint32_t bar_f = b_full + 8u * (uint32_t)((4 * s + q) * H + hh), seqa = a_seq + 4u * (uint32_t)((4 * s + q) * H + hh);
     if (pend && early && mbar_probe_a(bar_r, tph ^ 1u)) {
@@ -383,7 +442,7 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
       // (otherwise after the next product has been issued, which hides the wait)
       if (hb_prev != 0u) sts_u8(hb_prev, 0u);
       __syncwarp();
-      if (i - G + S < T) tma_load(i - G + S, xs_prev, bar_f_prev, seqa_prev);
+      refill(i - G + S, xs_prev, bar_f_prev, seqa_prev);
       pend = false;
     }
     {
@@ -395,7 +454,9 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
         asm volatile("ld.volatile.shared.u32 %0, [%1];" : "=r"(have) : "r"(seqa) : "memory");
       }
     }
+    if (XPROF && prof) pw6 += clock64() - tt0;
     tp_wait_p(bar_f, ph, 3, prof, pw0);
+    const long long tc0 = (XPROF && prof) ? clock64() : 0;
     // ---- this thread's row: tf32 operand -> TMEM, |x - mu|^2, fixed point in place
     float xa = 0.f, xb = 0.f;
 #pragma unroll
@@ -468,7 +529,10 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
     wl_tmem_wait_st();
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");       // fixed-point rows -> visible to the tensor core (second product)
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    const long long tc1 = (XPROF && prof) ? clock64() : 0;
     named_bar_sync(1 + grp, 128 * H);
+    const long long tm0 = (XPROF && prof) ? clock64() : 0;
+    if (XPROF && prof) { pw3 += tc1 - tc0; pw4 += tm0 - tc1; }
     if (q == 0 && hh == 0 && lane == 0) {
       asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 #pragma unroll
@@ -488,11 +552,13 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
       tp_wait_p(bar_r, tph ^ 1u, 8, prof, pw1);
       if (hb_prev != 0u) sts_u8(hb_prev, 0u);
       __syncwarp();
-      if (i - G + S < T) tma_load(i - G + S, xs_prev, bar_f_prev, seqa_prev);
+      refill(i - G + S, xs_prev, bar_f_prev, seqa_prev);
       pend = false;
     }
+    if (XPROF && prof) pw7 += clock64() - tm0;
     tp_wait_p(bar_t, tph, 5, prof, pw1);
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const long long ts0 = (XPROF && prof) ? clock64() : 0;
     // ---- sweep 1: top two of the packed scores (tournament per 16 columns)
     float m1 = 0.f, m2 = 0.f;
 #pragma unroll
@@ -535,6 +601,8 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
       m1 = fmaxf(m1, o1);
       xn2 += o3;
     }
+    const long long te0 = (XPROF && prof) ? clock64() : 0;
+    if (XPROF && prof) pw5 += te0 - ts0;
     const bool valid = row < rows_valid;
     const float eps = fmaf(kapv, sqrtf(xn2) * 1.001f, etab) + 6e-5f * fabsf(m1);
     const float thr = m1 - 2.0f * eps;
@@ -545,6 +613,12 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
       // sweep 2 + exact re-scoring of the undecided rows (hkm_lloyd_wg.cuh).  The stage holds the fixed-point form by now, so the
       // row's fp64 values come from global memory again (the table was just streamed: an L2 hit more often than not)
       const long long tr0 = prof ? clock64() : 0;
+      // with registers to spare, the first undecided row's values are requested before the second sweep, each further row's while
+      // its predecessor is scored
+      const double* xg = p.X + (((int64_t)blockIdx.x + (int64_t)i * gridDim.x) * kTileRows + 32 * q) * d + rlane;
+      int srcn = __ffs(ambmask) - 1;
+      double nx0 = 0.0, nx1 = 0.0;
+      if (HOIST && ract) { const double2 xv = __ldg(reinterpret_cast<const double2*>(xg + (size_t)srcn * d)); nx0 = xv.x; nx1 = xv.y; }
       if constexpr (H == 2) named_bar_sync(pair_id, 64);         // the other thread has read this row's sweep slot: the slots are reused below
       uint32_t w[NW];
 #pragma unroll
@@ -558,14 +632,18 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
 #pragma unroll
         for (int c = 0; c < 16; ++c) w[ch >> 1] |= (__uint_as_float(v[c]) >= thr) ? (1u << ((ch & 1) * 16 + c)) : 0u;
       }
-      const double* xg = p.X + (((int64_t)blockIdx.x + (int64_t)i * gridDim.x) * kTileRows + 32 * q) * d + rlane;
       while (ambmask) {
-        const int src = __ffs(ambmask) - 1; ambmask &= ambmask - 1;
+        const int src = HOIST ? srcn : __ffs(ambmask) - 1; ambmask &= ambmask - 1;
         uint32_t cm[NW];
 #pragma unroll
         for (int qq = 0; qq < NW; ++qq) cm[qq] = __shfl_sync(0xffffffffu, w[qq], src);
-        double x0 = 0.0, x1 = 0.0;
-        if (ract) { const double2 xv = __ldg(reinterpret_cast<const double2*>(xg + (size_t)src * d)); x0 = xv.x; x1 = xv.y; }
+        double x0 = nx0, x1 = nx1;
+        if constexpr (HOIST) {
+          if (ambmask) {
+            srcn = __ffs(ambmask) - 1;
+            if (ract) { const double2 xv = __ldg(reinterpret_cast<const double2*>(xg + (size_t)srcn * d)); nx0 = xv.x; nx1 = xv.y; }
+          }
+        } else if (ract) { const double2 xv = __ldg(reinterpret_cast<const double2*>(xg + (size_t)src * d)); x0 = xv.x; x1 = xv.y; }
         double best = -__longlong_as_double(0x7ff0000000000000LL); int bj = -1;
 #pragma unroll
         for (int qq = 0; qq < NW; ++qq) {
@@ -698,6 +776,7 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
       asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar_r) : "memory");
     }
     __syncwarp();
+    if (XPROF && prof) pw8 += clock64() - te0;
     hb_prev = (valid && hh == 0) ? hb : 0u; xs_prev = xs; bar_f_prev = bar_f; seqa_prev = seqa; pend = true;
     s += G; if (s >= S) { s -= S; ph ^= 1u; }
     tph ^= 1u;
@@ -708,7 +787,9 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
   if (prof && lane == 0) {
     unsigned long long* o = prof_buf + warp * 8;
     o[0] = (unsigned long long)(clock64() - pt0); o[1] = (unsigned long long)pw0; o[2] = (unsigned long long)pw1; o[3] = (unsigned long long)pw2;
-    o[4] = 0ull; o[5] = (unsigned long long)pcnt; o[6] = (unsigned long long)T; o[7] = 0ull;
+    o[4] = (unsigned long long)pw3; o[5] = (unsigned long long)pcnt; o[6] = (unsigned long long)T; o[7] = (unsigned long long)pw4;
+    // the first eight warps also report: sweep + exchange; top of the iteration; product issue + close of the previous tile; rest of the iteration
+    if (XPROF && warp < 8) { prof_buf[192 + warp] = (unsigned long long)pw5; prof_buf[200 + 4 * warp] = (unsigned long long)pw6; prof_buf[201 + 4 * warp] = (unsigned long long)pw7; prof_buf[202 + 4 * warp] = (unsigned long long)pw8; }
   }
   if constexpr (DIST != 0) {
     // ===================================================================== distance variant: only the cost is folded
@@ -723,7 +804,7 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
     __shared__ unsigned int s_tk;
     if (tid == 0) {
       double c = 0;
-      for (int wv = 0; wv < nwarps; ++wv) c += red_s[wv];
+      for (int wv = 0; wv < nwarps + PW; ++wv) c += red_s[wv];
       p.cta_partials[blockIdx.x] = c;
       __threadfence();
       s_tk = atomicAdd(p.counter, 1u);
@@ -783,7 +864,7 @@ __global__ void __launch_bounds__(GFIX * 128 * H, 1) lloyd_wl_kernel(const Lloyd
   __syncthreads();
   if (tid == 0) {
     double c = 0;
-    for (int wv = 0; wv < nwarps; ++wv) c += red_s[wv];
+    for (int wv = 0; wv < nwarps + PW; ++wv) c += red_s[wv];
     out[P - 1] = c; out[P] = 0.0;
   }
   // ===================================================================== two-level fold of the per-CTA partials

@@ -14,8 +14,10 @@ def _mods():
 
 def one(n, d, k, kind="blobs"):
     np, torch, N, O = _mods()
+    if os.environ.get("WL_PW"):
+        N.load().hkm_debug_wl_pw(ctypes.c_int(int(os.environ["WL_PW"])))
     rng = np.random.default_rng(n + 31 * d + 977 * k)
-    prof = rng.normal(size=(k, d)) * 1.5
+    prof = rng.normal(size=(k, d)) * (0.2 if kind == "close" else 1.5)     # "close": overlapping clusters, many rows re-scored exactly
     Xh = prof[rng.integers(0, k, size=n)] + rng.normal(size=(n, d))
     if kind == "offset":
         Xh += 300.0
@@ -95,6 +97,7 @@ if __name__ == "__main__":
                  (40000, 16, 40, "blobs"), (45000, 16, 64, "blobs"), (50000, 32, 20, "blobs"), (60000, 32, 64, "blobs"), (129, 32, 17, "blobs"),
                  (30000, 24, 17, "blobs"), (30011, 24, 32, "blobs"), (9000, 12, 20, "blobs"), (33333, 2, 10, "blobs"), (70003, 8, 12, "blobs"), (3000, 30, 33, "blobs"), (4097, 22, 64, "blobs"),
                  (20000, 64, 64, "blobs"), (20000, 64, 16, "blobs"), (6000, 48, 24, "blobs"), (5000, 40, 40, "blobs"), (4000, 62, 64, "blobs"), (65, 64, 64, "blobs"),
+                 (20011, 64, 64, "close"), (20000, 64, 33, "close"), (9000, 64, 17, "close"), (7000, 58, 12, "close"), (30000, 64, 48, "blobs"), (5000, 32, 32, "close"),
                  (70000, 16, 16, "offset"), (70000, 16, 24, "scales"), (50000, 16, 16, "outlier"), (3000000, 16, 16, "blobs")]
         bad = 0
         for n, d, k, kind in cases:
@@ -129,6 +132,7 @@ if __name__ == "__main__":
             g = torch.Generator(device="cuda"); g.manual_seed(1)
             partial = torch.empty(k * d + k + 1, dtype=torch.float64, device="cuda"); scratch = N.new_scratch(d, k, "cuda")
             xs = torch.zeros(1, dtype=torch.float64, device="cuda")
+            N.load().hkm_debug_wl_pw(ctypes.c_int(0 if "nopw" in sys.argv else 1))
             if "hospital" in sys.argv:      # bench.py's table and centres: first k rows, then 10 Lloyd steps
                 import hkm_b200
                 from hkm_b200 import datagen
@@ -141,17 +145,17 @@ if __name__ == "__main__":
                 X = prof[torch.randint(0, k, (n,), device="cuda", generator=g)] + torch.randn(n, d, dtype=torch.float64, device="cuda", generator=g)
                 C = prof + 0.1
             N.assign_reduce(X, C, partial, scratch=scratch, xnorm2_sum=xs, xnorm2_mode=1)
-            buf = torch.zeros(24 * 8, dtype=torch.int64, device="cuda")
+            buf = torch.zeros(24 * 8 + 8 + 32, dtype=torch.int64, device="cuda")
             fn = N.load().hkm_debug_wl_profile; fn.argtypes = [ctypes.c_void_p]; fn.restype = None
             fn(ctypes.c_void_p(buf.data_ptr()))
             for _ in range(3):
                 N.assign_reduce(X, C, partial, scratch=scratch, xnorm2_sum=xs, xnorm2_mode=2)
             torch.cuda.synchronize(); fn(None)
-            b = buf.cpu().numpy().reshape(24, 8); tiles = max(int(b[0, 6]), 1)
+            bx = buf.cpu().numpy(); b = bx[:192].reshape(24, 8); tiles = max(int(b[0, 6]), 1)
             print(json.dumps(dict(n=n, d=d, k=k, tiles_cta0=tiles, clk_per_tile=round(float(b[0, 0]) / tiles, 1))))
             for w in range(24):
                 if b[w, 0]:
-                    print(f"  warp {w:2d} total/tile {b[w, 0] / tiles:8.1f}  wait_tma {b[w, 1] / tiles:8.1f}  wait_mma {b[w, 2] / tiles:8.1f}  refine {b[w, 3] / tiles:7.1f}  refined rows/tile {b[w, 5] / tiles:6.3f}")
+                    print(f"  warp {w:2d} total/tile {b[w, 0] / tiles:8.1f}  wait_tma {b[w, 1] / tiles:8.1f}  wait_mma {b[w, 2] / tiles:8.1f}  refine {b[w, 3] / tiles:7.1f}  refined rows/tile {b[w, 5] / tiles:6.3f}  convert {b[w, 4] / tiles:7.1f}  group_barrier {b[w, 7] / tiles:7.1f}  sweep+exchange {(bx[192 + w] / tiles if w < 8 else -1):7.1f}" + (f"  top {bx[200 + 4 * w] / tiles:7.1f}  issue+close(incl. its wait) {bx[201 + 4 * w] / tiles:7.1f}  tail(incl. refine) {bx[202 + 4 * w] / tiles:7.1f}" if w < 8 else ""))
             del X
         sys.exit(0)
     if cmd == "fbench":
@@ -162,6 +166,12 @@ if __name__ == "__main__":
         sys.exit(0)
     if cmd == "bench64":
         bench([(20_000_000, 64, 64), (5_000_000, 64, 64), (5_000_000, 64, 16), (5_000_000, 64, 32), (5_000_000, 48, 24), (5_000_000, 48, 48), (5_000_000, 40, 40)])
+        sys.exit(0)
+    if cmd == "qbench":      # with and without the loading warp
+        np, torch, N, O = _mods()
+        for w in (0, 1):
+            N.load().hkm_debug_wl_pw(ctypes.c_int(w)); print("loading warp", w, flush=True)
+            bench([(20_000_000, 64, 64), (5_000_000, 64, 32), (5_000_000, 50, 20), (10_000_000, 32, 16), (5_000_000, 48, 48)])
         sys.exit(0)
     if cmd == "hbench":      # rows of 16 ns + 8 features: half slab against padding to whole slabs
         np, torch, N, O = _mods()
