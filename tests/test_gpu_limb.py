@@ -48,7 +48,7 @@ SHAPES = [(5000, 16, 16), (128, 16, 16), (127, 16, 9), (1, 16, 12), (200_000, 16
           # rows of 16 ns + 1..8 features: ns slabs of 16 and a half slab of 8 (64-byte rows, M = 64 limb product)
           (30000, 24, 12), (20000, 18, 9), (129, 24, 16), (50000, 36, 48), (200_000, 24, 32), (70001, 20, 64), (33000, 34, 20),
           # shapes served with a loading warp (64-feature rows; d = 32 with k <= 16)
-          (70001, 32, 16), (100, 32, 9), (9000, 64, 17), (20011, 64, 48), (300_000, 64, 64), (40000, 50, 12)]
+          (70001, 32, 16), (100, 32, 9), (9000, 64, 17), (20011, 64, 48), (300_000, 64, 64), (40000, 50, 20)]
 
 
 @pytest.mark.parametrize("n,d,k", SHAPES)
