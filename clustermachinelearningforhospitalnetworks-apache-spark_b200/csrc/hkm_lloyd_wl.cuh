@@ -645,15 +645,16 @@ __global__ void __launch_bounds__(GFIX * 128 * H + 32 * PW, 1) lloyd_wl_kernel(c
           }
         } else if (ract) { const double2 xv = __ldg(reinterpret_cast<const double2*>(xg + (size_t)src * d)); x0 = xv.x; x1 = xv.y; }
         double best = -__longlong_as_double(0x7ff0000000000000LL); int bj = -1;
+        constexpr int CB = 2;                                   // candidates scored side by side: an undecided row mostly has two
 #pragma unroll
         for (int qq = 0; qq < NW; ++qq) {
           uint32_t msk = cm[qq];
           while (msk) {
-            int jj[4]; double pp[4];
+            int jj[CB]; double pp[CB];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) { jj[u] = msk ? 32 * qq + __ffs(msk) - 1 : -1; msk &= msk - 1; }
+            for (int u = 0; u < CB; ++u) { jj[u] = msk ? 32 * qq + __ffs(msk) - 1 : -1; msk &= msk - 1; }
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
+            for (int u = 0; u < CB; ++u) {
               double c0 = 0.0, c1 = 0.0;
               if (ract && jj[u] >= 0) { const double* cr = Cr + (size_t)jj[u] * d + rlane; c0 = cr[0]; c1 = cr[1]; }
               pp[u] = fma(x0, c0, x1 * c1);
@@ -661,10 +662,10 @@ __global__ void __launch_bounds__(GFIX * 128 * H + 32 * PW, 1) lloyd_wl_kernel(c
 #pragma unroll
             for (int mk = RLANES / 2; mk >= 1; mk >>= 1) {
 #pragma unroll
-              for (int u = 0; u < 4; ++u) pp[u] += shfl_xor_d(pp[u], mk);
+              for (int u = 0; u < CB; ++u) pp[u] += shfl_xor_d(pp[u], mk);
             }
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
+            for (int u = 0; u < CB; ++u)
               if (jj[u] >= 0) { const double sc = pp[u] + cn_s[jj[u]]; if (sc > best) { best = sc; bj = jj[u]; } }
           }
         }
