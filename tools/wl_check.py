@@ -162,7 +162,8 @@ if __name__ == "__main__":
         np, torch, N, O = _mods()
         for f in (0, 1):
             N.load().hkm_debug_wl_flags(ctypes.c_int(f)); print("flags", f, flush=True)
-            bench([(20_000_000, 16, 16), (20_000_000, 16, 32), (10_000_000, 32, 16), (10_000_000, 32, 32), (5_000_000, 16, 12)])
+            bench([(20_000_000, 64, 64), (5_000_000, 64, 32), (10_000_000, 32, 16), (5_000_000, 48, 24)] if "wide" in sys.argv else
+                  [(20_000_000, 16, 16), (20_000_000, 16, 32), (10_000_000, 32, 16), (10_000_000, 32, 32), (5_000_000, 16, 12)])
         sys.exit(0)
     if cmd == "bench64":
         bench([(20_000_000, 64, 64), (5_000_000, 64, 64), (5_000_000, 64, 16), (5_000_000, 64, 32), (5_000_000, 48, 24), (5_000_000, 48, 48), (5_000_000, 40, 40)])
