@@ -128,7 +128,7 @@ if __name__ == "__main__":
         sys.exit(0)
     if cmd == "prof":
         np, torch, N, O = _mods()
-        for n, d, k in ([(20_000_000, 64, 64)] if "64" in sys.argv else [(20_000_000, 16, 16), (10_000_000, 32, 16), (20_000_000, 16, 32)]):
+        for n, d, k in ([(20_000_000, 64, 64)] if "64" in sys.argv else [(5_000_000, 24, 32), (5_000_000, 24, 16)] if "cfg5" in sys.argv else [(20_000_000, 16, 16), (10_000_000, 32, 16), (20_000_000, 16, 32)]):
             g = torch.Generator(device="cuda"); g.manual_seed(1)
             partial = torch.empty(k * d + k + 1, dtype=torch.float64, device="cuda"); scratch = N.new_scratch(d, k, "cuda")
             xs = torch.zeros(1, dtype=torch.float64, device="cuda")
@@ -136,7 +136,7 @@ if __name__ == "__main__":
             if "hospital" in sys.argv:      # bench.py's table and centres: first k rows, then 10 Lloyd steps
                 import hkm_b200
                 from hkm_b200 import datagen
-                X = datagen.hospital_matrix_device(n, d, k, 20250331, torch.device("cuda"))
+                X = datagen.hospital_matrix_device(n, d, 8 if "cfg5" in sys.argv else k, 20250331, torch.device("cuda"))
                 C = X[:k].clone(); st = N.new_state("cuda")
                 for it in range(10):
                     N.lloyd_step(X, C, partial, -1.0, st, scratch, xnorm2_sum=xs, xnorm2_mode=1 if it == 0 else 2)
