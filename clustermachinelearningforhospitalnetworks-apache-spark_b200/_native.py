@@ -17,7 +17,7 @@ EXPORTS = (
     "hkm_last_error", "hkm_version", "hkm_max_k", "hkm_max_k_single_pass", "hkm_max_d", "hkm_needs_workspace", "hkm_set_lloyd_variant",
     "hkm_assign_reduce_scratch_bytes", "hkm_assign_reduce", "hkm_update_centers", "hkm_update_centers_cosine", "hkm_lloyd_step", "hkm_lloyd_step_peer", "hkm_peer_exchange_bytes", "hkm_peer_exchange_slot_doubles",
     "hkm_kmpar_scratch_bytes", "hkm_kmpar_cost_update", "hkm_kmpar_sample", "hkm_kmpar_strip_rows", "hkm_closest_counts",
-    "hkm_silhouette_stats", "hkm_silhouette_score", "hkm_label_range",
+    "hkm_silhouette_stats", "hkm_silhouette_score", "hkm_label_range", "hkm_label_counts",
     "hkm_assemble_scratch_bytes", "hkm_assemble", "hkm_assemble_filtered", "hkm_fill_f64", "hkm_moments_scratch_bytes", "hkm_moments", "hkm_column_moments", "hkm_scale_rows", "hkm_normalize_rows", "hkm_local_kmeanspp",
 )
 
@@ -75,6 +75,7 @@ def load() -> ctypes.CDLL:
         L.hkm_local_kmeanspp.argtypes = [ctypes.c_int32, vp, vp, i32, i32, i32, i32, vp]
         L.hkm_silhouette_stats.argtypes = [vp, vp, vp, i64, i32, i32, vp, vp, sz, vp]
         L.hkm_label_range.argtypes = [vp, i64, vp, vp]
+        L.hkm_label_counts.argtypes = [vp, i64, i32, vp, vp]
         L.hkm_silhouette_score.argtypes = [vp, vp, vp, i64, i32, i32, vp, vp, vp, vp, sz, vp]
         _lib = L
     return _lib
@@ -219,6 +220,14 @@ def closest_counts(X, cand, labels_work, mind2_work, counts_out):
         rc = load().hkm_closest_counts(_ptr(X), n, d, _ptr(cand), cand.shape[0], _ptr(labels_work), _ptr(mind2_work),
                                        _ptr(counts_out), _stream())
     _check(rc)
+
+
+def label_counts(labels, m: int) -> torch.Tensor:
+    """hkm_label_counts: occurrences of each label in [0, m) as an int64 tensor on the labels' device."""
+    require_cuda(labels, "labels", torch.int32)
+    counts = torch.empty(m, dtype=torch.int64, device=labels.device)
+    _check(load().hkm_label_counts(_ptr(labels), labels.numel(), int(m), _ptr(counts), _stream()))
+    return counts
 
 
 def label_range(labels):

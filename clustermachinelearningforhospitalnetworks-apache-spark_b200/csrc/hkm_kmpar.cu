@@ -205,4 +205,17 @@ int hkm_closest_counts(const double* X, int64_t n, int d, const double* cand, in
   return HKM_OK;
 }
 
+int hkm_label_counts(const int32_t* labels, int64_t n, int m, unsigned long long* counts_out, void* stream) {
+  if (m < 1 || n < 0 || counts_out == nullptr || (n > 0 && labels == nullptr)) { set_error("hkm_label_counts: bad arguments"); return HKM_ERR_INVALID; }
+  if ((size_t)m * 4 > 200 * 1024) { set_error("hkm_label_counts: too many labels (%d)", m); return HKM_ERR_UNSUPPORTED; }
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  HKM_CUDA_TRY(cudaMemsetAsync(counts_out, 0, sizeof(unsigned long long) * (size_t)m, st));
+  if (n > 0) {
+    if ((size_t)m * 4 > 48 * 1024) HKM_CUDA_TRY(cudaFuncSetAttribute(label_counts_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, m * 4));
+    label_counts_kernel<<<sm_count() * 2, 256, (size_t)m * 4, st>>>(labels, n, m, counts_out);
+    HKM_CUDA_TRY(cudaGetLastError());
+  }
+  return HKM_OK;
+}
+
 }  // extern "C"

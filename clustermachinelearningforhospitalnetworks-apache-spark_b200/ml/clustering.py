@@ -376,9 +376,9 @@ def _predict_and_count(X: torch.Tensor, C: torch.Tensor):
     n, d = X.shape
     k = C.shape[0]
     labels = torch.empty(n, dtype=torch.int32, device=X.device)
-    partial = torch.zeros(k * d + k + 1, dtype=torch.float64, device=X.device)
     scratch = N.new_scratch(d, k, X.device)
-    N.assign_reduce(X, C, partial, labels=labels, scratch=scratch)
-    counts = partial[k * d:k * d + k].clone()
+    # a labels-only pass (no per-cluster sums: it runs at the rate of transform) and a histogram of the labels
+    N.assign_reduce(X, C, None, labels=labels, scratch=scratch, do_reduce=False)
+    counts = N.label_counts(labels, k)
     RT.all_reduce_sum(counts)
-    return labels, [int(round(v)) for v in counts.cpu().tolist()]
+    return labels, [int(v) for v in counts.cpu().tolist()]

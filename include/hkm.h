@@ -229,6 +229,13 @@ HKM_API int hkm_fill_f64(double* p, int64_t n, double value, void* stream);
 HKM_API int hkm_closest_counts(const double* X, int64_t n, int d, const double* cand, int m, int32_t* labels_work,
                                double* mind2_work, unsigned long long* counts_out, void* stream);
 
+/*
+ * counts_out[j] = number of rows with labels[i] == j, j in [0, m) (labels outside the range are not counted): the cluster sizes of a
+ * KMeansSummary (`KMeansModel.summary.clusterSizes`, pyspark.ml.clustering) from the labels of a transform pass
+ * (hkm_assign_reduce with do_reduce = 0), so that the summary needs no second reducing pass over the rows.
+ */
+HKM_API int hkm_label_counts(const int32_t* labels, int64_t n, int m, unsigned long long* counts_out, void* stream);
+
 /* ---------------------------------------------------------------------------------------------
  * ClusteringEvaluator silhouette, squared Euclidean (ml/evaluation/ClusteringMetrics.scala,
  * SURVEY 8a-10 / 8a-11).  Scratch: hkm_assign_reduce_scratch_bytes(d, k).

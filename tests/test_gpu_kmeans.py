@@ -244,3 +244,17 @@ def test_more_than_64_clusters(hkm, oracle, n, d, k):
     m2, ref = _fit_both(hkm, oracle, X, k, 11, P=4, max_iter=3)
     _assert_model_matches(m2, ref)
     assert model.predict(X[0]) == int(model.summary.predictions.to_numpy("prediction")[0])
+
+
+@pytest.mark.gpu
+def test_label_counts_matches_bincount(hkm):
+    """hkm_label_counts (cluster sizes of a summary from the labels of a transform pass): every label in [0, m) counted once,
+    labels outside the range ignored, empty input -> zeros."""
+    import torch
+    from hkm_b200 import _native as N
+    rng = np.random.default_rng(5)
+    for n, m in ((0, 3), (1, 1), (1000, 7), (300_001, 64), (50_000, 1000)):
+        lab = rng.integers(-2, m + 2, size=n).astype(np.int32)
+        got = N.label_counts(torch.from_numpy(lab).cuda(), m).cpu().numpy()
+        ok = lab[(lab >= 0) & (lab < m)]
+        assert np.array_equal(got, np.bincount(ok, minlength=m).astype(np.int64))
