@@ -95,11 +95,14 @@ bool lloyd_wl_shape(const LloydParams& p, int mode) {
 }
 
 // Distance-returning passes the same kernel takes without the limb sums (k-means|| cost update and candidate weights: running
-// minimum of the squared distance, labels, cost sum): 8 < k <= 64 centres per launch, even d <= 48
+// minimum of the squared distance, labels, cost sum) and labels-only passes (transform): 8 < k <= 64 centres per launch, even d <= 48
 bool lloyd_wd_shape(const LloydParams& p, int mode) {
   const int variant = lloyd_variant_override();
   if (g_wl_off || (variant != 0 && variant != 7)) return false;
-  if (mode != 0 || p.w != nullptr || p.mind2_out == nullptr || (p.do_reduce != 0 && p.do_reduce != 2)) return false;
+  if (mode != 0 || p.w != nullptr || (p.do_reduce != 0 && p.do_reduce != 2)) return false;
+  // with distances: any output mode; labels only (transform / predict): a plain pass that writes every row's label
+  // (k <= 16: the warp-group kernel's labels-only pass is already at the HBM rate -- 1.01 against 0.96 here)
+  if (p.mind2_out == nullptr && (p.labels_out == nullptr || p.do_reduce != 0 || p.out_mode != 0 || p.k <= 16)) return false;
   if (p.k <= 8 || p.k > 64 || p.d > 48 || p.d < 2 || (p.d & 1)) return false;
   if (p.n >= (int64_t)1 << 31) return false;
   const int kp = ((p.k + 15) / 16) * 16;

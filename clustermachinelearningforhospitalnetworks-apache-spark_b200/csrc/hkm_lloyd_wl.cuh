@@ -690,6 +690,15 @@ __global__ void __launch_bounds__(GFIX * 128 * H + 32 * PW, 1) lloyd_wl_kernel(c
       if (prof) pw2 += clock64() - tr0;
     }
     if constexpr (DIST != 0) {
+      if (p.mind2_out == nullptr) {
+        // labels only (transform / predict): nothing else to compute for the row
+        if (valid) p.labels_out[((int64_t)blockIdx.x + (int64_t)i * gridDim.x) * kTileRows + row] = lab;
+        __syncwarp();
+        if (i + S < T) tma_load(i + S, xs, bar_f, seqa);
+        s += G; if (s >= S) { s -= S; ph ^= 1u; }
+        tph ^= 1u;
+        continue;
+      }
       // ---- exact distance to the winner from the row's fp64 values (the stage still holds them) and the padded centre table:
       // score = x.c - 0.5|c|^2 and |x|^2 in ascending feature order, dist = max(|x|^2 - 2 score, 0), as every other variant
       double sc = 0.0, xx = 0.0;

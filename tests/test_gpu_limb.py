@@ -208,3 +208,28 @@ def test_distance_variant_kmpar_passes(hkm, n, d, m):
         assert np.abs(mind2 - dist.min(axis=1)).max() <= 1e-9 * scale
         assert counts.sum() == n and np.array_equal(counts, np.bincount(labels, minlength=m))
     assert (outs[0][2] == outs[1][2]).mean() >= 0.9999 and np.abs(outs[0][0] - outs[1][0]).max() <= 1e-9 * scale
+
+
+@pytest.mark.parametrize("n,d,k,spread", [(30011, 24, 32, 1.5), (1, 16, 17, 1.5), (129, 48, 64, 1.5), (70001, 16, 40, 0.2), (50000, 30, 33, 0.3),
+                                          (20000, 2, 20, 1.0), (9000, 48, 17, 0.2)])
+def test_labels_only_pass_k_over_16(hkm, oracle, n, d, k, spread):
+    """transform / predict with 16 < k <= 64, even d <= 48: the labels-only form of the distance-returning kernel -- labels
+    array_equal to the oracle (also on overlapping clusters, where many rows are re-scored exactly), equal to those of the
+    kernel it replaces, and nothing else written."""
+    N = hkm._native
+    Xh, Ch = _blobs(n, d, k, seed=n + d + k, spread=spread)
+    _, _, _, olab = oracle.lloyd_pass(Xh, Ch, P=1, want_labels=True)
+    X = torch.from_numpy(Xh).cuda(); C = torch.from_numpy(Ch).cuda()
+    lib = N.load()
+    got = []
+    for off in (0, 1):
+        lib.hkm_debug_wl_off(ctypes.c_int(off))
+        try:
+            labels = torch.full((n,), -9, dtype=torch.int32, device="cuda")
+            N.assign_reduce(X, C, None, labels=labels, scratch=N.new_scratch(d, k, "cuda"), do_reduce=False)
+            torch.cuda.synchronize()
+        finally:
+            lib.hkm_debug_wl_off(ctypes.c_int(0))
+        got.append(labels.cpu().numpy())
+    assert np.array_equal(got[0], olab)
+    assert np.array_equal(got[1], olab)
