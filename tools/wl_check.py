@@ -112,6 +112,22 @@ if __name__ == "__main__":
             print(out, flush=True)
         print("ALL OK" if bad == 0 else f"FAILED {bad}")
         sys.exit(0 if bad == 0 else 1)
+    if cmd == "soak":        # python tools/wl_check.py soak [cases] [seed]: random limb shapes against the oracle, in one process
+        import random
+        cases = int(sys.argv[2]) if len(sys.argv) > 2 else 150
+        rnd = random.Random(int(sys.argv[3]) if len(sys.argv) > 3 else 1)
+        bad = 0
+        for it in range(cases):
+            d = 2 * rnd.randint(1, 32); k = rnd.randint(9, 64)
+            n = rnd.choice([1, 31, 127, 128, 129, 1000, rnd.randint(2, 70000), rnd.randint(2, 300000)])
+            kind = rnd.choice(["blobs", "blobs", "close", "close", "offset", "scales"])
+            try:
+                ok = one(n, d, k, kind)
+            except Exception as e:                      # noqa: BLE001
+                ok = False; print("EXC", n, d, k, kind, repr(e)[:200], flush=True)
+            bad += 0 if ok else 1
+        print("SOAK OK" if bad == 0 else f"SOAK FAILED {bad}")
+        sys.exit(0 if bad == 0 else 1)
     if cmd == "single":     # python tools/wl_check.py single n d k: STORE pass, then three REUSE passes (for ncu)
         np, torch, N, O = _mods()
         n, d, k = int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4])
