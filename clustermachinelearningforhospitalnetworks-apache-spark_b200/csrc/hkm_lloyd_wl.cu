@@ -166,20 +166,22 @@ static int make_tmap(const LloydParams& p, CUtensorMap& tmap, int box_cols = 16)
   return HKM_OK;
 }
 
-template <int KP, int NS>
-static int launch_wd(const LloydParams& p, const CUtensorMap& tmap, cudaStream_t st) {
-  constexpr int G = wl_groups_dist(16 * NS, KP);
+template <int KP, int NS, int HS = 0>
+static int launch_wd(const LloydParams& p, const CUtensorMap& tmap, const CUtensorMap& tmap_h, cudaStream_t st) {
+  constexpr int DPAD = 16 * NS + 8 * HS;
+  constexpr int G = wl_groups_dist(DPAD, KP);
+  static_assert(HS == 0 || G > 0, "half-slab shapes must fit wherever the padded shape does");
   if constexpr (G == 0) { set_error("lloyd_wd: d=%d k=%d does not fit", p.d, p.k); return HKM_ERR_UNSUPPORTED; }
   else {
-    constexpr WlPlan L = wl_plan(16 * NS, KP, G, wl_stages(16 * NS, KP, G, 1, 1), 1, 1);
-    auto kern = lloyd_wl_kernel<KP, NS, G, 1, 1>;
+    constexpr WlPlan L = wl_plan(DPAD, KP, G, wl_stages(DPAD, KP, G, 1, 1), 1, 1);
+    auto kern = lloyd_wl_kernel<KP, NS, G, 1, 1, HS>;
     static bool attr_done[64];
     int dev = 0; HKM_CUDA_TRY(cudaGetDevice(&dev));
     if (dev >= 64 || !attr_done[dev]) {
       HKM_CUDA_TRY(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L.total));
       if (dev < 64) attr_done[dev] = true;
     }
-    kern<<<sm_count(), G * 128, L.total, st>>>(p, tmap, tmap, nullptr, g_wl_prof, 0);
+    kern<<<sm_count(), G * 128, L.total, st>>>(p, tmap, tmap_h, nullptr, g_wl_prof, 0);
     HKM_CUDA_TRY(cudaGetLastError());
     return HKM_OK;
   }
@@ -190,7 +192,18 @@ int launch_lloyd_wd(const LloydParams& p, cudaStream_t st) {
   const int rc = make_tmap(p, tmap);
   if (rc != HKM_OK) return rc;
   const int kp = ((p.k + 15) / 16) * 16, ns = (p.d + 15) / 16;
-#define HKM_WD_CASE(KPV, NSV) if (kp == KPV && ns == NSV) return launch_wd<KPV, NSV>(p, tmap, st);
+  // rows of 16 ns + 1 .. 16 ns + 8 features: ns slabs and a half slab, as in the reducing variant
+  const int r16 = p.d % 16;
+  if (r16 >= 1 && r16 <= 8 && p.d > 16 && p.d <= 40 && !g_wl_nohalf) {
+    CUtensorMap tmap_h;
+    { const int rc2 = make_tmap(p, tmap_h, 8); if (rc2 != HKM_OK) return rc2; }
+    const int nsf = p.d / 16;
+#define HKM_WDH_CASE(KPV, NSV) if (kp == KPV && nsf == NSV) return launch_wd<KPV, NSV, 1>(p, tmap, tmap_h, st);
+    HKM_WDH_CASE(16, 1) HKM_WDH_CASE(32, 1) HKM_WDH_CASE(48, 1) HKM_WDH_CASE(64, 1)
+    HKM_WDH_CASE(16, 2) HKM_WDH_CASE(32, 2) HKM_WDH_CASE(48, 2) HKM_WDH_CASE(64, 2)
+#undef HKM_WDH_CASE
+  }
+#define HKM_WD_CASE(KPV, NSV) if (kp == KPV && ns == NSV) return launch_wd<KPV, NSV>(p, tmap, tmap, st);
   HKM_WD_CASE(16, 1) HKM_WD_CASE(32, 1) HKM_WD_CASE(48, 1) HKM_WD_CASE(64, 1)
   HKM_WD_CASE(16, 2) HKM_WD_CASE(32, 2) HKM_WD_CASE(48, 2) HKM_WD_CASE(64, 2)
   HKM_WD_CASE(16, 3) HKM_WD_CASE(32, 3) HKM_WD_CASE(48, 3) HKM_WD_CASE(64, 3)

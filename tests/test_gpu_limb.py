@@ -170,7 +170,7 @@ def test_fit_with_limb_passes_matches_oracle(hkm, oracle):
 
 
 @pytest.mark.parametrize("n,d,m", [(50000, 16, 12), (30011, 24, 33), (40000, 32, 64), (20000, 48, 20), (129, 16, 16), (70003, 8, 40), (60000, 16, 100),
-                                   (50000, 20, 9)])
+                                   (50000, 20, 9), (33001, 18, 17), (20000, 40, 64), (9000, 34, 48), (5, 24, 12)])
 def test_distance_variant_kmpar_passes(hkm, n, d, m):
     """k-means|| data passes on the distance-returning variant of the same kernel (running minimum of the squared distance to the
     new centres, its sum, nearest candidate per row and the counts): against NumPy in the oracle's arithmetic, and against the
@@ -211,7 +211,7 @@ def test_distance_variant_kmpar_passes(hkm, n, d, m):
 
 
 @pytest.mark.parametrize("n,d,k,spread", [(30011, 24, 32, 1.5), (1, 16, 17, 1.5), (129, 48, 64, 1.5), (70001, 16, 40, 0.2), (50000, 30, 33, 0.3),
-                                          (20000, 2, 20, 1.0), (9000, 48, 17, 0.2)])
+                                          (20000, 2, 20, 1.0), (9000, 48, 17, 0.2), (40001, 20, 64, 0.3), (7000, 40, 24, 1.0)])
 def test_labels_only_pass_k_over_16(hkm, oracle, n, d, k, spread):
     """transform / predict with 16 < k <= 64, even d <= 48: the labels-only form of the distance-returning kernel -- labels
     array_equal to the oracle (also on overlapping clusters, where many rows are re-scored exactly), equal to those of the
