@@ -43,18 +43,23 @@ class NvmlSampler(threading.Thread):
 
     REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
-    def __init__(self, index: int, period_s: float = 0.004):
+    # One sample when the region starts, then one every 20 ms.  Measured at N = 2 (profiles/r02_sampler_skew.txt): with a 4 ms period
+    # the sampled rank arrived 7 us later at every step's exchange (0.4361 ms per step against 0.4282 without a sampler); at N = 1
+    # the period makes no difference.  HKM_BENCH_NVML_PERIOD / HKM_BENCH_SAMPLER_RANK are developer switches for that measurement.
+    def __init__(self, index: int, period_s: float = float(os.environ.get("HKM_BENCH_NVML_PERIOD", "0.02"))):
         super().__init__(daemon=True)
         import pynvml
         self.nv = pynvml
         pynvml.nvmlInit()
         self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
-        self.period, self.sm, self.bits, self._stop_evt = period_s, [], 0, threading.Event()
+        self.period, self.sm, self.bits, self._stop_evt, self._go = period_s, [], 0, threading.Event(), threading.Event()
         self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
 
     def run(self):
         nv = self.nv
         getr = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        self._go.wait()        # the thread is started before the ranks' barrier (its start-up must not delay this rank's first step)
+        self._stop_evt.wait(0.002)   # first sample two milliseconds into the region: the GPU is under load by then
         while not self._stop_evt.is_set():
             try:
                 self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
@@ -63,7 +68,11 @@ class NvmlSampler(threading.Thread):
                 pass
             self._stop_evt.wait(self.period)
 
+    def go(self):
+        self._go.set()
+
     def stop(self):
+        self._go.set()
         self._stop_evt.set()
         self.join(timeout=2)
         busy = [s for s in self.sm if s > 0.5 * self.mx] or self.sm
@@ -86,9 +95,13 @@ class ClockSampler(threading.Thread):
 
     def __init__(self, index: int):
         super().__init__(daemon=True)
-        self.index, self.rows, self._stop_evt = index, [], threading.Event()
+        self.index, self.rows, self._stop_evt, self._go = index, [], threading.Event(), threading.Event()
+
+    def go(self):
+        self._go.set()
 
     def run(self):
+        self._go.wait()
         while not self._stop_evt.is_set():
             try:
                 out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
@@ -100,6 +113,7 @@ class ClockSampler(threading.Thread):
             self._stop_evt.wait(0.2)
 
     def stop(self):
+        self._go.set()
         self._stop_evt.set()
         self.join(timeout=6)
         sm, mx, reasons = [], 0.0, set()
@@ -319,11 +333,13 @@ def main():
         # N == 1: a step IS one launch of the kernel, so the region's own events time it; N > 1: bracket each launch
         kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)] if world > 1 else None
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        sampler = make_sampler(local_rank) if (rank == 0 and sample_clocks) else None
-        barrier()
+        sampler = make_sampler(local_rank) if (rank == int(os.environ.get("HKM_BENCH_SAMPLER_RANK", "0")) and sample_clocks) else None
         if sampler:
-            sampler.start()
+            sampler.start()              # armed here, released after the barrier
+        barrier()
         e0.record()
+        if sampler:
+            sampler.go()
         for i in range(steps):
             step(2, kev[i] if kev else None)
         e1.record()
